@@ -1,0 +1,112 @@
+/*
+ * b200_w4a16.h -- C ABI of the B200-native W4A16 group-quantized GEMM library
+ * (libb200_w4a16.so, sm_100a only, no CPU fallback).
+ *
+ * This is the drop-in boundary for the QUICK/AWQ hot path of SqueezeBits/vllm-quick.
+ * The reference binds C++ functions taking torch::Tensor directly through pybind11
+ * (csrc/pybind.cpp:51-55, csrc/ops.h:68-83); it has no C ABI.  Each entry point below
+ * names the reference interface it replaces.  All pointers are DEVICE pointers on the
+ * current CUDA device unless stated otherwise; tensors are dense row-major; `half` is
+ * IEEE binary16 passed as uint16_t storage.  Nothing here allocates, synchronises or
+ * throws: every call validates its arguments, enqueues work on `stream` and returns a
+ * b200_status_t.  All entry points are CUDA-graph capturable.
+ *
+ * Weight layouts (`layout` argument):
+ *   B200_LAYOUT_AWQ  (0): qweight[K, N/8] int32, eight 4-bit values per word with logical
+ *                         element j in nibble {0,4,1,5,2,6,3,7}[j]  -- the checkpoint
+ *                         format the reference consumes (csrc/quantization/awq/dequantize.cuh:17-84).
+ *   B200_LAYOUT_B200 (1): the tile-major, K-packed interleave produced by
+ *                         b200_w4a16_repack: 128x128 tiles of 2048
+ *                         words, word j*512+c*4+w of tile (nt,kb) holding channel nt*128+c,
+ *                         rows kb*128+(j*4+w)*8+e, e=0..7 in nibble {0,4,1,5,2,6,3,7}[e].
+ * scales[K/G, N] half and qzeros[K/G, N/8] int32 stay in checkpoint format for both.
+ */
+#ifndef B200_W4A16_H_
+#define B200_W4A16_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st *b200_stream_t; /* == cudaStream_t */
+
+typedef enum {
+  B200_OK = 0,
+  B200_ERR_BAD_SHAPE = 1,  /* shape precondition violated (reference: std::invalid_argument,
+                              csrc/quantization/awq/gemm_kernels.cu:412-419) */
+  B200_ERR_BAD_ARG = 2,    /* null / misaligned pointer, unknown layout */
+  B200_ERR_WORKSPACE = 3,  /* workspace missing or smaller than b200_w4a16_workspace_bytes */
+  B200_ERR_CUDA = 4,       /* a CUDA runtime / driver call failed (see b200_w4a16_last_cuda_error) */
+  B200_ERR_NO_DEVICE = 5   /* no sm_100 device: the library has no fallback path */
+} b200_status_t;
+
+enum { B200_LAYOUT_AWQ = 0, B200_LAYOUT_B200 = 1 };
+enum { B200_REPACK_AWQ_TO_B200 = 0, B200_REPACK_B200_TO_AWQ = 1 };
+
+/* ABI version (major*100 + minor). */
+int b200_w4a16_version(void);
+
+/* Static string for a status code. */
+const char *b200_w4a16_strerror(int status);
+
+/* cudaError_t of the last failing CUDA call seen by this thread (0 if none). */
+int b200_w4a16_last_cuda_error(void);
+
+/* Number of int32 words of the B200-layout tensor for a [K, N/8] AWQ qweight
+ * (== K*N/8 when N % 128 == 0; N % 128 == 64 pads the last tile column). */
+size_t b200_w4a16_repacked_words(int K, int N);
+
+/* Bytes of zero-initialised scratch b200_w4a16_gemm needs for this problem.  The caller
+ * zero-fills it ONCE; every launch leaves it zeroed again.  One workspace may be shared by
+ * all GEMMs issued on one stream (size it for the largest).  `layout` B200_LAYOUT_AWQ adds
+ * room for an on-the-fly repack.
+ * Replaces: the internal `torch::empty({split_k, M, N})` scratch of awq_gemm
+ * (csrc/quantization/awq/gemm_kernels.cu:401). */
+size_t b200_w4a16_workspace_bytes(int M, int K, int N, int layout);
+
+/* y[M,N] = x[M,K] . dequant(qweight, scales, qzeros), fp16 in / fp32 accumulate / fp16 out.
+ * Replaces: awq_gemm(in_feats, kernel, scaling_factors, zeros, split_k_iters)
+ *           (csrc/ops.h:69-74, csrc/quantization/awq/gemm_kernels.cu:389-446), including
+ *           its trailing `.sum(0)` reduction kernel (:445), and the dequantize + torch.matmul
+ *           branch of AWQLinearMethod.apply_weights for >= 256 tokens
+ *           (vllm/model_executor/layers/quantization/awq.py:154-159).
+ * Preconditions (B200_ERR_BAD_SHAPE otherwise): M >= 0, N % 64 == 0, G % 32 == 0,
+ * K % G == 0, K % 128 == 0, G in {32, 64} or G % 128 == 0.  M == 0 is a no-op.
+ * `split_k_hint` is the reference's split_k_iters: accepted, used only as a tuning hint
+ * (<= 0 lets the library choose). */
+int b200_w4a16_gemm(const uint16_t *x, const int32_t *qweight, const uint16_t *scales,
+                    const int32_t *qzeros, uint16_t *y, int M, int K, int N, int G,
+                    int layout, int split_k_hint, void *workspace, size_t workspace_bytes,
+                    b200_stream_t stream);
+
+/* W[K,N] half = fp16((q - z) * s), bit-exact with the reference.
+ * Replaces: awq_dequantize(kernel, scaling_factors, zeros, split_k_iters, thx, thy)
+ *           (csrc/ops.h:76-82, csrc/quantization/awq/gemm_kernels.cu:274-381); the three
+ *           trailing launch-shape arguments of the reference have no meaning here.
+ * Preconditions: N % 8 == 0 (AWQ layout) / N % 64 == 0 (B200 layout), K % G == 0,
+ * K % 128 == 0 for the B200 layout. */
+int b200_w4a16_dequant(const int32_t *qweight, const uint16_t *scales, const int32_t *qzeros,
+                       uint16_t *W, int K, int N, int G, int layout, b200_stream_t stream);
+
+/* Layout conversion of qweight between the checkpoint format and the B200 interleave
+ * (a bijection on the nibbles; `dst` has b200_w4a16_repacked_words(K,N) words for
+ * AWQ_TO_B200 and K*N/8 words for B200_TO_AWQ).  src and dst must not overlap.
+ * Replaces: nothing in the mounted checkout (QUICK's offline interleave is not vendored,
+ * SURVEY.md F1); precedent for a post-load shuffle is gptq_shuffle
+ * (vllm/model_executor/layers/quantization/gptq.py:195-204).
+ * Preconditions: K % 128 == 0, N % 64 == 0. */
+int b200_w4a16_repack(const int32_t *src, int32_t *dst, int K, int N, int direction,
+                      b200_stream_t stream);
+
+/* Introspection for tests and benchmarks: how the library would launch the GEMM.
+ * Fills tok_tile (tokens per CTA tile), split_k, grid (CTAs), smem_bytes; returns status. */
+int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int *tok_tile,
+                         int *split_k, int *grid, int *smem_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_W4A16_H_ */

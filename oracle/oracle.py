@@ -1,0 +1,223 @@
+"""CPU oracle for the W4A16 (AWQ / QUICK) hot path -- TEST INFRASTRUCTURE ONLY.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import this module; the product package
+(``vllm-quick_b200/``) never does and fails loudly without its CUDA library.
+
+Two independent restatements of the reference arithmetic live here:
+
+* ``liboracle.so`` (``awq_oracle.c``) -- plain C, including a bit-level emulation of the
+  reference's PTX sequence (``csrc/quantization/awq/dequantize.cuh:17-84``);
+* the NumPy functions below (``np_*``) -- shift/mask unpack and
+  ``fp16((q - z) * s)`` (``csrc/quantization/awq/gemm_kernels.cu:153-160``).
+
+Parity pinning: the reference has no golden vectors for this path.
+``tests/golden/`` holds outputs of the reference's own kernels compiled unmodified for
+sm_100a (``oracle/build_ref.sh``) once a B200 run has produced them; see
+``tests/golden/README.md`` for the current state.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from typing import Tuple
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liboracle.so")
+
+# Logical element j of a packed word sits in nibble AWQ_ORDER[j]
+# (dequantize.cuh:42-56: lop3 pairs (0,4) (1,5) (2,6) (3,7)).
+AWQ_ORDER = (0, 4, 1, 5, 2, 6, 3, 7)
+
+
+def build(force: bool = False) -> str:
+    """Compile ``liboracle.so`` with the committed Makefile (gcc only)."""
+    if force or not os.path.exists(_LIB_PATH) or (
+        os.path.getmtime(_LIB_PATH) < os.path.getmtime(os.path.join(_HERE, "awq_oracle.c"))
+    ):
+        subprocess.run(["make", "-C", _HERE, "-s"] + (["-B"] if force else []), check=True)
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        build()
+        L = ctypes.CDLL(_LIB_PATH)
+        vp, i32 = ctypes.c_void_p, ctypes.c_int
+        L.oracle_awq_dequantize.argtypes = [vp, vp, vp, vp, i32, i32, i32]
+        L.oracle_awq_dequantize_lop3.argtypes = [vp, vp, vp, vp, i32, i32, i32]
+        L.oracle_gemm_f32.argtypes = [vp, vp, vp, vp, i32, i32, i32]
+        L.oracle_gemm_ref_splitk.argtypes = [vp, vp, vp, i32, i32, i32, i32]
+        L.oracle_awq_pack.argtypes = [vp, vp, i32, i32]
+        L.oracle_awq_unpack.argtypes = [vp, vp, i32, i32]
+        L.oracle_b200_repack.argtypes = [vp, vp, i32, i32]
+        L.oracle_b200_unrepack.argtypes = [vp, vp, i32, i32]
+        L.oracle_b200_words.argtypes = [i32, i32]
+        L.oracle_b200_words.restype = ctypes.c_size_t
+        L.oracle_dequant_word_lop3.argtypes = [ctypes.c_uint32, vp]
+        for f in ("oracle_awq_dequantize", "oracle_awq_dequantize_lop3", "oracle_gemm_f32",
+                  "oracle_gemm_ref_splitk", "oracle_awq_pack", "oracle_awq_unpack",
+                  "oracle_b200_repack", "oracle_b200_unrepack", "oracle_dequant_word_lop3"):
+            getattr(L, f).restype = None
+        _lib = L
+    return _lib
+
+
+def _p(a: np.ndarray) -> ctypes.c_void_p:
+    assert a.flags["C_CONTIGUOUS"]
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+# ----------------------------------------------------------------------------- C oracle
+
+def dequantize(qweight: np.ndarray, scales: np.ndarray, qzeros: np.ndarray,
+               lop3: bool = False) -> np.ndarray:
+    """``W[K,N]`` fp16 from AWQ tensors (gemm_kernels.cu:274-327 semantics)."""
+    K, NW = qweight.shape
+    N = NW * 8
+    G = K // scales.shape[0]
+    qweight = np.ascontiguousarray(qweight, dtype=np.int32)
+    qzeros = np.ascontiguousarray(qzeros, dtype=np.int32)
+    s16 = np.ascontiguousarray(scales, dtype=np.float16).view(np.uint16)
+    W = np.empty((K, N), dtype=np.uint16)
+    fn = lib().oracle_awq_dequantize_lop3 if lop3 else lib().oracle_awq_dequantize
+    fn(_p(qweight), _p(s16), _p(qzeros), _p(W), K, N, G)
+    return W.view(np.float16)
+
+
+def gemm_f32(x: np.ndarray, W: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """fp32 dequant-then-matmul oracle: returns (Y fp32, Y rounded to fp16)."""
+    M, K = x.shape
+    N = W.shape[1]
+    x16 = np.ascontiguousarray(x, dtype=np.float16).view(np.uint16)
+    w16 = np.ascontiguousarray(W, dtype=np.float16).view(np.uint16)
+    Yf = np.empty((M, N), dtype=np.float32)
+    Yh = np.empty((M, N), dtype=np.uint16)
+    lib().oracle_gemm_f32(_p(x16), _p(w16), _p(Yf), _p(Yh), M, K, N)
+    return Yf, Yh.view(np.float16)
+
+
+def gemm_ref_splitk(x: np.ndarray, W: np.ndarray, split_k: int = 8) -> np.ndarray:
+    """Model of the reference's fp16-partial split-K numerics (gemm_kernels.cu:112-115,262-270,445)."""
+    M, K = x.shape
+    N = W.shape[1]
+    x16 = np.ascontiguousarray(x, dtype=np.float16).view(np.uint16)
+    w16 = np.ascontiguousarray(W, dtype=np.float16).view(np.uint16)
+    Yh = np.empty((M, N), dtype=np.uint16)
+    lib().oracle_gemm_ref_splitk(_p(x16), _p(w16), _p(Yh), M, K, N, split_k)
+    return Yh.view(np.float16)
+
+
+def awq_gemm(x, qweight, scales, qzeros) -> np.ndarray:
+    """Oracle for ``ops.awq_gemm`` / ``ops.quick_gemm``: fp16 of the fp32 matmul."""
+    return gemm_f32(x, dequantize(qweight, scales, qzeros))[1]
+
+
+def pack(q: np.ndarray) -> np.ndarray:
+    """``q[K,N]`` uint8 nibble values -> AWQ ``qweight[K,N/8]`` int32."""
+    K, N = q.shape
+    q = np.ascontiguousarray(q, dtype=np.uint8)
+    out = np.empty((K, N // 8), dtype=np.int32)
+    lib().oracle_awq_pack(_p(q), _p(out), K, N)
+    return out
+
+
+def unpack(qweight: np.ndarray) -> np.ndarray:
+    K, NW = qweight.shape
+    qweight = np.ascontiguousarray(qweight, dtype=np.int32)
+    out = np.empty((K, NW * 8), dtype=np.uint8)
+    lib().oracle_awq_unpack(_p(qweight), _p(out), K, NW * 8)
+    return out
+
+
+def b200_words(K: int, N: int) -> int:
+    return int(lib().oracle_b200_words(K, N))
+
+
+def b200_repack(qweight: np.ndarray) -> np.ndarray:
+    """AWQ ``qweight[K,N/8]`` -> tile-major K-packed B200 layout (flat int32)."""
+    K, NW = qweight.shape
+    qweight = np.ascontiguousarray(qweight, dtype=np.int32)
+    out = np.empty(b200_words(K, NW * 8), dtype=np.int32)
+    lib().oracle_b200_repack(_p(qweight), _p(out), K, NW * 8)
+    return out
+
+
+def b200_unrepack(packed: np.ndarray, K: int, N: int) -> np.ndarray:
+    packed = np.ascontiguousarray(packed, dtype=np.int32)
+    out = np.empty((K, N // 8), dtype=np.int32)
+    lib().oracle_b200_unrepack(_p(packed), _p(out), K, N)
+    return out
+
+
+def dequant_word_lop3(w: int) -> np.ndarray:
+    out = np.empty(8, dtype=np.uint16)
+    lib().oracle_dequant_word_lop3(ctypes.c_uint32(w & 0xFFFFFFFF), _p(out))
+    return out.view(np.float16)
+
+
+# ----------------------------------------------------------------------------- NumPy restatement
+
+def np_unpack(qweight: np.ndarray) -> np.ndarray:
+    """Shift/mask unpack in logical order (dequantize.cuh:17-84 restated)."""
+    w = qweight.astype(np.int64) & 0xFFFFFFFF
+    shifts = np.array([4 * o for o in AWQ_ORDER], dtype=np.int64)
+    nib = (w[..., None] >> shifts) & 0xF
+    return nib.reshape(*qweight.shape[:-1], qweight.shape[-1] * 8).astype(np.uint8)
+
+
+def np_pack(q: np.ndarray) -> np.ndarray:
+    q = q.astype(np.int64).reshape(*q.shape[:-1], q.shape[-1] // 8, 8)
+    shifts = np.array([4 * o for o in AWQ_ORDER], dtype=np.int64)
+    w = ((q & 0xF) << shifts).sum(axis=-1) & 0xFFFFFFFF
+    return w.astype(np.uint32).view(np.int32)
+
+
+def np_dequantize(qweight: np.ndarray, scales: np.ndarray, qzeros: np.ndarray) -> np.ndarray:
+    """``fp16((q - z) * s + 0)`` with the reference's pairing (gemm_kernels.cu:128-160)."""
+    K = qweight.shape[0]
+    G = K // scales.shape[0]
+    q = np_unpack(qweight).astype(np.float32)
+    z = np.repeat(np_unpack(qzeros).astype(np.float32), G, axis=0)
+    s = np.repeat(scales.astype(np.float32), G, axis=0)
+    return ((q - z) * s + np.float32(0.0)).astype(np.float16)
+
+
+def np_gemm(x: np.ndarray, W: np.ndarray) -> np.ndarray:
+    return x.astype(np.float32) @ W.astype(np.float32)
+
+
+def np_b200_repack(qweight: np.ndarray) -> np.ndarray:
+    """Vectorised restatement of the B200 layout, N % 128 == 0 or 64."""
+    K, NW = qweight.shape
+    N = NW * 8
+    NT, KB = (N + 127) // 128, K // 128
+    q = np.zeros((K, NT * 128), dtype=np.int64)
+    q[:, :N] = np_unpack(qweight)
+    # [kb, j, w, e, nt, c] -> [nt, kb, j, c, w, e]
+    q = q.reshape(KB, 4, 4, 8, NT, 128).transpose(4, 0, 1, 5, 2, 3)
+    shifts = np.array([4 * o for o in AWQ_ORDER], dtype=np.int64)
+    words = ((q & 0xF) << shifts).sum(axis=-1) & 0xFFFFFFFF
+    return words.astype(np.uint32).view(np.int32).reshape(-1)
+
+
+# ----------------------------------------------------------------------------- synthetic inputs
+
+def make_inputs(M: int, K: int, N: int, G: int = 128, seed: int = 0, signed_scales: bool = False):
+    """Seeded synthetic AWQ tensors: x ~ N(0,1) fp16, uniform nibbles,
+    scales ~ U(1e-3, 2e-2) fp16.  NumPy generator so CPU and GPU tests share inputs."""
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal((M, K), dtype=np.float32).astype(np.float16)
+    qweight = rng.integers(-2**31, 2**31, size=(K, N // 8), dtype=np.int64).astype(np.int32)
+    qzeros = rng.integers(-2**31, 2**31, size=(K // G, N // 8), dtype=np.int64).astype(np.int32)
+    scales = rng.uniform(1e-3, 2e-2, size=(K // G, N)).astype(np.float16)
+    if signed_scales:
+        scales = (scales * rng.choice([-1.0, 1.0], size=scales.shape)).astype(np.float16)
+    return x, qweight, scales, qzeros
