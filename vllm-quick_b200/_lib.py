@@ -1,0 +1,99 @@
+"""ctypes binding of ``libb200_w4a16.so`` (the C ABI in ``include/b200_w4a16.h``).
+
+There is no fallback: if the library is missing or cannot be loaded every op raises.
+``build()`` compiles it in-tree with nvcc for sm_100a (works without a GPU).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from typing import Optional
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libb200_w4a16.so")
+CSRC = os.path.join(_PKG, "csrc")
+
+B200_OK, B200_ERR_BAD_SHAPE, B200_ERR_BAD_ARG, B200_ERR_WORKSPACE, B200_ERR_CUDA, \
+    B200_ERR_NO_DEVICE = range(6)
+LAYOUT_AWQ, LAYOUT_B200 = 0, 1
+REPACK_AWQ_TO_B200, REPACK_B200_TO_AWQ = 0, 1
+
+# every symbol include/b200_w4a16.h declares
+EXPORTS = (
+    "b200_w4a16_version", "b200_w4a16_strerror", "b200_w4a16_last_cuda_error",
+    "b200_w4a16_repacked_words", "b200_w4a16_workspace_bytes", "b200_w4a16_gemm",
+    "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan",
+)
+
+
+class B200LibraryError(RuntimeError):
+    pass
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile the CUDA library in-tree (``make -C csrc``)."""
+    cmd = ["make", "-C", CSRC, "-j4"] + (["-B"] if force else [])
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        print(res.stdout)
+        print(res.stderr)
+    if res.returncode != 0:
+        raise B200LibraryError("building libb200_w4a16.so failed (see output above)")
+    return LIB_PATH
+
+
+_lib: Optional[ctypes.CDLL] = None
+
+
+def lib() -> ctypes.CDLL:
+    """Load the library once; raise loudly if it is not there."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B200LibraryError(
+            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C vllm-quick_b200/csrc`. This package has no CPU or PyTorch fallback.")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, i32, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+    L.b200_w4a16_version.restype = i32
+    L.b200_w4a16_strerror.restype = ctypes.c_char_p
+    L.b200_w4a16_strerror.argtypes = [i32]
+    L.b200_w4a16_last_cuda_error.restype = i32
+    L.b200_w4a16_repacked_words.restype = sz
+    L.b200_w4a16_repacked_words.argtypes = [i32, i32]
+    L.b200_w4a16_workspace_bytes.restype = sz
+    L.b200_w4a16_workspace_bytes.argtypes = [i32, i32, i32, i32]
+    L.b200_w4a16_gemm.restype = i32
+    L.b200_w4a16_gemm.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, sz, vp]
+    L.b200_w4a16_dequant.restype = i32
+    L.b200_w4a16_dequant.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, vp]
+    L.b200_w4a16_repack.restype = i32
+    L.b200_w4a16_repack.argtypes = [vp, vp, i32, i32, i32, vp]
+    L.b200_w4a16_gemm_plan.restype = i32
+    L.b200_w4a16_gemm_plan.argtypes = [i32, i32, i32, i32, i32] + [ctypes.POINTER(i32)] * 4
+    _lib = L
+    return L
+
+
+def check(status: int, what: str) -> None:
+    """Map a b200_status_t to the exception the reference op would raise
+    (std::invalid_argument -> ValueError, csrc/quantization/awq/gemm_kernels.cu:412-419)."""
+    if status == B200_OK:
+        return
+    msg = lib().b200_w4a16_strerror(status).decode()
+    if status == B200_ERR_BAD_SHAPE:
+        raise ValueError(f"{what}: {msg}")
+    if status == B200_ERR_CUDA:
+        raise RuntimeError(f"{what}: {msg} (cudaError {lib().b200_w4a16_last_cuda_error()})")
+    raise RuntimeError(f"{what}: {msg}")
+
+
+def gemm_plan(M: int, K: int, N: int, G: int = 128, split_k_hint: int = 0) -> dict:
+    tok, split, grid, smem = (ctypes.c_int() for _ in range(4))
+    check(lib().b200_w4a16_gemm_plan(M, K, N, G, split_k_hint, ctypes.byref(tok),
+                                     ctypes.byref(split), ctypes.byref(grid),
+                                     ctypes.byref(smem)), "gemm_plan")
+    return {"tok_tile": tok.value, "split_k": split.value, "grid": grid.value,
+            "smem_bytes": smem.value}

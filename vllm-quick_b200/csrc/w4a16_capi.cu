@@ -1,0 +1,195 @@
+// w4a16_capi.cu -- the C ABI of libb200_w4a16.so (declared in include/b200_w4a16.h).
+// Argument validation mirrors the reference host functions
+// (csrc/quantization/awq/gemm_kernels.cu:332-446); nothing here allocates, synchronises
+// or throws.  There is no CPU path: without an sm_100 device every compute entry point
+// returns B200_ERR_NO_DEVICE.
+#include <stdlib.h>
+
+#include "../../include/b200_w4a16.h"
+#include "w4a16_internal.h"
+
+namespace {
+
+thread_local int g_last_cuda_error = 0;
+
+constexpr size_t kCounterBytes = 4096;  // arrival counters live at the front of the workspace
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct DeviceInfo {
+  int status;    // b200_status_t of the probe
+  int sm_count;
+};
+
+const DeviceInfo& device_info() {
+  static DeviceInfo info = [] {
+    DeviceInfo d{B200_ERR_NO_DEVICE, b200::kMaxCtas};
+    int dev = 0, major = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return d; }
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+      cudaGetLastError();
+      return d;
+    }
+    if (major != 10) return d;
+    d.status = B200_OK;
+    d.sm_count = sms < b200::kMaxCtas ? sms : b200::kMaxCtas;
+    return d;
+  }();
+  return info;
+}
+
+int sm_count_or_default() {
+  // workspace sizing must work before a device is touched: assume one full B200.
+  return b200::kMaxCtas;
+}
+
+inline int cuda_fail(int e) {
+  g_last_cuda_error = e;
+  return B200_ERR_CUDA;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+bool gemm_shape_ok(int M, int K, int N, int G) {
+  if (M < 0 || K <= 0 || N <= 0 || G <= 0) return false;
+  if (N % 64 != 0 || G % 32 != 0 || K % G != 0 || K % b200::kTileK != 0) return false;
+  if (!(G == 32 || G == 64 || G % 128 == 0)) return false;
+  return true;
+}
+
+bool use_pdl() {
+  static const bool on = [] {
+    const char* e = getenv("B200_W4A16_NO_PDL");
+    return !(e && e[0] == '1');
+  }();
+  return on;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_w4a16_version(void) { return 100; }
+
+const char* b200_w4a16_strerror(int status) {
+  switch (status) {
+    case B200_OK: return "ok";
+    case B200_ERR_BAD_SHAPE: return "shape precondition violated";
+    case B200_ERR_BAD_ARG: return "null or misaligned pointer, or unknown layout";
+    case B200_ERR_WORKSPACE: return "workspace missing or too small";
+    case B200_ERR_CUDA: return "CUDA call failed";
+    case B200_ERR_NO_DEVICE: return "no sm_100 device (this library has no fallback path)";
+    default: return "unknown status";
+  }
+}
+
+int b200_w4a16_last_cuda_error(void) { return g_last_cuda_error; }
+
+size_t b200_w4a16_repacked_words(int K, int N) {
+  if (K <= 0 || N <= 0) return 0;
+  return (size_t)((N + b200::kTileN - 1) / b200::kTileN) * (size_t)(K / b200::kTileK) *
+         b200::kTileWords;
+}
+
+size_t b200_w4a16_workspace_bytes(int M, int K, int N, int layout) {
+  if (M <= 0 || K <= 0 || N <= 0) return kCounterBytes;
+  b200::GemmPlan plan;
+  b200::make_gemm_plan(M, K, N, 128, 0, sm_count_or_default(), &plan);
+  size_t bytes = kCounterBytes + align_up(plan.ws_partial_bytes, 256);
+  if (layout == B200_LAYOUT_AWQ) bytes += align_up(b200_w4a16_repacked_words(K, N) * 4, 256);
+  return bytes;
+}
+
+int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int* tok_tile,
+                         int* split_k, int* grid, int* smem_bytes) {
+  if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
+  b200::GemmPlan plan;
+  b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, split_k_hint, sm_count_or_default(), &plan);
+  if (tok_tile) *tok_tile = plan.tok_tile;
+  if (split_k) *split_k = plan.max_split;
+  if (grid) *grid = plan.ctas;
+  if (smem_bytes) *smem_bytes = plan.smem_bytes;
+  return B200_OK;
+}
+
+int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
+                    const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G, int layout,
+                    int split_k_hint, void* workspace, size_t workspace_bytes,
+                    b200_stream_t stream) {
+  if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
+  if (layout != B200_LAYOUT_AWQ && layout != B200_LAYOUT_B200) return B200_ERR_BAD_ARG;
+  if (M == 0) return B200_OK;
+  if (!x || !qweight || !scales || !qzeros || !y) return B200_ERR_BAD_ARG;
+  if (!aligned16(x) || !aligned16(qweight) || !aligned16(scales) || !aligned16(qzeros) ||
+      !aligned16(y))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+
+  b200::GemmPlan plan;
+  b200::make_gemm_plan(M, K, N, G, split_k_hint, sm_count_or_default(), &plan);
+  const size_t part_bytes = align_up(plan.ws_partial_bytes, 256);
+  size_t need = kCounterBytes + part_bytes;
+  if (layout == B200_LAYOUT_AWQ) need += align_up(b200_w4a16_repacked_words(K, N) * 4, 256);
+  if (!workspace || workspace_bytes < need || !aligned16(workspace)) return B200_ERR_WORKSPACE;
+  if (plan.ws_counter_bytes > kCounterBytes && plan.max_split > 1) return B200_ERR_WORKSPACE;
+
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  int* counters = reinterpret_cast<int*>(ws);
+  void* partials = ws + kCounterBytes;
+  const int32_t* qw = qweight;
+  bool pdl = use_pdl();
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (layout == B200_LAYOUT_AWQ) {
+    // Checkpoint-layout weights: interleave into scratch first.  The weight prefetch of the
+    // GEMM must then wait for the repack, so programmatic launch is off for this call.
+    int32_t* scratch = reinterpret_cast<int32_t*>(ws + kCounterBytes + part_bytes);
+    int e = b200::launch_repack(qweight, scratch, K, N, B200_REPACK_AWQ_TO_B200, s);
+    if (e != 0) return cuda_fail(e);
+    qw = scratch;
+    pdl = false;
+  }
+  int e = b200::launch_gemm(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters, pdl, s);
+  if (e != 0) return cuda_fail(e);
+  return B200_OK;
+}
+
+int b200_w4a16_dequant(const int32_t* qweight, const uint16_t* scales, const int32_t* qzeros,
+                       uint16_t* W, int K, int N, int G, int layout, b200_stream_t stream) {
+  if (K < 0 || N < 0 || G <= 0) return B200_ERR_BAD_SHAPE;
+  if (layout == B200_LAYOUT_AWQ) {
+    if (N % 8 != 0 || K % G != 0 || G % 4 != 0) return B200_ERR_BAD_SHAPE;
+  } else if (layout == B200_LAYOUT_B200) {
+    if (N % 64 != 0 || K % G != 0 || K % b200::kTileK != 0 || G % 32 != 0) return B200_ERR_BAD_SHAPE;
+  } else {
+    return B200_ERR_BAD_ARG;
+  }
+  if (K == 0 || N == 0) return B200_OK;
+  if (!qweight || !scales || !qzeros || !W) return B200_ERR_BAD_ARG;
+  if (!aligned16(qweight) || !aligned16(scales) || !aligned16(W) ||
+      (reinterpret_cast<uintptr_t>(qzeros) & 3u))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_dequant(qweight, scales, qzeros, W, K, N, G, layout,
+                               reinterpret_cast<cudaStream_t>(stream));
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+int b200_w4a16_repack(const int32_t* src, int32_t* dst, int K, int N, int direction,
+                      b200_stream_t stream) {
+  if (K < 0 || N < 0 || K % b200::kTileK != 0 || N % 64 != 0) return B200_ERR_BAD_SHAPE;
+  if (direction != B200_REPACK_AWQ_TO_B200 && direction != B200_REPACK_B200_TO_AWQ)
+    return B200_ERR_BAD_ARG;
+  if (K == 0 || N == 0) return B200_OK;
+  if (!src || !dst || src == dst || (reinterpret_cast<uintptr_t>(src) & 3u) ||
+      (reinterpret_cast<uintptr_t>(dst) & 3u))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_repack(src, dst, K, N, direction, reinterpret_cast<cudaStream_t>(stream));
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+}  // extern "C"

@@ -1,0 +1,45 @@
+// w4a16_internal.h -- launcher prototypes shared by the translation units of libb200_w4a16.so.
+// Not part of the public ABI (that is include/b200_w4a16.h).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace b200 {
+
+constexpr int kTileN = 128;        // output channels per weight tile  (tcgen05 M)
+constexpr int kTileK = 128;        // input rows per weight tile       (8 x UMMA_K)
+constexpr int kTileWords = 2048;   // int32 words per packed tile (8 KiB)
+constexpr int kMaxCtas = 148;      // one CTA per SM on B200
+
+// How a GEMM is cut into CTAs (stream-K over the (channel tile, token tile, K block) space).
+struct GemmPlan {
+  int tok_tile;      // tokens per MMA tile (tcgen05 N): 16 / 32 / 64 / 128
+  int n_tiles;       // ceil(N / 128)
+  int m_tiles;       // ceil(M / tok_tile)
+  int k_blocks;      // K / 128
+  int ctas;          // grid size
+  int stages;        // smem pipeline depth
+  int smem_bytes;    // dynamic shared memory per CTA
+  int max_split;     // most CTAs contributing to one output tile
+  size_t ws_partial_bytes;  // fp32 partial-tile scratch
+  size_t ws_counter_bytes;  // per-output-tile arrival counters (must be zero on entry)
+};
+
+int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, GemmPlan* plan);
+
+// y[M,N] = x[M,K] . dequant(W) with W in the B200 layout.  Returns cudaError_t.
+int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
+                const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
+                const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
+                cudaStream_t stream);
+
+int launch_dequant(const int32_t* qweight, const uint16_t* scales, const int32_t* qzeros,
+                   uint16_t* W, int K, int N, int G, int layout, cudaStream_t stream);
+
+int launch_repack(const int32_t* src, int32_t* dst, int K, int N, int direction,
+                  cudaStream_t stream);
+
+}  // namespace b200

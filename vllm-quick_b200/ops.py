@@ -1,0 +1,173 @@
+"""Operator surface of the QUICK / AWQ hot path, same names and argument order as the
+reference's ``vllm._C.ops`` (csrc/pybind.cpp:51-55, csrc/ops.h:68-83):
+
+* ``awq_gemm(in_feats, kernel, scaling_factors, zeros, split_k_iters)``
+* ``awq_dequantize(kernel, scaling_factors, zeros, split_k_iters, thx, thy)``
+* ``quick_gemm(...)`` -- same five arguments, ``kernel`` in the B200 interleave
+* ``quick_repack`` / ``quick_unrepack`` / ``quick_dequantize`` -- layout helpers
+
+PyTorch is used for device memory and streams only; all arithmetic is in
+``libb200_w4a16.so``.  Nothing here falls back to torch math.
+"""
+from __future__ import annotations
+
+from typing import Dict, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import LAYOUT_AWQ, LAYOUT_B200
+
+PACK_FACTOR = 8
+# counters (4 KiB) + fp32 partial tiles of one full wave (148 CTAs x 2 x 128 x 128 x 4 B)
+_BASE_WORKSPACE_BYTES = 4096 + 148 * 2 * 128 * 128 * 4
+
+_workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+def _stream_ptr(device: torch.device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    """Zero-initialised scratch, one per (device, stream); the kernels leave it zeroed."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(),
+           _stream_ptr(device))
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.zeros(max(nbytes, _BASE_WORKSPACE_BYTES), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def _check_cuda(*tensors: torch.Tensor) -> torch.device:
+    dev = tensors[0].device
+    for t in tensors:
+        if not t.is_cuda:
+            raise RuntimeError("b200 w4a16 ops need CUDA tensors: there is no CPU path")
+        if t.device != dev:
+            raise RuntimeError("all tensors must be on the same device")
+        if not t.is_contiguous():
+            raise RuntimeError("tensors must be contiguous")
+    return dev
+
+
+def _gemm(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_factors: torch.Tensor,
+          zeros: torch.Tensor, split_k_iters: int, layout: int) -> torch.Tensor:
+    dev = _check_cuda(in_feats, kernel, scaling_factors, zeros)
+    if in_feats.dtype != torch.float16 or scaling_factors.dtype != torch.float16:
+        raise ValueError("in_feats and scaling_factors must be float16")
+    if kernel.dtype != torch.int32 or zeros.dtype != torch.int32:
+        raise ValueError("kernel and zeros must be int32")
+    if in_feats.dim() != 2:
+        raise ValueError("in_feats must be [num_tokens, in_features]")
+    M, K = in_feats.shape
+    N = scaling_factors.shape[1]
+    if scaling_factors.shape[0] == 0 or K % scaling_factors.shape[0] != 0:
+        raise ValueError("in_features must be a multiple of the number of groups")
+    G = K // scaling_factors.shape[0]
+    if zeros.shape != (K // G, N // PACK_FACTOR):
+        raise ValueError("zeros must be [in_features / group_size, out_features / 8]")
+    L = _lib.lib()
+    if layout == LAYOUT_AWQ:
+        if kernel.shape != (K, N // PACK_FACTOR):
+            raise ValueError("kernel must be [in_features, out_features / 8]")
+    elif kernel.numel() != L.b200_w4a16_repacked_words(K, N):
+        raise ValueError("kernel does not have the B200 layout size for these shapes")
+    out = torch.empty((M, N), dtype=torch.float16, device=dev)
+    with torch.cuda.device(dev):
+        need = L.b200_w4a16_workspace_bytes(M, K, N, layout)
+        ws = _workspace(dev, need)
+        st = L.b200_w4a16_gemm(in_feats.data_ptr(), kernel.data_ptr(), scaling_factors.data_ptr(),
+                               zeros.data_ptr(), out.data_ptr(), M, K, N, G, layout,
+                               int(split_k_iters), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _lib.check(st, "w4a16 gemm")
+    return out
+
+
+def awq_gemm(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_factors: torch.Tensor,
+             zeros: torch.Tensor, split_k_iters: int) -> torch.Tensor:
+    """``in_feats[M,K] @ dequant(kernel[K,N/8], scaling_factors[K/G,N], zeros[K/G,N/8])``.
+
+    Same contract as the reference op (csrc/quantization/awq/gemm_kernels.cu:389-446);
+    ``kernel`` is in the AWQ checkpoint layout and is interleaved on the fly (use
+    ``quick_gemm`` with a pre-interleaved weight on the hot path).
+    """
+    return _gemm(in_feats, kernel, scaling_factors, zeros, split_k_iters, LAYOUT_AWQ)
+
+
+def quick_gemm(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_factors: torch.Tensor,
+               zeros: torch.Tensor, split_k_iters: int) -> torch.Tensor:
+    """Same five arguments as ``awq_gemm`` with ``kernel`` produced by ``quick_repack``."""
+    return _gemm(in_feats, kernel, scaling_factors, zeros, split_k_iters, LAYOUT_B200)
+
+
+def _dequant(kernel, scaling_factors, zeros, layout) -> torch.Tensor:
+    dev = _check_cuda(kernel, scaling_factors, zeros)
+    if kernel.dtype != torch.int32 or zeros.dtype != torch.int32:
+        raise ValueError("kernel and zeros must be int32")
+    if scaling_factors.dtype != torch.float16:
+        raise ValueError("scaling_factors must be float16")
+    N = scaling_factors.shape[1]
+    L = _lib.lib()
+    if layout == LAYOUT_AWQ:
+        K = kernel.shape[0]
+    else:
+        if N == 0 or (kernel.numel() * PACK_FACTOR) % (((N + 127) // 128) * 128) != 0:
+            raise ValueError("kernel does not have the B200 layout size for these shapes")
+        K = kernel.numel() * PACK_FACTOR // (((N + 127) // 128) * 128)
+    if scaling_factors.shape[0] == 0 or K % scaling_factors.shape[0] != 0:
+        raise ValueError("in_features must be a multiple of the number of groups")
+    G = K // scaling_factors.shape[0]  # gemm_kernels.cu:343
+    out = torch.empty((K, N), dtype=scaling_factors.dtype, device=dev)
+    with torch.cuda.device(dev):
+        st = L.b200_w4a16_dequant(kernel.data_ptr(), scaling_factors.data_ptr(), zeros.data_ptr(),
+                                  out.data_ptr(), K, N, G, layout, _stream_ptr(dev))
+    _lib.check(st, "w4a16 dequantize")
+    return out
+
+
+def awq_dequantize(kernel: torch.Tensor, scaling_factors: torch.Tensor, zeros: torch.Tensor,
+                   split_k_iters: int = 0, thx: int = 0, thy: int = 0) -> torch.Tensor:
+    """``W[K,N] = fp16((q - z) * s)``, bit-exact with the reference
+    (csrc/quantization/awq/gemm_kernels.cu:274-381).  The three trailing launch-shape
+    arguments of the reference are accepted and ignored."""
+    return _dequant(kernel, scaling_factors, zeros, LAYOUT_AWQ)
+
+
+def quick_dequantize(kernel: torch.Tensor, scaling_factors: torch.Tensor,
+                     zeros: torch.Tensor) -> torch.Tensor:
+    return _dequant(kernel, scaling_factors, zeros, LAYOUT_B200)
+
+
+def _repack(kernel: torch.Tensor, K: int, N: int, direction: int) -> torch.Tensor:
+    dev = _check_cuda(kernel)
+    if kernel.dtype != torch.int32:
+        raise ValueError("kernel must be int32")
+    L = _lib.lib()
+    words = L.b200_w4a16_repacked_words(K, N)
+    if direction == _lib.REPACK_AWQ_TO_B200:
+        out = torch.empty((K, N // PACK_FACTOR) if words == K * N // PACK_FACTOR else (words,),
+                          dtype=torch.int32, device=dev)
+    else:
+        if kernel.numel() != words:
+            raise ValueError("kernel does not have the B200 layout size for these shapes")
+        out = torch.empty((K, N // PACK_FACTOR), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        st = L.b200_w4a16_repack(kernel.data_ptr(), out.data_ptr(), K, N, direction,
+                                 _stream_ptr(dev))
+    _lib.check(st, "w4a16 repack")
+    return out
+
+
+def quick_repack(kernel: torch.Tensor) -> torch.Tensor:
+    """AWQ ``qweight[K, N/8]`` -> B200 interleave (same number of words when N % 128 == 0)."""
+    if kernel.dim() != 2:
+        raise ValueError("kernel must be [in_features, out_features / 8]")
+    K, NW = kernel.shape
+    return _repack(kernel, K, NW * PACK_FACTOR, _lib.REPACK_AWQ_TO_B200)
+
+
+def quick_unrepack(kernel: torch.Tensor, in_features: int, out_features: int) -> torch.Tensor:
+    """Inverse of ``quick_repack``."""
+    return _repack(kernel, in_features, out_features, _lib.REPACK_B200_TO_AWQ)
