@@ -64,6 +64,7 @@ struct GemmParams {
   long long T;  // total (output tile, K block) work items
   int P;        // CTAs
   int R;        // (scale, zero) rows per K block: max(1, 128 / G)
+  int Gdiv;     // K blocks per group: max(1, G / 128)
 };
 
 __device__ __forceinline__ int owner_of(long long t, int P, long long T) {
@@ -127,57 +128,75 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       const uint64_t pol_w = policy_evict_first();
       const int npre = (int)((t_end - t_begin) < C::kStages ? (t_end - t_begin) : C::kStages);
       // -- phase 1: weight side of the first npre stages (independent of the previous kernel)
-      auto issue_w = [&](long long t, int stage) {
-        const int o = (int)(t / p.KB), kb = (int)(t - (long long)o * p.KB);
-        const int nt = o / p.MT;
-        const int nvalid = min(kTileN, p.N - nt * kTileN);
+      // Tile coordinates advance incrementally: no divisions on the single producer thread.
+      struct Coord { int kb, nt, mt; };
+      auto advance = [&](Coord& c) {
+        if (++c.kb == p.KB) {
+          c.kb = 0;
+          if (++c.mt == p.MT) { c.mt = 0; ++c.nt; }
+        }
+      };
+      Coord cw, cx;
+      {
+        const int o = (int)(t_begin / p.KB);
+        cw.kb = (int)(t_begin - (long long)o * p.KB);
+        cw.nt = o / p.MT;
+        cw.mt = o - cw.nt * p.MT;
+        cx = cw;
+      }
+      const int n_total = (int)(t_end - t_begin);
+      const uint32_t zs_row_bytes_full = kTileN * 2 + kTileN / 2;
+      auto issue_w = [&](const Coord& c, int stage) {
+        const int nvalid = min(kTileN, p.N - c.nt * kTileN);
         const uint32_t sb = stage0 + stage * C::kStageBytes;
         const uint32_t bar = bar_full + 8 * stage;
-        const uint32_t bytes = C::kXBytes + kTileWords * 4 + p.R * (nvalid * 2 + nvalid / 2);
-        mbar_arrive_expect_tx(bar, bytes);
-        bulk_g2s_hint(sb + C::kWOff, p.qw + ((size_t)nt * p.KB + kb) * kTileWords,
+        const uint32_t zs_row = nvalid == kTileN ? zs_row_bytes_full : (uint32_t)(nvalid * 2 + nvalid / 2);
+        mbar_arrive_expect_tx(bar, C::kXBytes + kTileWords * 4 + p.R * zs_row);
+        bulk_g2s_hint(sb + C::kWOff, p.qw + ((size_t)c.nt * p.KB + c.kb) * kTileWords,
                       kTileWords * 4, bar, pol_w);
-        const int g0 = (kb * kTileK) / p.G;
+        const int g0 = p.R > 1 ? c.kb * p.R : (p.Gdiv == 1 ? c.kb : c.kb / p.Gdiv);
         for (int r = 0; r < p.R; ++r) {
-          bulk_g2s(sb + C::kSOff + r * 256, p.scales + (size_t)(g0 + r) * p.N + nt * kTileN,
+          bulk_g2s(sb + C::kSOff + r * 256, p.scales + (size_t)(g0 + r) * p.N + c.nt * kTileN,
                    nvalid * 2, bar);
-          bulk_g2s(sb + C::kZOff + r * 64, p.qz + (size_t)(g0 + r) * (p.N >> 3) + nt * 16,
+          bulk_g2s(sb + C::kZOff + r * 64, p.qz + (size_t)(g0 + r) * (p.N >> 3) + c.nt * 16,
                    nvalid / 2, bar);
         }
       };
-      auto issue_x = [&](long long t, int stage) {
-        const int o = (int)(t / p.KB), kb = (int)(t - (long long)o * p.KB);
-        const int mt = o % p.MT;
+      auto issue_x = [&](const Coord& c, int stage) {
         const uint32_t sb = stage0 + stage * C::kStageBytes;
         const uint32_t bar = bar_full + 8 * stage;
-        tma_load_2d(sb, &tmap_x, kb * kTileK, mt * MTOK, bar);
-        tma_load_2d(sb + MTOK * 128, &tmap_x, kb * kTileK + 64, mt * MTOK, bar);
+        tma_load_2d(sb, &tmap_x, c.kb * kTileK, c.mt * MTOK, bar);
+        tma_load_2d(sb + MTOK * 128, &tmap_x, c.kb * kTileK + 64, c.mt * MTOK, bar);
       };
-      for (int i = 0; i < npre; ++i) issue_w(t_begin + i, i);
+      for (int i = 0; i < npre; ++i) { issue_w(cw, i); advance(cw); }
       asm volatile("griddepcontrol.wait;" ::: "memory");
-      for (int i = 0; i < npre; ++i) issue_x(t_begin + i, i);
+      for (int i = 0; i < npre; ++i) { issue_x(cx, i); advance(cx); }
       // -- phase 2: steady state
-      int it = npre;
-      for (long long t = t_begin + npre; t < t_end; ++t, ++it) {
-        const int stage = it % C::kStages;
-        mbar_wait(bar_empty + 8 * stage, ((it / C::kStages) & 1) ^ 1);
-        issue_w(t, stage);
-        issue_x(t, stage);
+      int stage = npre % C::kStages;
+      uint32_t ephase = npre == C::kStages ? 0u : 1u;  // parity to wait for on empty[stage]
+      for (int it = npre; it < n_total; ++it) {
+        mbar_wait(bar_empty + 8 * stage, ephase);
+        issue_w(cw, stage);
+        issue_x(cw, stage);
+        advance(cw);
+        if (++stage == C::kStages) { stage = 0; ephase ^= 1u; }
       }
     }
   } else if (warp == kMmaWarp) {
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_f16_m128(MTOK);
       int it = 0, seg = 0;
-      long long t = t_begin;
-      while (t < t_end) {
-        const int o = (int)(t / p.KB), kb0 = (int)(t - (long long)o * p.KB);
-        const int n = (int)min((long long)(p.KB - kb0), t_end - t);
+      int kb0 = (int)(t_begin % p.KB);
+      int remaining = (int)(t_end - t_begin);
+      int stage = 0;
+      uint32_t fphase = 0;
+      while (remaining > 0) {
+        const int n = min(p.KB - kb0, remaining);
         mbar_wait(bar_dempty, (seg & 1) ^ 1);  // accumulators drained by the previous epilogue
         tc_fence_after();
         for (int i = 0; i < n; ++i, ++it) {
-          const int stage = it % C::kStages, a = it % kDequantGroups;
-          mbar_wait(bar_full + 8 * stage, (it / C::kStages) & 1);
+          const int a = it % kDequantGroups;
+          mbar_wait(bar_full + 8 * stage, fphase);
           mbar_wait(bar_afull + 8 * a, (it / kDequantGroups) & 1);
           tc_fence_after();
           const uint32_t xb = stage0 + stage * C::kStageBytes;
@@ -189,9 +208,11 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           }
           tc_commit(bar_empty + 8 * stage);
           tc_commit(bar_aempty + 8 * a);
+          if (++stage == C::kStages) { stage = 0; fphase ^= 1u; }
         }
         tc_commit(bar_dfull);
-        t += n;
+        remaining -= n;
+        kb0 = 0;
         ++seg;
       }
     }
@@ -428,6 +449,7 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   prm.T = (long long)plan.n_tiles * plan.m_tiles * plan.k_blocks;
   prm.P = plan.ctas;
   prm.R = G >= kTileK ? 1 : kTileK / G;
+  prm.Gdiv = G >= kTileK ? G / kTileK : 1;
   switch (plan.tok_tile) {
     case 16: return launch_impl<16>(prm, tmap, plan, pdl, stream);
     case 32: return launch_impl<32>(prm, tmap, plan, pdl, stream);
