@@ -86,6 +86,11 @@ const char* b200_w4a16_strerror(int status) {
 
 int b200_w4a16_last_cuda_error(void) { return g_last_cuda_error; }
 
+/* tuning aid, not part of the public ABI: per-CTA pipeline timestamps in B200_TRACE builds */
+void b200_w4a16_debug_set_trace(void* dev_buffer) {
+  b200::set_trace_buffer(static_cast<uint32_t*>(dev_buffer));
+}
+
 size_t b200_w4a16_repacked_words(int K, int N) {
   if (K <= 0 || N <= 0) return 0;
   return (size_t)((N + b200::kTileN - 1) / b200::kTileN) * (size_t)(K / b200::kTileK) *
@@ -105,7 +110,8 @@ int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int* tok_
                          int* split_k, int* grid, int* smem_bytes) {
   if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
   b200::GemmPlan plan;
-  b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, split_k_hint, sm_count_or_default(), &plan);
+  if (b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, split_k_hint, sm_count_or_default(), &plan))
+    return B200_ERR_BAD_SHAPE;
   if (tok_tile) *tok_tile = plan.tok_tile;
   if (split_k) *split_k = plan.max_split;
   if (grid) *grid = plan.ctas;
@@ -128,12 +134,13 @@ int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* s
   if (dev.status != B200_OK) return dev.status;
 
   b200::GemmPlan plan;
-  b200::make_gemm_plan(M, K, N, G, split_k_hint, sm_count_or_default(), &plan);
+  if (b200::make_gemm_plan(M, K, N, G, split_k_hint, sm_count_or_default(), &plan))
+    return B200_ERR_BAD_SHAPE;
   const size_t part_bytes = align_up(plan.ws_partial_bytes, 256);
   size_t need = kCounterBytes + part_bytes;
   if (layout == B200_LAYOUT_AWQ) need += align_up(b200_w4a16_repacked_words(K, N) * 4, 256);
   if (!workspace || workspace_bytes < need || !aligned16(workspace)) return B200_ERR_WORKSPACE;
-  if (plan.ws_counter_bytes > kCounterBytes && plan.max_split > 1) return B200_ERR_WORKSPACE;
+  if (plan.ws_counter_bytes > kCounterBytes) return B200_ERR_WORKSPACE;
 
   uint8_t* ws = static_cast<uint8_t*>(workspace);
   int* counters = reinterpret_cast<int*>(ws);

@@ -10,19 +10,24 @@
 //    dimension is TOKENS (16..128), so a decode batch of 1..16 tokens still fills the MMA.
 //  * weights arrive as contiguous 8 KiB tiles (128 channels x 128 rows, B200 layout) by 1-D
 //    bulk async copy; activations by 2-D TMA with the 128-byte swizzle tcgen05 expects.
-//  * dequant warps read one 16-byte word group per thread (bank-conflict free), expand it in
-//    registers with the reference's exact lop3 / sub / fma sequence, and write the fp16 pairs
-//    straight into TENSOR MEMORY with tcgen05.st: thread = TMEM lane = channel, so the
-//    registers already are the MMA A-operand -- no shared-memory round trip for the
-//    dequantized tile (the reference's :168 store + :198-203 ldmatrix).
-//  * one thread issues tcgen05.mma (A from TMEM, B from shared memory), accumulators in TMEM.
+//  * four dequant warpgroups take tiles round-robin.  A thread reads one 16-byte word group
+//    (bank-conflict free), expands it in registers with the reference's exact lop3 / sub / fma
+//    sequence, and writes the fp16 pairs straight into TENSOR MEMORY with tcgen05.st:
+//    thread = TMEM lane = channel, so the registers already are the MMA A-operand -- no
+//    shared-memory round trip for the dequantized tile (the reference's :168 store +
+//    :198-203 ldmatrix).  A ring of 4-6 operand buffers decouples them from the MMA.
+//  * one thread issues tcgen05.mma (A from TMEM, B from shared memory); two fp32 accumulator
+//    buffers in TMEM let a dedicated epilogue warpgroup drain tile i while tile i+1 runs.
 //  * stream-K: the (channel tile, token tile, K block) space is cut into equal contiguous
-//    ranges, one per SM; an output tile touched by several CTAs is reduced in fixed CTA order
-//    by whichever CTA arrives last (fp32 partials through L2, no second kernel, deterministic).
+//    ranges, one per SM.  A CTA does its two partial output tiles FIRST, so the cross-CTA
+//    reduction (fp32 partials through L2, fixed CTA order, done by whichever CTA arrives
+//    last -- no second kernel, deterministic) overlaps the rest of the weight stream.
 //  * programmatic dependent launch: the weight pipeline is filled BEFORE griddepcontrol.wait
 //    (weights never depend on the previous kernel), so launch ramp overlaps the previous op.
 #include "w4a16_common.cuh"
 #include "w4a16_internal.h"
+
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -31,25 +36,33 @@ namespace {
 constexpr int kProducerWarp = 0;
 constexpr int kMmaWarp = 1;
 constexpr int kAllocWarp = 2;
-constexpr int kFirstDequantWarp = 4;
-constexpr int kDequantGroups = 2;                       // warpgroups alternating tiles
-constexpr int kDequantThreads = kDequantGroups * 128;
-constexpr int kThreads = kFirstDequantWarp * 32 + kDequantThreads;  // 384
+constexpr int kFirstEpiWarp = 4;                        // warps 4..7 (warp % 4 == lane quarter)
+constexpr int kEpiThreads = 128;
+constexpr int kFirstDequantWarp = 8;
+constexpr int kGroups = 4;                              // dequant warpgroups, tiles round-robin
+constexpr int kDequantThreads = kGroups * 128;
+constexpr int kThreads = kFirstDequantWarp * 32 + kDequantThreads;  // 768
 constexpr int kScaleRowsMax = 4;                        // G = 32 -> four (scale, zero) rows / tile
 constexpr int kTmemACols = 64;                          // one dequantized tile: 128 fp16 per lane
-constexpr int kTmemDCol = kDequantGroups * kTmemACols;  // accumulators start here
-constexpr int kTmemCols = 256;
+constexpr int kTmemCols = 512;
+constexpr int kMaxSmem = 227 * 1024;
 
 template <int MTOK>
 struct Cfg {
+  static constexpr int kABufs = MTOK <= 64 ? 6 : 4;    // dequantized-operand ring in TMEM
+  static constexpr int kDCol = kABufs * kTmemACols;    // accumulators start here
+  static constexpr int kDStride = MTOK <= 64 ? 64 : 128;  // two accumulator buffers
   static constexpr int kXBytes = MTOK * 256;           // two swizzle atoms of [MTOK x 64] fp16
   static constexpr int kWOff = kXBytes;
   static constexpr int kSOff = kWOff + kTileWords * 4;
   static constexpr int kZOff = kSOff + kScaleRowsMax * 256;
   static constexpr int kStageBytes = ((kZOff + kScaleRowsMax * 64 + 1023) / 1024) * 1024;
-  static constexpr int kStages = MTOK <= 16 ? 8 : MTOK <= 32 ? 6 : 4;
   static constexpr int kBarBytes = 1024;
+  static constexpr int kStagesFit = (kMaxSmem - kBarBytes - 1024) / kStageBytes;
+  static constexpr int kStages = kStagesFit > 16 ? 16 : kStagesFit;
   static constexpr int kSmemBytes = kBarBytes + kStages * kStageBytes + 1024;  // + align slack
+  static_assert(kStages > kGroups, "stage ring must be deeper than the dequant group count");
+  static_assert(kDCol + 2 * kDStride <= kTmemCols, "TMEM budget");
 };
 
 struct GemmParams {
@@ -61,15 +74,84 @@ struct GemmParams {
   int* counters;
   int M, K, N, G;
   int KB, NT, MT;
-  long long T;  // total (output tile, K block) work items
+  int T;        // total (output tile, K block) work items
   int P;        // CTAs
   int R;        // (scale, zero) rows per K block: max(1, 128 / G)
   int Gdiv;     // K blocks per group: max(1, G / 128)
+  int flags;    // bit 0: no L2 evict-first hint on the weight stream
+  uint32_t* trace;  // B200_TRACE builds only: per-CTA event timestamps
 };
 
-__device__ __forceinline__ int owner_of(long long t, int P, long long T) {
-  return (int)(((t + 1) * P - 1) / T);
+#ifdef B200_TRACE
+// event types: 0 producer issues tile, 1 dequant sees tile landed, 2 dequant starts (operand
+// buffer free), 3 dequant done, 4 MMA starts tile, 5 MMA issued, 6 epilogue seg (2*idx: dfull
+// seen, 2*idx+1: segment finished incl. fix-up), 7 misc (0 setup done, 1 exit)
+#define TR(type, i)                                                                          \
+  do {                                                                                       \
+    if (p.trace && (i) < 64) p.trace[((size_t)blockIdx.x * 8 + (type)) * 64 + (i)] = (uint32_t)clock64(); \
+  } while (0)
+#else
+#define TR(type, i) do { } while (0)
+#endif
+
+__device__ __forceinline__ int range_begin(int p, int T, int P) {
+  return (int)((long long)p * T / P);
 }
+__device__ __forceinline__ int owner_of(int t, int P, int T) {
+  return (int)((((long long)t + 1) * P - 1) / T);
+}
+
+// The order in which a CTA walks its contiguous work range [t_begin, t_end): the segment
+// that finishes someone else's output tile first, then the segment that starts a tile someone
+// else finishes, then its whole tiles.  Every warp role derives the same sequence.
+struct Walk {
+  int t_begin, t_end, KB;
+  int first_end;   // end of the first segment
+  int tail_start;  // start of a distinct, partial last segment, or -1
+  int nseg;
+  __device__ __forceinline__ Walk(int tb, int te, int kb) : t_begin(tb), t_end(te), KB(kb) {
+    if (te <= tb) { first_end = tb; tail_start = -1; nseg = 0; return; }
+    const int fe = (tb / kb + 1) * kb;
+    first_end = fe < te ? fe : te;
+    const int ls = ((te - 1) / kb) * kb;
+    tail_start = (ls >= first_end && te - ls < kb) ? ls : -1;
+    const int mid_end = tail_start >= 0 ? tail_start : te;
+    nseg = 1 + (tail_start >= 0 ? 1 : 0) + (mid_end - first_end) / kb;
+  }
+  __device__ __forceinline__ void seg(int idx, int& t0, int& n) const {
+    if (idx == 0) { t0 = t_begin; n = first_end - t_begin; return; }
+    if (tail_start >= 0) {
+      if (idx == 1) { t0 = tail_start; n = t_end - tail_start; return; }
+      --idx;
+    }
+    t0 = first_end + (idx - 1) * KB;
+    n = KB;
+  }
+};
+
+// Tile-by-tile cursor over a Walk (used by the single producer thread).
+struct TileCursor {
+  const Walk& w;
+  int MT;
+  int idx, left;
+  int kb, nt, mt;
+  __device__ __forceinline__ TileCursor(const Walk& walk, int mt_count)
+      : w(walk), MT(mt_count), idx(-1), left(0), kb(0), nt(0), mt(0) { load_next(); }
+  __device__ __forceinline__ void load_next() {
+    if (++idx >= w.nseg) return;
+    int t0, n;
+    w.seg(idx, t0, n);
+    const int o = t0 / w.KB;
+    kb = t0 - o * w.KB;
+    nt = o / MT;
+    mt = o - nt * MT;
+    left = n;
+  }
+  __device__ __forceinline__ void next() {
+    ++kb;
+    if (--left == 0) load_next();
+  }
+};
 
 template <int MTOK>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -80,14 +162,15 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
 
   // barrier block
-  const uint32_t bar_full = smem_base;                       // [kStages]
-  const uint32_t bar_empty = smem_base + 8 * C::kStages;     // [kStages]
-  const uint32_t bar_afull = smem_base + 16 * C::kStages;    // [kDequantGroups]
-  const uint32_t bar_aempty = bar_afull + 8 * kDequantGroups;
-  const uint32_t bar_dfull = bar_aempty + 8 * kDequantGroups;
-  const uint32_t bar_dempty = bar_dfull + 8;
-  const uint32_t tmem_slot = bar_dempty + 8;
+  const uint32_t bar_full = smem_base;                          // [kStages] TMA landed
+  const uint32_t bar_empty = bar_full + 8 * C::kStages;         // [kStages] MMA done with stage
+  const uint32_t bar_afull = bar_empty + 8 * C::kStages;        // [kABufs]  operand dequantized
+  const uint32_t bar_aempty = bar_afull + 8 * C::kABufs;        // [kABufs]  MMA done with operand
+  const uint32_t bar_dfull = bar_aempty + 8 * C::kABufs;        // [2] accumulator complete
+  const uint32_t bar_dempty = bar_dfull + 16;                   // [2] accumulator drained
+  const uint32_t tmem_slot = bar_dempty + 16;
   const uint32_t flag_slot = tmem_slot + 4;
+  static_assert(16 * C::kStages + 16 * C::kABufs + 40 <= C::kBarBytes, "barrier block");
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(
       smem_gen + (tmem_slot - smem_base));
   volatile uint32_t* flag_gen = reinterpret_cast<volatile uint32_t*>(
@@ -102,12 +185,14 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       mbar_init(bar_full + 8 * s, 1);
       mbar_init(bar_empty + 8 * s, 1);
     }
-    for (int g = 0; g < kDequantGroups; ++g) {
-      mbar_init(bar_afull + 8 * g, 128);
-      mbar_init(bar_aempty + 8 * g, 1);
+    for (int b = 0; b < C::kABufs; ++b) {
+      mbar_init(bar_afull + 8 * b, 128);
+      mbar_init(bar_aempty + 8 * b, 1);
     }
-    mbar_init(bar_dfull, 1);
-    mbar_init(bar_dempty, kDequantThreads);
+    for (int d = 0; d < 2; ++d) {
+      mbar_init(bar_dfull + 8 * d, 1);
+      mbar_init(bar_dempty + 8 * d, kEpiThreads);
+    }
     fence_barrier_init();
   } else if (warp == kAllocWarp) {
     tmem_alloc<kTmemCols>(tmem_slot);
@@ -117,40 +202,26 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_gen;
 
-  // This CTA's contiguous slice of the work space.
-  const long long t_begin = (long long)blockIdx.x * p.T / p.P;
-  const long long t_end = (long long)(blockIdx.x + 1) * p.T / p.P;
+  // This CTA's contiguous slice of the work space, and the order it is walked in.
+  const int t_begin = range_begin(blockIdx.x, p.T, p.P);
+  const int t_end = range_begin(blockIdx.x + 1, p.T, p.P);
+  const Walk walk(t_begin, t_end, p.KB);
+  const int n_total = t_end - t_begin;
+  if (threadIdx.x == 0) TR(7, 0);
 
   if (warp == kProducerWarp) {
-    if (lane == 0) {
-      // Let the next kernel in the stream start its own weight prefetch right away.
+    if (elect_one()) {
+      // Let the next kernel in the stream start its own weight prefetch as soon as an SM frees.
       asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-      const uint64_t pol_w = policy_evict_first();
-      const int npre = (int)((t_end - t_begin) < C::kStages ? (t_end - t_begin) : C::kStages);
-      // -- phase 1: weight side of the first npre stages (independent of the previous kernel)
-      // Tile coordinates advance incrementally: no divisions on the single producer thread.
-      struct Coord { int kb, nt, mt; };
-      auto advance = [&](Coord& c) {
-        if (++c.kb == p.KB) {
-          c.kb = 0;
-          if (++c.mt == p.MT) { c.mt = 0; ++c.nt; }
-        }
-      };
-      Coord cw, cx;
-      {
-        const int o = (int)(t_begin / p.KB);
-        cw.kb = (int)(t_begin - (long long)o * p.KB);
-        cw.nt = o / p.MT;
-        cw.mt = o - cw.nt * p.MT;
-        cx = cw;
-      }
-      const int n_total = (int)(t_end - t_begin);
+      const uint64_t pol_w = (p.flags & 1) ? policy_evict_normal() : policy_evict_first();
+      const int npre = n_total < C::kStages ? n_total : C::kStages;
       const uint32_t zs_row_bytes_full = kTileN * 2 + kTileN / 2;
-      auto issue_w = [&](const Coord& c, int stage) {
+      auto issue_w = [&](const TileCursor& c, int stage) {
         const int nvalid = min(kTileN, p.N - c.nt * kTileN);
         const uint32_t sb = stage0 + stage * C::kStageBytes;
         const uint32_t bar = bar_full + 8 * stage;
-        const uint32_t zs_row = nvalid == kTileN ? zs_row_bytes_full : (uint32_t)(nvalid * 2 + nvalid / 2);
+        const uint32_t zs_row =
+            nvalid == kTileN ? zs_row_bytes_full : (uint32_t)(nvalid * 2 + nvalid / 2);
         mbar_arrive_expect_tx(bar, C::kXBytes + kTileWords * 4 + p.R * zs_row);
         bulk_g2s_hint(sb + C::kWOff, p.qw + ((size_t)c.nt * p.KB + c.kb) * kTileWords,
                       kTileWords * 4, bar, pol_w);
@@ -162,178 +233,204 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
                    nvalid / 2, bar);
         }
       };
-      auto issue_x = [&](const Coord& c, int stage) {
+      auto issue_x = [&](const TileCursor& c, int stage) {
         const uint32_t sb = stage0 + stage * C::kStageBytes;
         const uint32_t bar = bar_full + 8 * stage;
         tma_load_2d(sb, &tmap_x, c.kb * kTileK, c.mt * MTOK, bar);
         tma_load_2d(sb + MTOK * 128, &tmap_x, c.kb * kTileK + 64, c.mt * MTOK, bar);
       };
-      for (int i = 0; i < npre; ++i) { issue_w(cw, i); advance(cw); }
+      // -- phase 1: weight side of the first npre stages (independent of the previous kernel)
+      TileCursor cw(walk, p.MT), cx(walk, p.MT);
+      for (int i = 0; i < npre; ++i) { TR(0, i); issue_w(cw, i); cw.next(); }
       asm volatile("griddepcontrol.wait;" ::: "memory");
-      for (int i = 0; i < npre; ++i) { issue_x(cx, i); advance(cx); }
+      for (int i = 0; i < npre; ++i) { issue_x(cx, i); cx.next(); }
       // -- phase 2: steady state
       int stage = npre % C::kStages;
-      uint32_t ephase = npre == C::kStages ? 0u : 1u;  // parity to wait for on empty[stage]
+      uint32_t ephase = 0;  // first refill of a stage waits for phase 0 of its empty barrier
       for (int it = npre; it < n_total; ++it) {
         mbar_wait(bar_empty + 8 * stage, ephase);
+        TR(0, it);
         issue_w(cw, stage);
         issue_x(cw, stage);
-        advance(cw);
+        cw.next();
         if (++stage == C::kStages) { stage = 0; ephase ^= 1u; }
       }
     }
   } else if (warp == kMmaWarp) {
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_f16_m128(MTOK);
-      int it = 0, seg = 0;
-      int kb0 = (int)(t_begin % p.KB);
-      int remaining = (int)(t_end - t_begin);
-      int stage = 0;
-      uint32_t fphase = 0;
-      while (remaining > 0) {
-        const int n = min(p.KB - kb0, remaining);
-        mbar_wait(bar_dempty, (seg & 1) ^ 1);  // accumulators drained by the previous epilogue
+      int stage = 0, buf = 0, itg = 0;
+      uint32_t fphase = 0, aphase = 0;
+      for (int idx = 0; idx < walk.nseg; ++idx) {
+        int t0, n;
+        walk.seg(idx, t0, n);
+        const int d = idx & 1;
+        mbar_wait(bar_dempty + 8 * d, ((idx >> 1) & 1) ^ 1);  // drained by the epilogue warps
         tc_fence_after();
-        for (int i = 0; i < n; ++i, ++it) {
-          const int a = it % kDequantGroups;
+        const uint32_t dcol = tmem + C::kDCol + d * C::kDStride;
+        for (int i = 0; i < n; ++i) {
           mbar_wait(bar_full + 8 * stage, fphase);
-          mbar_wait(bar_afull + 8 * a, (it / kDequantGroups) & 1);
+          mbar_wait(bar_afull + 8 * buf, aphase);
           tc_fence_after();
+          TR(4, itg);
           const uint32_t xb = stage0 + stage * C::kStageBytes;
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) {
             const uint64_t bdesc = make_desc_k_sw128(xb + (kk >> 2) * (MTOK * 128) + (kk & 3) * 32);
-            tc_mma_ts(tmem + kTmemDCol, tmem + a * kTmemACols + kk * 8, bdesc, idesc,
-                      (i | kk) != 0);
+            tc_mma_ts(dcol, tmem + buf * kTmemACols + kk * 8, bdesc, idesc, (i | kk) != 0);
           }
           tc_commit(bar_empty + 8 * stage);
-          tc_commit(bar_aempty + 8 * a);
+          tc_commit(bar_aempty + 8 * buf);
+          TR(5, itg);
+          ++itg;
           if (++stage == C::kStages) { stage = 0; fphase ^= 1u; }
+          if (++buf == C::kABufs) { buf = 0; aphase ^= 1u; }
         }
-        tc_commit(bar_dfull);
-        remaining -= n;
-        kb0 = 0;
-        ++seg;
+        tc_commit(bar_dfull + 8 * d);
       }
     }
   } else if (warp >= kFirstDequantWarp) {
+    // ---- dequant warpgroups: tile it -> group it % 4, stage it % kStages, operand it % kABufs
     const int wi = warp - kFirstDequantWarp;
     const int grp = wi >> 2, q = wi & 3;
     const int c = q * 32 + lane;                              // channel inside the tile
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int zsh = 4 * awq_nibble(c & 7);
-    asm volatile("griddepcontrol.wait;" ::: "memory");        // y / workspace may alias earlier work
-    int it = 0, seg = 0;
-    long long t = t_begin;
-    while (t < t_end) {
-      const int o = (int)(t / p.KB), kb0 = (int)(t - (long long)o * p.KB);
-      const int n = (int)min((long long)(p.KB - kb0), t_end - t);
-      const int nt = o / p.MT, mt = o % p.MT;
-      // ---- dequantize this group's tiles of the segment into tensor memory
-      for (int i = 0; i < n; ++i, ++it) {
-        if ((it % kDequantGroups) != grp) continue;
-        const int stage = it % C::kStages;
-        const uint8_t* sb = smem_gen + C::kBarBytes + stage * C::kStageBytes;
-        mbar_wait(bar_full + 8 * stage, (it / C::kStages) & 1);
-        uint4 wv[4];
+    int stage = grp % C::kStages, buf = grp % C::kABufs;
+    uint32_t fphase = 0, aphase = (grp / C::kABufs) & 1;
+    for (int it = grp; it < n_total; it += kGroups) {
+      const uint8_t* sb = smem_gen + C::kBarBytes + stage * C::kStageBytes;
+      mbar_wait(bar_full + 8 * stage, fphase);
+      if ((threadIdx.x & 127) == 0) TR(1, it);
+      uint4 wv[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          wv[j] = *reinterpret_cast<const uint4*>(sb + C::kWOff + j * 2048 + c * 16);
-        const uint16_t* sS = reinterpret_cast<const uint16_t*>(sb + C::kSOff);
-        const uint32_t* sZ = reinterpret_cast<const uint32_t*>(sb + C::kZOff);
-        mbar_wait(bar_aempty + 8 * grp, ((it / kDequantGroups) & 1) ^ 1);
-        tc_fence_after();
-        uint32_t zlo = 0, zhi = 0, s2 = 0;
-        int rprev = -1;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int r = (p.R == 1) ? 0 : (j * 32) / p.G;
-          if (r != rprev) {
-            make_zs1((sZ[r * 16 + (c >> 3)] >> zsh) & 0xFu, sS[r * 128 + c], zlo, zhi, s2);
-            rprev = r;
-          }
-          uint32_t v[16];
-          dequant_word_zs1(wv[j].x, zlo, zhi, s2, v[0], v[1], v[2], v[3]);
-          dequant_word_zs1(wv[j].y, zlo, zhi, s2, v[4], v[5], v[6], v[7]);
-          dequant_word_zs1(wv[j].z, zlo, zhi, s2, v[8], v[9], v[10], v[11]);
-          dequant_word_zs1(wv[j].w, zlo, zhi, s2, v[12], v[13], v[14], v[15]);
-          tmem_st_x16(tmem + lane_base + grp * kTmemACols + j * 16, v);
-        }
-        tc_wait_st();
-        tc_fence_before();
-        mbar_arrive(bar_afull + 8 * grp);
-      }
-      // ---- epilogue of the segment: this group owns half of the token columns
-      mbar_wait(bar_dfull, seg & 1);
+      for (int j = 0; j < 4; ++j)
+        wv[j] = *reinterpret_cast<const uint4*>(sb + C::kWOff + j * 2048 + c * 16);
+      const uint16_t* sS = reinterpret_cast<const uint16_t*>(sb + C::kSOff);
+      const uint32_t* sZ = reinterpret_cast<const uint32_t*>(sb + C::kZOff);
+      uint32_t zlo = 0, zhi = 0, s2 = 0;
+      make_zs1((sZ[c >> 3] >> zsh) & 0xFu, sS[c], zlo, zhi, s2);
+      mbar_wait(bar_aempty + 8 * buf, aphase ^ 1u);
       tc_fence_after();
-      const bool whole = (kb0 == 0 && n == p.KB);
+      if ((threadIdx.x & 127) == 0) TR(2, it);
+      const uint32_t abase = tmem + lane_base + buf * kTmemACols;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (p.R > 1) {
+          const int r = (j * 32) / p.G;
+          if (j == 0 || r != ((j - 1) * 32) / p.G)
+            make_zs1((sZ[r * 16 + (c >> 3)] >> zsh) & 0xFu, sS[r * 128 + c], zlo, zhi, s2);
+        }
+        uint32_t v[16];
+        dequant_word_zs1(wv[j].x, zlo, zhi, s2, v[0], v[1], v[2], v[3]);
+        dequant_word_zs1(wv[j].y, zlo, zhi, s2, v[4], v[5], v[6], v[7]);
+        dequant_word_zs1(wv[j].z, zlo, zhi, s2, v[8], v[9], v[10], v[11]);
+        dequant_word_zs1(wv[j].w, zlo, zhi, s2, v[12], v[13], v[14], v[15]);
+        tmem_st_x16(abase + j * 16, v);
+      }
+      tc_wait_st();
+      tc_fence_before();
+      mbar_arrive(bar_afull + 8 * buf);
+      if ((threadIdx.x & 127) == 0) TR(3, it);
+      stage += kGroups;
+      if (stage >= C::kStages) { stage -= C::kStages; fphase ^= 1u; }
+      buf += kGroups;
+      if (buf >= C::kABufs) { buf -= C::kABufs; aphase ^= 1u; }
+    }
+  } else if (warp >= kFirstEpiWarp) {
+    // ---- epilogue warpgroup: drains accumulators, writes y or fp32 partials, stream-K fix-up
+    const int q = warp - kFirstEpiWarp;
+    const int c = q * 32 + lane;                              // channel inside the tile
+    const int et = threadIdx.x - kFirstEpiWarp * 32;          // 0..127
+    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    asm volatile("griddepcontrol.wait;" ::: "memory");        // y / workspace may alias earlier work
+    for (int idx = 0; idx < walk.nseg; ++idx) {
+      int t0, n;
+      walk.seg(idx, t0, n);
+      const int o = t0 / p.KB;
+      const int nt = o / p.MT, mt = o - nt * p.MT;
+      const int d = idx & 1;
+      const bool whole = (n == p.KB);
       const int n_glob = nt * kTileN + c;
-      constexpr int kColsPerGroup = MTOK / kDequantGroups;
-      const int col0 = grp * kColsPerGroup;
-      float* part = p.partials +
-                    ((size_t)blockIdx.x * 2 + (t == t_begin ? 0 : 1)) * (size_t)(MTOK * kTileN);
+      const int m0 = mt * MTOK;
+      const uint32_t dbase = tmem + lane_base + C::kDCol + d * C::kDStride;
+      float* part = p.partials + ((size_t)blockIdx.x * 2 + (idx == 0 ? 0 : 1)) * (size_t)(MTOK * kTileN);
+      mbar_wait(bar_dfull + 8 * d, (idx >> 1) & 1);
+      tc_fence_after();
+      if (et == 0) TR(6, 2 * idx);
 #pragma unroll 1
-      for (int cc = 0; cc < kColsPerGroup; cc += 8) {
-        uint32_t v[8];
-        tmem_ld_x8(tmem + lane_base + kTmemDCol + col0 + cc, v);
+      for (int cc = 0; cc < MTOK; cc += 16) {
+        uint32_t v[16];
+        tmem_ld_x16(dbase + cc, v);
         tc_wait_ld();
         if (whole) {
           if (n_glob < p.N) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const int m = mt * MTOK + col0 + cc + e;
+            for (int e = 0; e < 16; ++e) {
+              const int m = m0 + cc + e;
               if (m < p.M)
-                p.y[(size_t)m * p.N + n_glob] = __half_as_ushort(__float2half_rn(__uint_as_float(v[e])));
+                p.y[(size_t)m * p.N + n_glob] =
+                    __half_as_ushort(__float2half_rn(__uint_as_float(v[e])));
             }
           }
         } else {
 #pragma unroll
-          for (int e = 0; e < 8; ++e) part[(col0 + cc + e) * kTileN + c] = __uint_as_float(v[e]);
+          for (int e = 0; e < 16; ++e) __stcg(part + (cc + e) * kTileN + c, __uint_as_float(v[e]));
         }
       }
       tc_fence_before();
-      mbar_arrive(bar_dempty);
+      mbar_arrive(bar_dempty + 8 * d);
       if (!whole) {
         // stream-K fix-up: the last CTA to arrive sums all contributors in CTA order.
-        const long long o_lo = (long long)o * p.KB;
+        const int o_lo = o * p.KB;
         const int p_first = owner_of(o_lo, p.P, p.T);
         const int p_last = owner_of(o_lo + p.KB - 1, p.P, p.T);
-        __threadfence();
-        named_bar_sync(1, kDequantThreads);
-        if (wi == 0 && lane == 0) {
-          const int old = atomicAdd(p.counters + o, 1);
+        named_bar_sync(1, kEpiThreads);                       // every partial store is issued
+        if (et == 0) {
+          // release our partials / acquire everyone else's (cumulative through the barrier)
+          const int old = atom_add_acq_rel_gpu(p.counters + p_first, 1);
           *flag_gen = (old == p_last - p_first) ? 1u : 0u;
         }
-        named_bar_sync(1, kDequantThreads);
+        named_bar_sync(1, kEpiThreads);
         const bool last = (*flag_gen != 0u);
-        named_bar_sync(1, kDequantThreads);  // flag consumed before anyone can overwrite it
+        named_bar_sync(1, kEpiThreads);  // flag consumed before anyone can overwrite it
         if (last) {
-          __threadfence();
-          if (wi == 0 && lane == 0) p.counters[o] = 0;
+          if (et == 0) p.counters[p_first] = 0;               // leave the workspace zeroed
           if (n_glob < p.N) {
-            for (int cc = 0; cc < kColsPerGroup; ++cc) {
-              const int col = col0 + cc;
-              const int m = mt * MTOK + col;
-              if (m >= p.M) break;
-              float acc = 0.f;
+#pragma unroll 1
+            for (int cc = 0; cc < MTOK; cc += 16) {
+              float acc[16];
+#pragma unroll
+              for (int e = 0; e < 16; ++e) acc[e] = 0.f;
+#pragma unroll 1
               for (int pc = p_first; pc <= p_last; ++pc) {
-                const long long pc_begin = (long long)pc * p.T / p.P;
+                const int pc_begin = range_begin(pc, p.T, p.P);
                 const float* src = p.partials +
-                                   ((size_t)pc * 2 + (pc_begin >= o_lo ? 0 : 1)) * (size_t)(MTOK * kTileN);
-                acc += __ldcg(src + col * kTileN + c);
+                                   ((size_t)pc * 2 + (pc_begin >= o_lo ? 0 : 1)) * (size_t)(MTOK * kTileN) +
+                                   cc * kTileN + c;
+                float f[16];
+#pragma unroll
+                for (int e = 0; e < 16; ++e) f[e] = __ldcg(src + e * kTileN);
+#pragma unroll
+                for (int e = 0; e < 16; ++e) acc[e] += f[e];
               }
-              p.y[(size_t)m * p.N + n_glob] = __half_as_ushort(__float2half_rn(acc));
+#pragma unroll
+              for (int e = 0; e < 16; ++e) {
+                const int m = m0 + cc + e;
+                if (m < p.M)
+                  p.y[(size_t)m * p.N + n_glob] = __half_as_ushort(__float2half_rn(acc[e]));
+              }
             }
           }
         }
       }
-      t += n;
-      ++seg;
+      if (et == 0) TR(6, 2 * idx + 1);
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) TR(7, 1);
   if (warp == kAllocWarp) {
     tc_fence_after();
     tmem_dealloc<kTmemCols>(tmem);
@@ -384,6 +481,16 @@ int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& 
   return (int)cudaLaunchKernelEx(&cfg, w4a16_gemm_kernel<MTOK>, prm, tmap);
 }
 
+int gemm_flags() {
+  static const int f = [] {
+    const char* e = getenv("B200_W4A16_FLAGS");
+    return e ? atoi(e) : 0;
+  }();
+  return f;
+}
+
+uint32_t* g_trace = nullptr;
+
 template <int MTOK>
 void fill_plan(GemmPlan* plan) {
   plan->stages = Cfg<MTOK>::kStages;
@@ -391,6 +498,8 @@ void fill_plan(GemmPlan* plan) {
 }
 
 }  // namespace
+
+void set_trace_buffer(uint32_t* dev) { g_trace = dev; }
 
 int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, GemmPlan* plan) {
   (void)G;
@@ -402,15 +511,18 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
   plan->k_blocks = K / kTileK;
   const long long outs = (long long)plan->n_tiles * plan->m_tiles;
   const long long T = outs * plan->k_blocks;
+  if (T >= (1LL << 31)) return 1;
   if (sm_count <= 0) sm_count = kMaxCtas;
-  // Few output tiles: stream-K over one wave of SMs.  Many: one CTA per output tile.
-  long long ctas = outs >= 2LL * sm_count ? outs : (T < sm_count ? T : sm_count);
+  // Persistent stream-K: one CTA per SM, equal contiguous ranges of (output tile, K block).
+  long long ctas = T < sm_count ? T : sm_count;
   if (ctas < 1) ctas = 1;
   plan->ctas = (int)ctas;
-  const long long per = (T + ctas - 1) / ctas;
-  plan->max_split = (ctas == outs) ? 1 : (int)((plan->k_blocks + per - 1) / per + 1);
-  plan->ws_partial_bytes = (ctas == outs) ? 0 : (size_t)ctas * 2 * tok * kTileN * sizeof(float);
-  plan->ws_counter_bytes = (size_t)outs * sizeof(int);
+  const long long per = T / ctas;  // shortest range
+  plan->max_split = (plan->k_blocks == 0 || (T % ctas == 0 && per % plan->k_blocks == 0))
+                        ? 1
+                        : (int)((plan->k_blocks + per - 1) / (per > 0 ? per : 1) + 1);
+  plan->ws_partial_bytes = (size_t)ctas * 2 * tok * kTileN * sizeof(float);
+  plan->ws_counter_bytes = (size_t)ctas * sizeof(int);
   switch (tok) {
     case 16: fill_plan<16>(plan); break;
     case 32: fill_plan<32>(plan); break;
@@ -446,10 +558,12 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   prm.counters = ws_counters;
   prm.M = M; prm.K = K; prm.N = N; prm.G = G;
   prm.KB = plan.k_blocks; prm.NT = plan.n_tiles; prm.MT = plan.m_tiles;
-  prm.T = (long long)plan.n_tiles * plan.m_tiles * plan.k_blocks;
+  prm.T = plan.n_tiles * plan.m_tiles * plan.k_blocks;
   prm.P = plan.ctas;
   prm.R = G >= kTileK ? 1 : kTileK / G;
   prm.Gdiv = G >= kTileK ? G / kTileK : 1;
+  prm.flags = gemm_flags();
+  prm.trace = g_trace;
   switch (plan.tok_tile) {
     case 16: return launch_impl<16>(prm, tmap, plan, pdl, stream);
     case 32: return launch_impl<32>(prm, tmap, plan, pdl, stream);

@@ -36,6 +36,9 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
                 const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
                 cudaStream_t stream);
 
+// B200_TRACE builds: device buffer of 148 x 8 x 64 uint32 timestamps (nullptr = off).
+void set_trace_buffer(uint32_t* dev);
+
 int launch_dequant(const int32_t* qweight, const uint16_t* scales, const int32_t* qzeros,
                    uint16_t* W, int K, int N, int G, int layout, cudaStream_t stream);
 
