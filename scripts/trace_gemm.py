@@ -23,7 +23,7 @@ def main():
     ap.add_argument("--k", type=int, default=4096)
     ap.add_argument("--n", type=int, default=22016)
     ap.add_argument("--ctas", default="0,73,147")
-    ap.add_argument("--warm", type=int, default=2)
+    ap.add_argument("--warm", type=int, default=4)
     args = ap.parse_args()
     M, K, N, G = args.m, args.k, args.n, 128
     dev = torch.device("cuda", 0)
@@ -38,17 +38,34 @@ def main():
     L = pkg._lib.lib()
     L.b200_w4a16_debug_set_trace.argtypes = [ctypes.c_void_p]
     L.b200_w4a16_debug_set_trace.restype = None
-    trace = torch.zeros((148, 8, 64), dtype=torch.int32, device=dev)
-    for (qw, s, qz) in sets[:-1]:
+    nl = len(sets)
+    traces = torch.zeros((nl, 148, 8, 64), dtype=torch.int32, device=dev)
+    for (qw, s, qz) in sets[:2]:
         pkg.ops.quick_gemm(x, qw, s, qz, 8)
     torch.cuda.synchronize()
     # flush L2
     junk = torch.empty(512 << 20, dtype=torch.uint8, device=dev); junk.zero_(); torch.cuda.synchronize()
-    L.b200_w4a16_debug_set_trace(trace.data_ptr())
-    pkg.ops.quick_gemm(x, *sets[-1], 8)
+    # back-to-back launches, one trace buffer each (the pointer is a launch-time parameter)
+    for i, (qw, s, qz) in enumerate(sets):
+        L.b200_w4a16_debug_set_trace(traces[i].data_ptr())
+        pkg.ops.quick_gemm(x, qw, s, qz, 8)
     torch.cuda.synchronize()
     L.b200_w4a16_debug_set_trace(None)
-    t = trace.cpu().numpy().astype(np.uint32)
+    ta = traces.cpu().numpy().astype(np.uint32)
+    t = ta[-1]
+    grid = pkg._lib.gemm_plan(M, K, N)["grid"]
+    # absolute timeline (globaltimer ns): kernel entry / setup done / epilogue done per launch
+    g0 = np.int64(ta[0, :grid, 7, 2].min())
+    for i in range(nl):
+        ent = ta[i, :grid, 7, 2].astype(np.int64) - g0
+        setup = ta[i, :grid, 7, 3].astype(np.int64) - g0
+        done = ta[i, :grid, 7, 4].astype(np.int64) - g0
+        cyc = (ta[i, :grid, 7, 6].astype(np.int64) - ta[i, :grid, 7, 5].astype(np.int64))
+        ns = done - ent
+        print(f"launch {i}: entry ns min {ent.min()} med {int(np.median(ent))} max {ent.max()} | "
+              f"setup-entry med {int(np.median(setup - ent))} | done min {done.min()} med "
+              f"{int(np.median(done))} max {done.max()} | CTA life ns med {int(np.median(ns))} "
+              f"cycles med {int(np.median(cyc))} => {np.median(cyc) / max(np.median(ns), 1):.3f} GHz")
     plan = pkg._lib.gemm_plan(M, K, N)
     print("plan", plan)
     names = ["issue", "landed", "dq_start", "dq_done", "mma_start", "mma_issued"]

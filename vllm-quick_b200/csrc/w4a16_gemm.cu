@@ -61,6 +61,12 @@ struct Cfg {
   static constexpr int kStagesFit = (kMaxSmem - kBarBytes - 1024) / kStageBytes;
   static constexpr int kStages = kStagesFit > 16 ? 16 : kStagesFit;
   static constexpr int kSmemBytes = kBarBytes + kStages * kStageBytes + 1024;  // + align slack
+  // A tcgen05.commit costs the tensor pipe ~110 cycles (scripts/probes/mma_probe.cu), so MMA
+  // completion is signalled once per kCommit tiles on a ring of kDoneBars barriers; both the
+  // producer (stage reuse) and the dequant groups (operand-buffer reuse) wait on that ring.
+  static constexpr int kCommit = 2;
+  static constexpr int kRingMax = kStages > kABufs ? kStages : kABufs;
+  static constexpr int kDoneBars = (kRingMax + kCommit - 1) / kCommit + 1;
   static_assert(kStages > kGroups, "stage ring must be deeper than the dequant group count");
   static_assert(kDCol + 2 * kDStride <= kTmemCols, "TMEM budget");
 };
@@ -90,8 +96,17 @@ struct GemmParams {
   do {                                                                                       \
     if (p.trace && (i) < 64) p.trace[((size_t)blockIdx.x * 8 + (type)) * 64 + (i)] = (uint32_t)clock64(); \
   } while (0)
+#define TRG(i)                                                                               \
+  do {                                                                                       \
+    if (p.trace) {                                                                           \
+      unsigned long long gt_;                                                                \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_));                                \
+      p.trace[((size_t)blockIdx.x * 8 + 7) * 64 + (i)] = (uint32_t)gt_;                      \
+    }                                                                                        \
+  } while (0)
 #else
 #define TR(type, i) do { } while (0)
+#define TRG(i) do { } while (0)
 #endif
 
 __device__ __forceinline__ int range_begin(int p, int T, int P) {
@@ -157,20 +172,21 @@ template <int MTOK>
 __global__ void __launch_bounds__(kThreads, 1)
 w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
   using C = Cfg<MTOK>;
+  if (threadIdx.x == 0) { TRG(2); TR(7, 5); }
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
 
   // barrier block
-  const uint32_t bar_full = smem_base;                          // [kStages] TMA landed
-  const uint32_t bar_empty = bar_full + 8 * C::kStages;         // [kStages] MMA done with stage
-  const uint32_t bar_afull = bar_empty + 8 * C::kStages;        // [kABufs]  operand dequantized
-  const uint32_t bar_aempty = bar_afull + 8 * C::kABufs;        // [kABufs]  MMA done with operand
-  const uint32_t bar_dfull = bar_aempty + 8 * C::kABufs;        // [2] accumulator complete
+  const uint32_t bar_full = smem_base;                          // [kStages]   TMA landed
+  const uint32_t bar_done = bar_full + 8 * C::kStages;          // [kDoneBars] MMA done, per group
+  const uint32_t bar_afull = bar_done + 8 * C::kDoneBars;       // [kABufs]    operand dequantized
+  const uint32_t bar_dfull = bar_afull + 8 * C::kABufs;         // [2] accumulator complete
   const uint32_t bar_dempty = bar_dfull + 16;                   // [2] accumulator drained
-  const uint32_t tmem_slot = bar_dempty + 16;
+  constexpr int kNumBars = C::kStages + C::kDoneBars + C::kABufs + 4;
+  const uint32_t tmem_slot = smem_base + 8 * kNumBars;
   const uint32_t flag_slot = tmem_slot + 4;
-  static_assert(16 * C::kStages + 16 * C::kABufs + 40 <= C::kBarBytes, "barrier block");
+  static_assert(8 * kNumBars + 8 <= C::kBarBytes, "barrier block");
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(
       smem_gen + (tmem_slot - smem_base));
   volatile uint32_t* flag_gen = reinterpret_cast<volatile uint32_t*>(
@@ -179,21 +195,57 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (warp == kProducerWarp && lane == 0) {
-    tma_prefetch_desc(&tmap_x);
-    for (int s = 0; s < C::kStages; ++s) {
-      mbar_init(bar_full + 8 * s, 1);
-      mbar_init(bar_empty + 8 * s, 1);
+  // This CTA's contiguous slice of the work space, and the order it is walked in.
+  const int t_begin = range_begin(blockIdx.x, p.T, p.P);
+  const int t_end = range_begin(blockIdx.x + 1, p.T, p.P);
+  const Walk walk(t_begin, t_end, p.KB);
+  const int n_total = t_end - t_begin;
+  const int npre = n_total < C::kStages ? n_total : C::kStages;
+
+  // Producer-side helpers (used by the elected thread of warp 0 only).
+  const uint64_t pol_w = (p.flags & 1) ? policy_evict_normal() : policy_evict_first();
+  auto issue_w = [&](const TileCursor& c, int stage) {
+    const int nvalid = min(kTileN, p.N - c.nt * kTileN);
+    const uint32_t sb = stage0 + stage * C::kStageBytes;
+    const uint32_t bar = bar_full + 8 * stage;
+    const uint32_t zs_row = (uint32_t)(nvalid * 2 + nvalid / 2);
+    mbar_arrive_expect_tx(bar, C::kXBytes + kTileWords * 4 + p.R * zs_row);
+    bulk_g2s_hint(sb + C::kWOff, p.qw + ((size_t)c.nt * p.KB + c.kb) * kTileWords,
+                  kTileWords * 4, bar, pol_w);
+    const int g0 = p.R > 1 ? c.kb * p.R : (p.Gdiv == 1 ? c.kb : c.kb / p.Gdiv);
+    for (int r = 0; r < p.R; ++r) {
+      bulk_g2s(sb + C::kSOff + r * 256, p.scales + (size_t)(g0 + r) * p.N + c.nt * kTileN,
+               nvalid * 2, bar);
+      bulk_g2s(sb + C::kZOff + r * 64, p.qz + (size_t)(g0 + r) * (p.N >> 3) + c.nt * 16,
+               nvalid / 2, bar);
     }
-    for (int b = 0; b < C::kABufs; ++b) {
-      mbar_init(bar_afull + 8 * b, 128);
-      mbar_init(bar_aempty + 8 * b, 1);
-    }
-    for (int d = 0; d < 2; ++d) {
-      mbar_init(bar_dfull + 8 * d, 1);
-      mbar_init(bar_dempty + 8 * d, kEpiThreads);
+  };
+  auto issue_x = [&](const TileCursor& c, int stage) {
+    const uint32_t sb = stage0 + stage * C::kStageBytes;
+    const uint32_t bar = bar_full + 8 * stage;
+    tma_load_2d(sb, &tmap_x, c.kb * kTileK, c.mt * MTOK, bar);
+    tma_load_2d(sb + MTOK * 128, &tmap_x, c.kb * kTileK + 64, c.mt * MTOK, bar);
+  };
+  TileCursor cw(walk, p.MT);
+
+  if (warp == kProducerWarp) {
+    // Lane-parallel barrier init, then the weight side of the first npre stages goes out
+    // BEFORE the CTA-wide setup barrier and before griddepcontrol.wait: weights never depend
+    // on the previous kernel, so launch ramp and TMEM allocation overlap the first HBM fetch.
+    for (int b = lane; b < kNumBars; b += 32) {
+      const uint32_t count = b < C::kStages + C::kDoneBars ? 1u
+                             : b < C::kStages + C::kDoneBars + C::kABufs ? 128u
+                             : b < kNumBars - 2 ? 1u : (uint32_t)kEpiThreads;
+      mbar_init(smem_base + 8 * b, count);
     }
     fence_barrier_init();
+    __syncwarp();
+    if (elect_one()) {
+      // Let the next kernel in the stream start its own weight prefetch as soon as an SM frees.
+      asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+      tma_prefetch_desc(&tmap_x);
+      for (int i = 0; i < npre; ++i) { TR(0, i); issue_w(cw, i); cw.next(); }
+    }
   } else if (warp == kAllocWarp) {
     tmem_alloc<kTmemCols>(tmem_slot);
   }
@@ -201,62 +253,30 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_gen;
-
-  // This CTA's contiguous slice of the work space, and the order it is walked in.
-  const int t_begin = range_begin(blockIdx.x, p.T, p.P);
-  const int t_end = range_begin(blockIdx.x + 1, p.T, p.P);
-  const Walk walk(t_begin, t_end, p.KB);
-  const int n_total = t_end - t_begin;
-  if (threadIdx.x == 0) TR(7, 0);
+  if (threadIdx.x == 0) { TR(7, 0); TRG(3); }
 
   if (warp == kProducerWarp) {
+    __syncwarp();
     if (elect_one()) {
-      // Let the next kernel in the stream start its own weight prefetch as soon as an SM frees.
-      asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-      const uint64_t pol_w = (p.flags & 1) ? policy_evict_normal() : policy_evict_first();
-      const int npre = n_total < C::kStages ? n_total : C::kStages;
-      const uint32_t zs_row_bytes_full = kTileN * 2 + kTileN / 2;
-      auto issue_w = [&](const TileCursor& c, int stage) {
-        const int nvalid = min(kTileN, p.N - c.nt * kTileN);
-        const uint32_t sb = stage0 + stage * C::kStageBytes;
-        const uint32_t bar = bar_full + 8 * stage;
-        const uint32_t zs_row =
-            nvalid == kTileN ? zs_row_bytes_full : (uint32_t)(nvalid * 2 + nvalid / 2);
-        mbar_arrive_expect_tx(bar, C::kXBytes + kTileWords * 4 + p.R * zs_row);
-        bulk_g2s_hint(sb + C::kWOff, p.qw + ((size_t)c.nt * p.KB + c.kb) * kTileWords,
-                      kTileWords * 4, bar, pol_w);
-        const int g0 = p.R > 1 ? c.kb * p.R : (p.Gdiv == 1 ? c.kb : c.kb / p.Gdiv);
-        for (int r = 0; r < p.R; ++r) {
-          bulk_g2s(sb + C::kSOff + r * 256, p.scales + (size_t)(g0 + r) * p.N + c.nt * kTileN,
-                   nvalid * 2, bar);
-          bulk_g2s(sb + C::kZOff + r * 64, p.qz + (size_t)(g0 + r) * (p.N >> 3) + c.nt * 16,
-                   nvalid / 2, bar);
-        }
-      };
-      auto issue_x = [&](const TileCursor& c, int stage) {
-        const uint32_t sb = stage0 + stage * C::kStageBytes;
-        const uint32_t bar = bar_full + 8 * stage;
-        tma_load_2d(sb, &tmap_x, c.kb * kTileK, c.mt * MTOK, bar);
-        tma_load_2d(sb + MTOK * 128, &tmap_x, c.kb * kTileK + 64, c.mt * MTOK, bar);
-      };
-      // -- phase 1: weight side of the first npre stages (independent of the previous kernel)
-      TileCursor cw(walk, p.MT), cx(walk, p.MT);
-      for (int i = 0; i < npre; ++i) { TR(0, i); issue_w(cw, i); cw.next(); }
-      asm volatile("griddepcontrol.wait;" ::: "memory");
-      for (int i = 0; i < npre; ++i) { issue_x(cx, i); cx.next(); }
-      // -- phase 2: steady state
+      asm volatile("griddepcontrol.wait;" ::: "memory");      // x is the previous kernel's output
+      {
+        TileCursor cx(walk, p.MT);
+        for (int i = 0; i < npre; ++i) { issue_x(cx, i); cx.next(); }
+      }
+      // -- steady state: refill stage it % kStages once the MMAs of tile it - kStages are done
       int stage = npre % C::kStages;
-      uint32_t ephase = 0;  // first refill of a stage waits for phase 0 of its empty barrier
       for (int it = npre; it < n_total; ++it) {
-        mbar_wait(bar_empty + 8 * stage, ephase);
+        const int g = (it - C::kStages) / C::kCommit;
+        mbar_wait(bar_done + 8 * (g % C::kDoneBars), (g / C::kDoneBars) & 1);
         TR(0, it);
         issue_w(cw, stage);
         issue_x(cw, stage);
         cw.next();
-        if (++stage == C::kStages) { stage = 0; ephase ^= 1u; }
+        if (++stage == C::kStages) stage = 0;
       }
     }
   } else if (warp == kMmaWarp) {
+    __syncwarp();
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_f16_m128(MTOK);
       int stage = 0, buf = 0, itg = 0;
@@ -279,8 +299,10 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
             const uint64_t bdesc = make_desc_k_sw128(xb + (kk >> 2) * (MTOK * 128) + (kk & 3) * 32);
             tc_mma_ts(dcol, tmem + buf * kTmemACols + kk * 8, bdesc, idesc, (i | kk) != 0);
           }
-          tc_commit(bar_empty + 8 * stage);
-          tc_commit(bar_aempty + 8 * buf);
+          if ((itg + 1) % C::kCommit == 0 || itg == n_total - 1) {
+            const int g = itg / C::kCommit;
+            tc_commit(bar_done + 8 * (g % C::kDoneBars));
+          }
           TR(5, itg);
           ++itg;
           if (++stage == C::kStages) { stage = 0; fphase ^= 1u; }
@@ -297,7 +319,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int zsh = 4 * awq_nibble(c & 7);
     int stage = grp % C::kStages, buf = grp % C::kABufs;
-    uint32_t fphase = 0, aphase = (grp / C::kABufs) & 1;
+    uint32_t fphase = 0;
     for (int it = grp; it < n_total; it += kGroups) {
       const uint8_t* sb = smem_gen + C::kBarBytes + stage * C::kStageBytes;
       mbar_wait(bar_full + 8 * stage, fphase);
@@ -310,7 +332,10 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       const uint32_t* sZ = reinterpret_cast<const uint32_t*>(sb + C::kZOff);
       uint32_t zlo = 0, zhi = 0, s2 = 0;
       make_zs1((sZ[c >> 3] >> zsh) & 0xFu, sS[c], zlo, zhi, s2);
-      mbar_wait(bar_aempty + 8 * buf, aphase ^ 1u);
+      if (it >= C::kABufs) {  // operand buffer last used by tile it - kABufs
+        const int g = (it - C::kABufs) / C::kCommit;
+        mbar_wait(bar_done + 8 * (g % C::kDoneBars), (g / C::kDoneBars) & 1);
+      }
       tc_fence_after();
       if ((threadIdx.x & 127) == 0) TR(2, it);
       const uint32_t abase = tmem + lane_base + buf * kTmemACols;
@@ -335,7 +360,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       stage += kGroups;
       if (stage >= C::kStages) { stage -= C::kStages; fphase ^= 1u; }
       buf += kGroups;
-      if (buf >= C::kABufs) { buf -= C::kABufs; aphase ^= 1u; }
+      if (buf >= C::kABufs) buf -= C::kABufs;
     }
   } else if (warp >= kFirstEpiWarp) {
     // ---- epilogue warpgroup: drains accumulators, writes y or fp32 partials, stream-K fix-up
@@ -426,6 +451,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       }
       if (et == 0) TR(6, 2 * idx + 1);
     }
+    if (et == 0) { TRG(4); TR(7, 6); }
   }
 
   tc_fence_before();
