@@ -68,6 +68,7 @@ struct Cfg {
   static constexpr int kRingMax = kStages > kABufs ? kStages : kABufs;
   static constexpr int kDoneBars = (kRingMax + kCommit - 1) / kCommit + 1;
   static_assert(kStages > kGroups, "stage ring must be deeper than the dequant group count");
+  static_assert(kABufs <= kStages, "operand-ring wait must imply the stage's previous phase landed");
   static_assert(kDCol + 2 * kDStride <= kTmemCols, "TMEM budget");
 };
 
@@ -322,6 +323,15 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     uint32_t fphase = 0;
     for (int it = grp; it < n_total; it += kGroups) {
       const uint8_t* sb = smem_gen + C::kBarBytes + stage * C::kStageBytes;
+      // Operand buffer it % kABufs was last read by the MMAs of tile it - kABufs.  This wait
+      // comes FIRST on purpose: the stage this tile sits in was last used by tile it - kStages
+      // (< it - kABufs + 1), and a parity wait on its full barrier is only meaningful once
+      // that earlier phase has completed -- bulk copies of different stages can land out of
+      // order, and a group that runs ahead would otherwise see the stale phase as "landed".
+      if (it >= C::kABufs) {
+        const int g = (it - C::kABufs) / C::kCommit;
+        mbar_wait(bar_done + 8 * (g % C::kDoneBars), (g / C::kDoneBars) & 1);
+      }
       mbar_wait(bar_full + 8 * stage, fphase);
       if ((threadIdx.x & 127) == 0) TR(1, it);
       uint4 wv[4];
@@ -332,10 +342,6 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       const uint32_t* sZ = reinterpret_cast<const uint32_t*>(sb + C::kZOff);
       uint32_t zlo = 0, zhi = 0, s2 = 0;
       make_zs1((sZ[c >> 3] >> zsh) & 0xFu, sS[c], zlo, zhi, s2);
-      if (it >= C::kABufs) {  // operand buffer last used by tile it - kABufs
-        const int g = (it - C::kABufs) / C::kCommit;
-        mbar_wait(bar_done + 8 * (g % C::kDoneBars), (g / C::kDoneBars) & 1);
-      }
       tc_fence_after();
       if ((threadIdx.x & 127) == 0) TR(2, it);
       const uint32_t abase = tmem + lane_base + buf * kTmemACols;
