@@ -8,7 +8,7 @@
 using namespace b200;
 
 template <int N, int MODE>  // MODE 0: ts, 1: ss
-__global__ void __launch_bounds__(192, 1) probe(int tiles, int st_on, int commit_every, long long* out) {
+__global__ void __launch_bounds__(192, 1) probe(int tiles, int st_on, int commit_every, int nacc, long long* out) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar = base, slot = base + 64;
@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(192, 1) probe(int tiles, int st_on, int commit
         for (int kk = 0; kk < 8; ++kk) {
           const uint64_t bdesc = make_desc_k_sw128(bsm + (kk >> 2) * (N * 128) + (kk & 3) * 32);
           if (MODE == 0) {
-            tc_mma_ts(tmem + 256, tmem + (t & 3) * 64 + kk * 8, bdesc, idesc, 1);
+            tc_mma_ts(tmem + 256 + (kk % nacc) * N, tmem + (t & 3) * 64 + kk * 8, bdesc, idesc, 1);
           } else {
             const uint64_t adesc = make_desc_k_sw128(asm_ + (kk >> 2) * (128 * 128) + (kk & 3) * 32);
             tc_mma_ss(tmem + 256, adesc, bdesc, idesc, 1);
@@ -79,16 +79,16 @@ __global__ void __launch_bounds__(192, 1) probe(int tiles, int st_on, int commit
 }
 
 template <int N, int MODE>
-void run(int tiles, int st_on, int commit_every, long long* dout) {
+void run(int tiles, int st_on, int commit_every, long long* dout, int nacc = 1) {
   const int smem = 2048 + N * 256 + 128 * 256 + 1024;
   cudaFuncSetAttribute(probe<N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   cudaMemset(dout, 0, 16);
-  probe<N, MODE><<<148, 192, smem>>>(tiles, st_on, commit_every, dout);
+  probe<N, MODE><<<148, 192, smem>>>(tiles, st_on, commit_every, nacc, dout);
   cudaError_t e = cudaDeviceSynchronize();
   long long h[2];
   cudaMemcpy(h, dout, 16, cudaMemcpyDeviceToHost);
-  printf("N=%3d %s st=%d commit_every=%d: %.1f cycles/mma  (st x16 issued %lld, %.1f B/cycle)  %s\n", N,
-         MODE ? "ss" : "ts", st_on, commit_every, (double)h[0] / (tiles * 8.0), h[1],
+  printf("N=%3d %s st=%d nacc=%d commit_every=%d: %.1f cycles/mma  (st x16 issued %lld, %.1f B/cycle)  %s\n", N,
+         MODE ? "ss" : "ts", st_on, nacc, commit_every, (double)h[0] / (tiles * 8.0), h[1],
          h[0] ? (double)h[1] * 2048.0 * 4 / h[0] : 0.0, e == cudaSuccess ? "" : cudaGetErrorString(e));
 }
 
@@ -96,18 +96,15 @@ int main() {
   long long* dout;
   cudaMalloc(&dout, 16);
   const int tiles = 2000;
-  for (int st = 0; st < 2; ++st) {
-    run<16, 0>(tiles, st, 1, dout);
-    run<32, 0>(tiles, st, 1, dout);
-    run<64, 0>(tiles, st, 1, dout);
-    run<128, 0>(tiles, st, 1, dout);
-    run<256, 0>(tiles, st, 1, dout);
-    run<16, 1>(tiles, st, 1, dout);
-    run<64, 1>(tiles, st, 1, dout);
-    run<128, 1>(tiles, st, 1, dout);
-    run<256, 1>(tiles, st, 1, dout);
-  }
-  run<16, 0>(tiles, 0, 1000000, dout);
-  run<128, 0>(tiles, 0, 1000000, dout);
+  for (int nacc = 1; nacc <= 4; nacc *= 2)
+    for (int ce = 1; ce <= 8; ce *= 2) {
+      run<16, 0>(tiles, 0, ce, dout, nacc);
+      run<32, 0>(tiles, 0, ce, dout, nacc);
+      if (nacc <= 2) run<64, 0>(tiles, 0, ce, dout, nacc);
+    }
+  run<16, 0>(tiles, 1, 4, dout, 2);
+  run<16, 0>(tiles, 0, 1000000, dout, 2);
+  run<16, 0>(tiles, 0, 1000000, dout, 4);
+  run<128, 0>(tiles, 0, 4, dout, 1);
   return 0;
 }
