@@ -107,9 +107,11 @@ def test_no_device_means_no_compute(pkg, cuda_lib):
 
 
 @pytest.mark.parametrize("M,K,N,tok,grid", [
-    (1, 4096, 4096, 16, 148), (16, 4096, 12288, 16, 148), (17, 4096, 4096, 32, 148),
-    (64, 11008 // 128 * 128, 4096, 64, 148), (256, 4096, 4096, 128, 148),
-    (8192, 5120, 15360, 128, 148), (3, 128, 64, 16, 1), (16, 256, 128, 16, 2),
+    # M <= 16: mma.sync decode kernel, one persistent CTA per SM, 8- or 16-token tiles
+    (1, 4096, 4096, 8, 148), (16, 4096, 12288, 16, 148), (3, 128, 64, 8, 1), (16, 256, 128, 16, 2),
+    # above: tcgen05 stream-K kernel, one persistent CTA per SM
+    (17, 4096, 4096, 32, 148), (64, 11008 // 128 * 128, 4096, 64, 148),
+    (256, 4096, 4096, 128, 148), (8192, 5120, 15360, 128, 148),
 ])
 def test_gemm_plan(pkg, M, K, N, tok, grid):
     plan = pkg._lib.gemm_plan(M, K, N)

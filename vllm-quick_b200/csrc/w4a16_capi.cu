@@ -157,7 +157,11 @@ int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* s
     qw = scratch;
     pdl = false;
   }
-  int e = b200::launch_gemm(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters, pdl, s);
+  int e = plan.kind == b200::kKindDecode
+              ? b200::launch_decode(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters,
+                                    pdl, s)
+              : b200::launch_gemm(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters,
+                                  pdl, s);
   if (e != 0) return cuda_fail(e);
   return B200_OK;
 }

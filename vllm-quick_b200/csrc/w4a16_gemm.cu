@@ -26,6 +26,7 @@
 //    (weights never depend on the previous kernel), so launch ramp overlaps the previous op.
 #include "w4a16_common.cuh"
 #include "w4a16_internal.h"
+#include "w4a16_streamk.cuh"
 
 #include <stdlib.h>
 
@@ -109,65 +110,6 @@ struct GemmParams {
 #define TR(type, i) do { } while (0)
 #define TRG(i) do { } while (0)
 #endif
-
-__device__ __forceinline__ int range_begin(int p, int T, int P) {
-  return (int)((long long)p * T / P);
-}
-__device__ __forceinline__ int owner_of(int t, int P, int T) {
-  return (int)((((long long)t + 1) * P - 1) / T);
-}
-
-// The order in which a CTA walks its contiguous work range [t_begin, t_end): the segment
-// that finishes someone else's output tile first, then the segment that starts a tile someone
-// else finishes, then its whole tiles.  Every warp role derives the same sequence.
-struct Walk {
-  int t_begin, t_end, KB;
-  int first_end;   // end of the first segment
-  int tail_start;  // start of a distinct, partial last segment, or -1
-  int nseg;
-  __device__ __forceinline__ Walk(int tb, int te, int kb) : t_begin(tb), t_end(te), KB(kb) {
-    if (te <= tb) { first_end = tb; tail_start = -1; nseg = 0; return; }
-    const int fe = (tb / kb + 1) * kb;
-    first_end = fe < te ? fe : te;
-    const int ls = ((te - 1) / kb) * kb;
-    tail_start = (ls >= first_end && te - ls < kb) ? ls : -1;
-    const int mid_end = tail_start >= 0 ? tail_start : te;
-    nseg = 1 + (tail_start >= 0 ? 1 : 0) + (mid_end - first_end) / kb;
-  }
-  __device__ __forceinline__ void seg(int idx, int& t0, int& n) const {
-    if (idx == 0) { t0 = t_begin; n = first_end - t_begin; return; }
-    if (tail_start >= 0) {
-      if (idx == 1) { t0 = tail_start; n = t_end - tail_start; return; }
-      --idx;
-    }
-    t0 = first_end + (idx - 1) * KB;
-    n = KB;
-  }
-};
-
-// Tile-by-tile cursor over a Walk (used by the single producer thread).
-struct TileCursor {
-  const Walk& w;
-  int MT;
-  int idx, left;
-  int kb, nt, mt;
-  __device__ __forceinline__ TileCursor(const Walk& walk, int mt_count)
-      : w(walk), MT(mt_count), idx(-1), left(0), kb(0), nt(0), mt(0) { load_next(); }
-  __device__ __forceinline__ void load_next() {
-    if (++idx >= w.nseg) return;
-    int t0, n;
-    w.seg(idx, t0, n);
-    const int o = t0 / w.KB;
-    kb = t0 - o * w.KB;
-    nt = o / MT;
-    mt = o - nt * MT;
-    left = n;
-  }
-  __device__ __forceinline__ void next() {
-    ++kb;
-    if (--left == 0) load_next();
-  }
-};
 
 template <int MTOK>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -532,19 +474,52 @@ void fill_plan(GemmPlan* plan) {
 }  // namespace
 
 void set_trace_buffer(uint32_t* dev) { g_trace = dev; }
+uint32_t* trace_buffer() { return g_trace; }
+
+// B200_W4A16_KERNEL=tcgen05|decode pins the variant (tuning / tests); default: by shape.
+static int forced_kind() {
+  static const int k = [] {
+    const char* e = getenv("B200_W4A16_KERNEL");
+    if (!e) return -1;
+    if (e[0] == 't') return (int)kKindTcgen05;
+    if (e[0] == 'd') return (int)kKindDecode;
+    return -1;
+  }();
+  return k;
+}
 
 int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, GemmPlan* plan) {
-  (void)G;
   (void)split_k_hint;
+  if (sm_count <= 0) sm_count = kMaxCtas;
+  plan->n_tiles = (N + kTileN - 1) / kTileN;
+  plan->k_blocks = K / kTileK;
+  const bool decode_ok = M <= kDecodeMaxTokens && G % kTileK == 0;
+  const int fk = forced_kind();
+  const bool decode = decode_ok && fk != (int)kKindTcgen05;
+  if (decode) {
+    // Decode variant: stream-K over (channel tile, K block), two CTAs per SM.
+    plan->kind = kKindDecode;
+    plan->m_tiles = 1;
+    const long long T = (long long)plan->n_tiles * plan->k_blocks;
+    if (T >= (1LL << 31)) return 1;
+    long long ctas = (long long)sm_count * kDecodeCtasPerSm;
+    if (T < ctas) ctas = T;
+    if (ctas < 1) ctas = 1;
+    plan->ctas = (int)ctas;
+    const long long per = T / ctas;
+    plan->max_split = (plan->k_blocks == 0 || (T % ctas == 0 && per % plan->k_blocks == 0))
+                          ? 1
+                          : (int)((plan->k_blocks + per - 1) / (per > 0 ? per : 1) + 1);
+    fill_decode_plan(M, plan);
+    return 0;
+  }
+  plan->kind = kKindTcgen05;
   const int tok = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;
   plan->tok_tile = tok;
-  plan->n_tiles = (N + kTileN - 1) / kTileN;
   plan->m_tiles = (M + tok - 1) / tok;
-  plan->k_blocks = K / kTileK;
   const long long outs = (long long)plan->n_tiles * plan->m_tiles;
   const long long T = outs * plan->k_blocks;
   if (T >= (1LL << 31)) return 1;
-  if (sm_count <= 0) sm_count = kMaxCtas;
   // Persistent stream-K: one CTA per SM, equal contiguous ranges of (output tile, K block).
   long long ctas = T < sm_count ? T : sm_count;
   if (ctas < 1) ctas = 1;

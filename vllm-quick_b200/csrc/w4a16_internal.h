@@ -13,9 +13,14 @@ constexpr int kTileN = 128;        // output channels per weight tile  (tcgen05 
 constexpr int kTileK = 128;        // input rows per weight tile       (8 x UMMA_K)
 constexpr int kTileWords = 2048;   // int32 words per packed tile (8 KiB)
 constexpr int kMaxCtas = 148;      // one CTA per SM on B200
+constexpr int kDecodeCtasPerSm = 1;    // decode kernel residency (w4a16_decode.cu)
+constexpr int kDecodeMaxTokens = 16;   // M above this goes to the tcgen05 kernel
+
+enum GemmKind { kKindTcgen05 = 0, kKindDecode = 1 };
 
 // How a GEMM is cut into CTAs (stream-K over the (channel tile, token tile, K block) space).
 struct GemmPlan {
+  int kind;          // GemmKind: tcgen05 stream-K kernel or the mma.sync decode kernel
   int tok_tile;      // tokens per MMA tile (tcgen05 N): 16 / 32 / 64 / 128
   int n_tiles;       // ceil(N / 128)
   int m_tiles;       // ceil(M / tok_tile)
@@ -36,8 +41,16 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
                 const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
                 cudaStream_t stream);
 
+// Decode variant (M <= 16, G % 128 == 0): same layout, workspace protocol and semantics.
+void fill_decode_plan(int M, GemmPlan* plan);
+int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
+                  const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
+                  const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
+                  cudaStream_t stream);
+
 // B200_TRACE builds: device buffer of 148 x 8 x 64 uint32 timestamps (nullptr = off).
 void set_trace_buffer(uint32_t* dev);
+uint32_t* trace_buffer();
 
 int launch_dequant(const int32_t* qweight, const uint16_t* scales, const int32_t* qzeros,
                    uint16_t* W, int K, int N, int G, int layout, cudaStream_t stream);
