@@ -340,4 +340,14 @@ __device__ __forceinline__ int atom_add_acq_rel_gpu(int* addr, int v) {
   return old;
 }
 
+// Fire-and-forget publish / polling read used by the deferred stream-K fix-up.
+__device__ __forceinline__ void red_add_release_gpu(int* addr, int v) {
+  asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_gpu(const int* addr) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+
 }  // namespace b200

@@ -37,6 +37,7 @@ namespace {
 constexpr int kProducerWarp = 0;
 constexpr int kMmaWarp = 1;
 constexpr int kAllocWarp = 2;
+constexpr int kXProducerWarp = 3;
 constexpr int kFirstEpiWarp = 4;                        // warps 4..7 (warp % 4 == lane quarter)
 constexpr int kEpiThreads = 128;
 constexpr int kFirstDequantWarp = 8;
@@ -128,12 +129,9 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   const uint32_t bar_dempty = bar_dfull + 16;                   // [2] accumulator drained
   constexpr int kNumBars = C::kStages + C::kDoneBars + C::kABufs + 4;
   const uint32_t tmem_slot = smem_base + 8 * kNumBars;
-  const uint32_t flag_slot = tmem_slot + 4;
   static_assert(8 * kNumBars + 8 <= C::kBarBytes, "barrier block");
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(
       smem_gen + (tmem_slot - smem_base));
-  volatile uint32_t* flag_gen = reinterpret_cast<volatile uint32_t*>(
-      smem_gen + (flag_slot - smem_base));
   const uint32_t stage0 = smem_base + C::kBarBytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -145,36 +143,60 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   const int n_total = t_end - t_begin;
   const int npre = n_total < C::kStages ? n_total : C::kStages;
 
-  // Producer-side helpers (used by the elected thread of warp 0 only).
-  const uint64_t pol_w = (p.flags & 1) ? policy_evict_normal() : policy_evict_first();
-  auto issue_w = [&](const TileCursor& c, int stage) {
-    const int nvalid = min(kTileN, p.N - c.nt * kTileN);
-    const uint32_t sb = stage0 + stage * C::kStageBytes;
-    const uint32_t bar = bar_full + 8 * stage;
-    const uint32_t zs_row = (uint32_t)(nvalid * 2 + nvalid / 2);
-    mbar_arrive_expect_tx(bar, C::kXBytes + kTileWords * 4 + p.R * zs_row);
-    bulk_g2s_hint(sb + C::kWOff, p.qw + ((size_t)c.nt * p.KB + c.kb) * kTileWords,
-                  kTileWords * 4, bar, pol_w);
-    const int g0 = p.R > 1 ? c.kb * p.R : (p.Gdiv == 1 ? c.kb : c.kb / p.Gdiv);
-    for (int r = 0; r < p.R; ++r) {
-      bulk_g2s(sb + C::kSOff + r * 256, p.scales + (size_t)(g0 + r) * p.N + c.nt * kTileN,
-               nvalid * 2, bar);
-      bulk_g2s(sb + C::kZOff + r * 64, p.qz + (size_t)(g0 + r) * (p.N >> 3) + c.nt * 16,
-               nvalid / 2, bar);
+  // Weight stream of this CTA (elected thread of warp 0): tiles in walk order with addresses
+  // advanced incrementally -- consecutive K blocks of a channel tile are contiguous in the
+  // B200 layout, so the steady state is an add, an mbarrier wait and three bulk copies.
+  struct WStream {
+    const GemmParams& p;
+    const Walk& walk;
+    int idx, left, nt, kb;
+    uint32_t tx;
+    const uint32_t* wsrc;
+    const uint16_t* s0;
+    const uint32_t* z0;
+    uint32_t nvalid;
+    __device__ __forceinline__ WStream(const GemmParams& pp, const Walk& w)
+        : p(pp), walk(w), idx(-1), left(0), nt(0), kb(0), tx(0), wsrc(nullptr), s0(nullptr),
+          z0(nullptr), nvalid(0) {}
+    __device__ __forceinline__ void open() {
+      if (++idx >= walk.nseg) return;
+      int t0, n;
+      walk.seg(idx, t0, n);
+      const int o = t0 / p.KB;
+      kb = t0 - o * p.KB;
+      nt = o / p.MT;
+      left = n;
+      nvalid = (uint32_t)min(kTileN, p.N - nt * kTileN);
+      tx = (uint32_t)Cfg<MTOK>::kXBytes + kTileWords * 4 + (uint32_t)p.R * (nvalid * 2 + nvalid / 2);
+      wsrc = p.qw + ((size_t)nt * p.KB + kb) * kTileWords;
+      s0 = p.scales + nt * kTileN;
+      z0 = p.qz + nt * 16;
+    }
+    __device__ __forceinline__ void next() {
+      ++kb;
+      wsrc += kTileWords;
+      if (--left == 0) open();
     }
   };
-  auto issue_x = [&](const TileCursor& c, int stage) {
+  const uint64_t pol_w = (p.flags & 1) ? policy_evict_normal() : policy_evict_first();
+  auto issue_w = [&](const WStream& c, int stage) {
     const uint32_t sb = stage0 + stage * C::kStageBytes;
     const uint32_t bar = bar_full + 8 * stage;
-    tma_load_2d(sb, &tmap_x, c.kb * kTileK, c.mt * MTOK, bar);
-    tma_load_2d(sb + MTOK * 128, &tmap_x, c.kb * kTileK + 64, c.mt * MTOK, bar);
+    mbar_arrive_expect_tx(bar, c.tx);
+    bulk_g2s_hint(sb + C::kWOff, c.wsrc, kTileWords * 4, bar, pol_w);
+    const uint32_t g0 = p.R > 1 ? (uint32_t)(c.kb * p.R)
+                                : (p.Gdiv == 1 ? (uint32_t)c.kb : (uint32_t)c.kb / (uint32_t)p.Gdiv);
+    for (int r = 0; r < p.R; ++r) {
+      bulk_g2s(sb + C::kSOff + r * 256, c.s0 + (size_t)(g0 + r) * p.N, c.nvalid * 2, bar);
+      bulk_g2s(sb + C::kZOff + r * 64, c.z0 + (size_t)(g0 + r) * (p.N >> 3), c.nvalid / 2, bar);
+    }
   };
-  TileCursor cw(walk, p.MT);
 
+  WStream cw(p, walk);                                      // opened by the producer thread only
   if (warp == kProducerWarp) {
     // Lane-parallel barrier init, then the weight side of the first npre stages goes out
-    // BEFORE the CTA-wide setup barrier and before griddepcontrol.wait: weights never depend
-    // on the previous kernel, so launch ramp and TMEM allocation overlap the first HBM fetch.
+    // BEFORE the CTA-wide setup barrier and without ever waiting for the previous kernel:
+    // weights never depend on it, so launch ramp and TMEM allocation overlap the first fetch.
     for (int b = lane; b < kNumBars; b += 32) {
       const uint32_t count = b < C::kStages + C::kDoneBars ? 1u
                              : b < C::kStages + C::kDoneBars + C::kABufs ? 128u
@@ -186,9 +208,10 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     if (elect_one()) {
       // Let the next kernel in the stream start its own weight prefetch as soon as an SM frees.
       asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-      tma_prefetch_desc(&tmap_x);
+      cw.open();
       for (int i = 0; i < npre; ++i) { TR(0, i); issue_w(cw, i); cw.next(); }
     }
+    __syncwarp();
   } else if (warp == kAllocWarp) {
     tmem_alloc<kTmemCols>(tmem_slot);
   }
@@ -199,23 +222,45 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   if (threadIdx.x == 0) { TR(7, 0); TRG(3); }
 
   if (warp == kProducerWarp) {
+    // -- steady state: refill stage it % kStages once the MMAs of tile it - kStages are done.
+    // elect.sync picks the same lane as before the setup barrier, so `cw` carries over.
     __syncwarp();
     if (elect_one()) {
-      asm volatile("griddepcontrol.wait;" ::: "memory");      // x is the previous kernel's output
-      {
-        TileCursor cx(walk, p.MT);
-        for (int i = 0; i < npre; ++i) { issue_x(cx, i); cx.next(); }
-      }
-      // -- steady state: refill stage it % kStages once the MMAs of tile it - kStages are done
       int stage = npre % C::kStages;
       for (int it = npre; it < n_total; ++it) {
         const int g = (it - C::kStages) / C::kCommit;
         mbar_wait(bar_done + 8 * (g % C::kDoneBars), (g / C::kDoneBars) & 1);
         TR(0, it);
         issue_w(cw, stage);
-        issue_x(cw, stage);
         cw.next();
         if (++stage == C::kStages) stage = 0;
+      }
+    }
+  } else if (warp == kXProducerWarp) {
+    // Activation stream (elected thread of warp 3): two 64-column TMA boxes per tile, issued
+    // once the previous kernel's output is visible.
+    __syncwarp();
+    if (elect_one()) {
+      tma_prefetch_desc(&tmap_x);
+      asm volatile("griddepcontrol.wait;" ::: "memory");      // x is the previous kernel's output
+      int it = 0;
+      for (int idx = 0; idx < walk.nseg; ++idx) {
+        int t0, n;
+        walk.seg(idx, t0, n);
+        const int o = t0 / p.KB;
+        int kb = t0 - o * p.KB;
+        const int m0 = (o % p.MT) * MTOK;
+        for (int i = 0; i < n; ++i, ++it, ++kb) {
+          const int stage = it % C::kStages;
+          if (it >= C::kStages) {
+            const int g = (it - C::kStages) / C::kCommit;
+            mbar_wait(bar_done + 8 * (g % C::kDoneBars), (g / C::kDoneBars) & 1);
+          }
+          const uint32_t sb = stage0 + stage * C::kStageBytes;
+          const uint32_t bar = bar_full + 8 * stage;
+          tma_load_2d(sb, &tmap_x, kb * kTileK, m0, bar);
+          tma_load_2d(sb + MTOK * 128, &tmap_x, kb * kTileK + 64, m0, bar);
+        }
       }
     }
   } else if (warp == kMmaWarp) {
@@ -311,11 +356,15 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       if (buf >= C::kABufs) buf -= C::kABufs;
     }
   } else if (warp >= kFirstEpiWarp) {
-    // ---- epilogue warpgroup: drains accumulators, writes y or fp32 partials, stream-K fix-up
+    // ---- epilogue warpgroup: drains accumulators; a whole tile goes to y, a partial one is
+    // published as fp32 and finished after the main loop by the CTA that owns the tile's first
+    // K block (deferred stream-K fix-up: nothing here waits on another CTA mid-stream)
     const int q = warp - kFirstEpiWarp;
     const int c = q * 32 + lane;                              // channel inside the tile
     const int et = threadIdx.x - kFirstEpiWarp * 32;          // 0..127
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    constexpr int kPartVec = MTOK * kTileN / 4;               // float4 per partial tile
+    int own_o = -1, own_slot = 0, own_last = 0;               // tile this CTA finishes, if any
     asm volatile("griddepcontrol.wait;" ::: "memory");        // y / workspace may alias earlier work
     for (int idx = 0; idx < walk.nseg; ++idx) {
       int t0, n;
@@ -327,7 +376,10 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       const int n_glob = nt * kTileN + c;
       const int m0 = mt * MTOK;
       const uint32_t dbase = tmem + lane_base + C::kDCol + d * C::kDStride;
-      float* part = p.partials + ((size_t)blockIdx.x * 2 + (idx == 0 ? 0 : 1)) * (size_t)(MTOK * kTileN);
+      const int slot = idx == 0 ? 0 : 1;
+      // partial layout: float4 v of channel c holds tokens 4 v .. 4 v + 3 -> [v][c], coalesced
+      float4* part = reinterpret_cast<float4*>(p.partials) +
+                     ((size_t)blockIdx.x * 2 + slot) * kPartVec + c;
       mbar_wait(bar_dfull + 8 * d, (idx >> 1) & 1);
       tc_fence_after();
       if (et == 0) TR(6, 2 * idx);
@@ -348,56 +400,99 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           }
         } else {
 #pragma unroll
-          for (int e = 0; e < 16; ++e) __stcg(part + (cc + e) * kTileN + c, __uint_as_float(v[e]));
+          for (int e = 0; e < 16; e += 4)
+            __stcg(part + ((cc + e) >> 2) * kTileN,
+                   make_float4(__uint_as_float(v[e]), __uint_as_float(v[e + 1]),
+                               __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3])));
         }
       }
       tc_fence_before();
       mbar_arrive(bar_dempty + 8 * d);
       if (!whole) {
-        // stream-K fix-up: the last CTA to arrive sums all contributors in CTA order.
         const int o_lo = o * p.KB;
         const int p_first = owner_of(o_lo, p.P, p.T);
-        const int p_last = owner_of(o_lo + p.KB - 1, p.P, p.T);
         named_bar_sync(1, kEpiThreads);                       // every partial store is issued
-        if (et == 0) {
-          // release our partials / acquire everyone else's (cumulative through the barrier)
-          const int old = atom_add_acq_rel_gpu(p.counters + p_first, 1);
-          *flag_gen = (old == p_last - p_first) ? 1u : 0u;
+        if (et == 0) red_add_release_gpu(p.counters + p_first, 1);   // publish, do not wait
+        if (p_first == (int)blockIdx.x) {                     // at most one such tile per CTA
+          own_o = o;
+          own_slot = slot;
+          own_last = owner_of(o_lo + p.KB - 1, p.P, p.T);
         }
-        named_bar_sync(1, kEpiThreads);
-        const bool last = (*flag_gen != 0u);
-        named_bar_sync(1, kEpiThreads);  // flag consumed before anyone can overwrite it
-        if (last) {
-          if (et == 0) p.counters[p_first] = 0;               // leave the workspace zeroed
-          if (n_glob < p.N) {
+      }
+      if (et == 0) TR(6, 2 * idx + 1);
+    }
+
+    // ---- deferred fix-up: sum the contributors of the owned tile in CTA order (bit-identical
+    // run to run).  The others handled this tile FIRST in their walk, so their partials are
+    // normally long there; every CTA of the grid is resident (grid <= SM count), so the wait
+    // cannot deadlock.
+    if (own_o >= 0) {
+      if (et == 0) {
+        const int need = own_last - (int)blockIdx.x + 1;
+        const long long w0 = clock64();
+        while (ld_acquire_gpu(p.counters + blockIdx.x) < need) {
+          if (clock64() - w0 > B200_WATCHDOG_CYCLES) {
+            printf("b200_w4a16: stream-K fix-up timeout block %d\n", blockIdx.x);
+            __trap();
+          }
+        }
+        p.counters[blockIdx.x] = 0;                           // leave the workspace zeroed
+      }
+      named_bar_sync(1, kEpiThreads);
+      const int nt = own_o / p.MT, mt = own_o - nt * p.MT;
+      const int n_glob = nt * kTileN + c;
+      const int m0 = mt * MTOK;
+      const float4* mine = reinterpret_cast<const float4*>(p.partials) +
+                           ((size_t)blockIdx.x * 2 + own_slot) * kPartVec + c;
+      // later contributors start inside the tile: their partial sits in slot 0
+      const float4* others = reinterpret_cast<const float4*>(p.partials) +
+                             ((size_t)(blockIdx.x + 1) * 2) * kPartVec + c;
+      const int nother = own_last - (int)blockIdx.x;
+      if (n_glob < p.N) {
 #pragma unroll 1
-            for (int cc = 0; cc < MTOK; cc += 16) {
-              float acc[16];
+        for (int cc = 0; cc < MTOK; cc += 16) {
+          float4 acc[4], f[2][4];
 #pragma unroll
-              for (int e = 0; e < 16; ++e) acc[e] = 0.f;
+          for (int e = 0; e < 4; ++e) acc[e] = __ldcg(mine + ((cc >> 2) + e) * kTileN);
+          if (nother > 0) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) f[0][e] = __ldcg(others + ((cc >> 2) + e) * kTileN);
+          }
+          // two contributors in flight: the loads of j + 1 overlap the adds of j
 #pragma unroll 1
-              for (int pc = p_first; pc <= p_last; ++pc) {
-                const int pc_begin = range_begin(pc, p.T, p.P);
-                const float* src = p.partials +
-                                   ((size_t)pc * 2 + (pc_begin >= o_lo ? 0 : 1)) * (size_t)(MTOK * kTileN) +
-                                   cc * kTileN + c;
-                float f[16];
+          for (int j = 0; j < nother; j += 2) {
+            const float4* s1 = others + (size_t)(j + 1) * 2 * kPartVec;
+            if (j + 1 < nother) {
 #pragma unroll
-                for (int e = 0; e < 16; ++e) f[e] = __ldcg(src + e * kTileN);
+              for (int e = 0; e < 4; ++e) f[1][e] = __ldcg(s1 + ((cc >> 2) + e) * kTileN);
+            }
 #pragma unroll
-                for (int e = 0; e < 16; ++e) acc[e] += f[e];
+            for (int e = 0; e < 4; ++e) {
+              acc[e].x += f[0][e].x; acc[e].y += f[0][e].y; acc[e].z += f[0][e].z; acc[e].w += f[0][e].w;
+            }
+            if (j + 2 < nother) {
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                f[0][e] = __ldcg(s1 + (size_t)2 * kPartVec + ((cc >> 2) + e) * kTileN);
+            }
+            if (j + 1 < nother) {
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                acc[e].x += f[1][e].x; acc[e].y += f[1][e].y; acc[e].z += f[1][e].z; acc[e].w += f[1][e].w;
               }
+            }
+          }
 #pragma unroll
-              for (int e = 0; e < 16; ++e) {
-                const int m = m0 + cc + e;
-                if (m < p.M)
-                  p.y[(size_t)m * p.N + n_glob] = __half_as_ushort(__float2half_rn(acc[e]));
-              }
+          for (int e = 0; e < 4; ++e) {
+            const float r[4] = {acc[e].x, acc[e].y, acc[e].z, acc[e].w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int m = m0 + cc + 4 * e + u;
+              if (m < p.M) p.y[(size_t)m * p.N + n_glob] = __half_as_ushort(__float2half_rn(r[u]));
             }
           }
         }
       }
-      if (et == 0) TR(6, 2 * idx + 1);
     }
     if (et == 0) { TRG(4); TR(7, 6); }
   }
