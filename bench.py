@@ -167,6 +167,13 @@ def run_reference(args, model, tp):
     }))
 
 
+def kernel_name(pkg, M, K, N):
+    plan = pkg._lib.gemm_plan(M, K, N)
+    if plan["variant"] == "decode":
+        return f"w4a16_decode_kernel<{plan['tok_tile'] // 8}>"
+    return f"w4a16_gemm_kernel<{plan['tok_tile']}>"
+
+
 def workload_config(model, tp, M):
     return {"workload": f"{model} AWQ W4 g{GROUP} decode linear layers (qkv,o,gate_up,down x all layers), "
                         f"batch M={M}, tensor-parallel={tp}",
@@ -186,6 +193,8 @@ def main():
     ap.add_argument("--model", default=None, help="llama2-7b | llama2-13b | llama2-70b")
     ap.add_argument("--layers", type=int, default=None, help="override layer count (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--nccl-allreduce", action="store_true",
+                    help="row-parallel all-reduce through NCCL instead of the NVLink peer-memory kernel")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -211,36 +220,52 @@ def main():
     M = args.batch
     shapes = layer_shapes(model, tp)
     n_layers = args.layers or MODELS[model][5]
+    hidden, inter, qh, kvh, hd, _ = MODELS[model]
+    pl = importlib.import_module("vllm-quick_b200.parallel_linear")
+    pu = importlib.import_module("vllm-quick_b200.parallel_utils")
+    if world > 1:
+        pu.initialize_model_parallel(world)
+        if not args.nccl_allreduce:
+            pu.custom_all_reduce.init_custom_all_reduce(max_bytes=M * hidden * 2)
     method = pkg.QuickConfig(4, GROUP, True).get_linear_method()
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
 
-    # ---- weights through the plugin's own create_weights + post-load interleave
+    # ---- the four tensor-parallel quantized linears of every decoder layer, built through the
+    # plugin's own create_weights (inside the layer classes) + post-load interleave
+    def fill(layer):
+        w = layer.linear_weights
+        for name in ("qweight", "qzeros"):
+            t = w[name]
+            t.data = torch.randint(-2**31, 2**31 - 1, tuple(t.shape), dtype=torch.int32, device=dev, generator=g)
+        w["scales"].data = (torch.rand(tuple(w["scales"].shape), device=dev, generator=g) * 0.019 + 0.001).half()
+        method.process_weights_after_loading(w)
+        return layer
+
+    kw = dict(bias=False, linear_method=method, params_dtype=torch.float16)
     layers = []
     for _ in range(n_layers):
-        ws = []
-        for (_, K, N, _) in shapes:
-            w = method.create_weights(K, N, K, N, torch.float16)
-            w = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in w.items()}
-            w["qweight"].data = torch.randint(-2**31, 2**31 - 1, (K, N // 8), dtype=torch.int32, device=dev, generator=g)
-            w["qzeros"].data = torch.randint(-2**31, 2**31 - 1, (K // GROUP, N // 8), dtype=torch.int32, device=dev, generator=g)
-            w["scales"].data = (torch.rand((K // GROUP, N), device=dev, generator=g) * 0.019 + 0.001).half()
-            method.process_weights_after_loading(w)
-            ws.append(w)
-        layers.append(ws)
+        layers.append([
+            fill(pl.QKVParallelLinear(hidden, hd, qh, kvh, **kw)),
+            fill(pl.RowParallelLinear(hidden, hidden, input_is_parallel=True, **kw)),
+            fill(pl.MergedColumnParallelLinear(hidden, [inter, inter], **kw)),
+            fill(pl.RowParallelLinear(inter, hidden, input_is_parallel=True, **kw)),
+        ])
+    for (name, K, N, _), layer in zip(shapes, layers[0]):
+        got = (layer.linear_weights["scales"].shape[0] * GROUP, layer.linear_weights["scales"].shape[1])
+        assert got == (K, N), (name, got, (K, N))
+    # inputs of the four GEMMs (attention and the activation between them are outside the path:
+    # fixed stand-in activations of the right per-rank shape)
     xs = {K: torch.randn((M, K), device=dev, generator=g).half() for (_, K, _, _) in shapes}
-    hidden = shapes[0][1]
     x_host = torch.randn((M, hidden)).half().pin_memory()
     y_host = torch.empty((M, hidden), dtype=torch.float16).pin_memory()
 
     def step(x_in):
         """All quantized linears of all layers; returns the last down_proj output."""
         out = None
-        for ws in layers:
-            for (name, K, N, row), w in zip(shapes, ws):
+        for lyr in layers:
+            for (name, K, N, row), layer in zip(shapes, lyr):
                 inp = x_in if K == hidden and not row else xs[K]
-                out = method.apply_weights(w, inp)
-                if row and world > 1:
-                    dist.all_reduce(out)
+                out, _ = layer(inp)          # row-parallel layers all-reduce inside
         return out
 
     stream = torch.cuda.Stream(device=dev)
@@ -320,7 +345,7 @@ def main():
                     "d2h_bytes_per_step": M * hidden * 2, "ms_per_step": ms_e2e / args.steps},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": f"w4a16_gemm_kernel<{pkg._lib.gemm_plan(M, shapes[0][1], shapes[0][2])['tok_tile']}>",
+                         "kernel": kernel_name(pkg, M, shapes[0][1], shapes[0][2]),
                          "alg_bytes_per_launch": alg_per_launch, "us_per_launch": us_per_launch},
         }
         if world == 1 and not args.no_cpu_baseline:

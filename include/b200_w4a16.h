@@ -106,6 +106,15 @@ int b200_w4a16_repack(const int32_t *src, int32_t *dst, int K, int N, int direct
 int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int *tok_tile,
                          int *split_k, int *grid, int *smem_bytes);
 
+/* Which kernel variant b200_w4a16_gemm launches for this problem: B200_VARIANT_DECODE
+ * (M <= 16 and G % 128 == 0: warp-level mma.sync with the dequantized registers as the A
+ * fragment, bandwidth bound) or B200_VARIANT_TCGEN05 (tcgen05 MMA with TMEM operands and
+ * accumulators).  Negative: -b200_status_t.  The reference picks between its GEMM kernel and
+ * dequantize + cuBLAS on `num_tokens >= 256`
+ * (vllm/model_executor/layers/quantization/awq.py:154). */
+enum { B200_VARIANT_TCGEN05 = 0, B200_VARIANT_DECODE = 1 };
+int b200_w4a16_gemm_variant(int M, int K, int N, int G);
+
 #ifdef __cplusplus
 }
 #endif

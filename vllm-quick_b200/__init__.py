@@ -7,6 +7,9 @@ with ``importlib.import_module("vllm-quick_b200")``.
 """
 from . import _lib, ops  # noqa: F401
 from .linear import LinearMethodBase, set_weight_attrs  # noqa: F401
+from . import parallel_linear, parallel_utils  # noqa: F401
+from .parallel_linear import (ColumnParallelLinear, MergedColumnParallelLinear,  # noqa: F401
+                              QKVParallelLinear, ReplicatedLinear, RowParallelLinear)
 from .quantization import (AWQConfig, AWQLinearMethod, QuantizationConfig, QuickConfig,  # noqa: F401
                            QuickLinearMethod, get_quantization_config)
 

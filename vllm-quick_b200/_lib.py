@@ -26,7 +26,7 @@ REPACK_AWQ_TO_B200, REPACK_B200_TO_AWQ = 0, 1
 EXPORTS = (
     "b200_w4a16_version", "b200_w4a16_strerror", "b200_w4a16_last_cuda_error",
     "b200_w4a16_repacked_words", "b200_w4a16_workspace_bytes", "b200_w4a16_gemm",
-    "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan",
+    "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan", "b200_w4a16_gemm_variant",
 )
 
 
@@ -76,6 +76,8 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_repack.argtypes = [vp, vp, i32, i32, i32, vp]
     L.b200_w4a16_gemm_plan.restype = i32
     L.b200_w4a16_gemm_plan.argtypes = [i32, i32, i32, i32, i32] + [ctypes.POINTER(i32)] * 4
+    L.b200_w4a16_gemm_variant.restype = i32
+    L.b200_w4a16_gemm_variant.argtypes = [i32, i32, i32, i32]
     _lib = L
     return L
 
@@ -98,5 +100,6 @@ def gemm_plan(M: int, K: int, N: int, G: int = 128, split_k_hint: int = 0) -> di
     check(lib().b200_w4a16_gemm_plan(M, K, N, G, split_k_hint, ctypes.byref(tok),
                                      ctypes.byref(split), ctypes.byref(grid),
                                      ctypes.byref(smem)), "gemm_plan")
+    variant = lib().b200_w4a16_gemm_variant(M, K, N, G)
     return {"tok_tile": tok.value, "split_k": split.value, "grid": grid.value,
-            "smem_bytes": smem.value}
+            "smem_bytes": smem.value, "variant": "decode" if variant == 1 else "tcgen05"}

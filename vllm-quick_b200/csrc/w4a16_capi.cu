@@ -70,7 +70,7 @@ bool use_pdl() {
 
 extern "C" {
 
-int b200_w4a16_version(void) { return 100; }
+int b200_w4a16_version(void) { return 101; }
 
 const char* b200_w4a16_strerror(int status) {
   switch (status) {
@@ -117,6 +117,14 @@ int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int* tok_
   if (grid) *grid = plan.ctas;
   if (smem_bytes) *smem_bytes = plan.smem_bytes;
   return B200_OK;
+}
+
+int b200_w4a16_gemm_variant(int M, int K, int N, int G) {
+  if (!gemm_shape_ok(M, K, N, G)) return -B200_ERR_BAD_SHAPE;
+  b200::GemmPlan plan;
+  if (b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, 0, sm_count_or_default(), &plan))
+    return -B200_ERR_BAD_SHAPE;
+  return plan.kind == b200::kKindDecode ? B200_VARIANT_DECODE : B200_VARIANT_TCGEN05;
 }
 
 int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
