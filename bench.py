@@ -277,7 +277,8 @@ def main():
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph, stream=stream):
             y_static = step(x_dev)
-        launches_per_step = n_layers * len(shapes)
+        launches_per_step = n_layers * len(shapes)          # GEMM launches (roofline denominator)
+        ar_launches = 2 * n_layers if (world > 1 and pu.custom_all_reduce.is_initialized()) else 0
 
         def barrier():
             torch.cuda.synchronize(dev)
@@ -339,7 +340,9 @@ def main():
             "vs_baseline": None, "dtype": "f16", "data": "synthetic",
             "config": workload_config(model, tp, M),
             "tokens_per_s": M / (ms_step * 1e-3),
-            "gpu_launches": launches_per_step * args.steps,
+            "gpu_launches": (launches_per_step + ar_launches) * args.steps,
+            "allreduce": None if world == 1 else (
+                "nvlink peer-memory kernel (b200_w4a16_allreduce)" if ar_launches else "nccl"),
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": M * hidden * 2,
                     "d2h_bytes_per_step": M * hidden * 2, "ms_per_step": ms_e2e / args.steps},
@@ -364,7 +367,16 @@ def main():
                           "PyTorch CPU dequantize + matmul (oracle/torch_cpu.py)"}
         print(json.dumps(line))
     if world > 1:
-        dist.destroy_process_group()
+        # Tear down without destroying communicators that captured graphs still reference
+        # (an NCCL communicator with live captured collectives can block in its destructor):
+        # drop the graph, drain the device, meet the other ranks, then leave the process.
+        sys.stdout.flush()
+        del graph
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        pu.custom_all_reduce.destroy_custom_all_reduce()
+        torch.cuda.synchronize(dev)
+        os._exit(0)
 
 
 if __name__ == "__main__":

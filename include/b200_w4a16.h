@@ -115,6 +115,37 @@ int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int *tok_
 enum { B200_VARIANT_TCGEN05 = 0, B200_VARIANT_DECODE = 1 };
 int b200_w4a16_gemm_variant(int M, int K, int N, int G);
 
+/* ---- NVLink peer-memory all-reduce for the row-parallel linears --------------------------
+ * Replaces: tensor_model_parallel_all_reduce after RowParallelLinear's GEMM
+ * (vllm/model_executor/layers/linear.py:541-542,
+ *  vllm/model_executor/parallel_utils/communication_op.py:17-41) for fp16 messages that fit a
+ * registered region; the reference's own peer-memory kernel is csrc/custom_all_reduce.cuh:214-232
+ * (init / registration: csrc/custom_all_reduce.cu:12-148), disabled in that version for
+ * world_size > 1 (vllm/config.py:403-410).  One process per GPU; every rank allocates one
+ * region, exports it, imports the peers' and passes the `world` base pointers (index = rank)
+ * to every call.  Larger messages go through NCCL in the Python layer. */
+
+/* Bytes of one rank's region for messages up to max_message_bytes. */
+size_t b200_w4a16_ar_region_bytes(size_t max_message_bytes);
+/* cudaMalloc + zero-fill a region on the current device / free it. */
+int b200_w4a16_ar_alloc(size_t bytes, void **dev_ptr);
+int b200_w4a16_ar_free(void *dev_ptr);
+/* CUDA IPC: 64-byte handle of a region from b200_w4a16_ar_alloc / map a peer's handle /
+ * unmap it. */
+int b200_w4a16_ar_export(const void *dev_ptr, void *handle64);
+int b200_w4a16_ar_import(const void *handle64, void **dev_ptr);
+int b200_w4a16_ar_unimport(void *dev_ptr);
+/* out[n_halfs] = sum over ranks of in[n_halfs] (fp16, fp32 accumulate, rank order: every rank
+ * gets bit-identical results).  `regions` is a HOST array of `world` device pointers (own
+ * region at index `rank`, peers' mappings elsewhere).  n_halfs % 8 == 0,
+ * 2 * n_halfs <= max_message_bytes, in/out 16-byte aligned, in != out allowed to alias
+ * nothing else.  Collective: every rank of the group calls it with the same n_halfs, in the
+ * same order.  CUDA-graph capturable.  `barrier` must be 1 (0 is the single-GPU emulation used
+ * by the tests: peers' slots are pre-filled and no cross-GPU wait happens). */
+int b200_w4a16_allreduce(void *const *regions, int rank, int world, const uint16_t *in,
+                         uint16_t *out, size_t n_halfs, size_t max_message_bytes, int barrier,
+                         b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -27,6 +27,9 @@ EXPORTS = (
     "b200_w4a16_version", "b200_w4a16_strerror", "b200_w4a16_last_cuda_error",
     "b200_w4a16_repacked_words", "b200_w4a16_workspace_bytes", "b200_w4a16_gemm",
     "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan", "b200_w4a16_gemm_variant",
+    "b200_w4a16_ar_region_bytes", "b200_w4a16_ar_alloc", "b200_w4a16_ar_free",
+    "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
+    "b200_w4a16_allreduce",
 )
 
 
@@ -76,6 +79,20 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_repack.argtypes = [vp, vp, i32, i32, i32, vp]
     L.b200_w4a16_gemm_plan.restype = i32
     L.b200_w4a16_gemm_plan.argtypes = [i32, i32, i32, i32, i32] + [ctypes.POINTER(i32)] * 4
+    L.b200_w4a16_ar_region_bytes.restype = sz
+    L.b200_w4a16_ar_region_bytes.argtypes = [sz]
+    L.b200_w4a16_ar_alloc.restype = i32
+    L.b200_w4a16_ar_alloc.argtypes = [sz, ctypes.POINTER(vp)]
+    L.b200_w4a16_ar_free.restype = i32
+    L.b200_w4a16_ar_free.argtypes = [vp]
+    L.b200_w4a16_ar_export.restype = i32
+    L.b200_w4a16_ar_export.argtypes = [vp, vp]
+    L.b200_w4a16_ar_import.restype = i32
+    L.b200_w4a16_ar_import.argtypes = [vp, ctypes.POINTER(vp)]
+    L.b200_w4a16_ar_unimport.restype = i32
+    L.b200_w4a16_ar_unimport.argtypes = [vp]
+    L.b200_w4a16_allreduce.restype = i32
+    L.b200_w4a16_allreduce.argtypes = [ctypes.POINTER(vp), i32, i32, vp, vp, sz, sz, i32, vp]
     L.b200_w4a16_gemm_variant.restype = i32
     L.b200_w4a16_gemm_variant.argtypes = [i32, i32, i32, i32]
     _lib = L

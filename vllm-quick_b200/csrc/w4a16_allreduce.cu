@@ -1,0 +1,174 @@
+// w4a16_allreduce.cu -- one-shot fp16 all-reduce over NVLink peer memory for the row-parallel
+// linears (o_proj, down_proj) of the W4A16 path.
+//
+// Replaces, for messages up to a few MiB inside one NVSwitch domain:
+//   tensor_model_parallel_all_reduce  vllm/model_executor/parallel_utils/communication_op.py:17-41
+//   and is the B200 counterpart of the reference's own (disabled for world_size > 1,
+//   vllm/config.py:403-410) one-stage kernel  csrc/custom_all_reduce.cuh:214-232, 144-202.
+//
+// Every rank owns one REGION (cudaMalloc'd, exported with CUDA IPC, mapped by all peers):
+//     [ flags  kArMaxBlocks x kArMaxRanks x u32 ][ per-block epoch counters ][ slot 0 ][ slot 1 ]
+// A call on rank r with grid B:
+//   1. block b copies its chunk set of `in` into slot (epoch & 1) of r's own region;
+//   2. block b publishes: one thread per peer p stores epoch into flags[b][r] of p's region
+//      (st.release.sys through NVLink) and spins (ld.acquire.sys) until flags[b][q] of its OWN
+//      region carries the epoch for every q -- peers' block b have then written exactly the
+//      chunk set this block is about to read;
+//   3. block b sums its chunks over all ranks in rank order with fp32 accumulation (every
+//      rank computes bit-identical results) and writes `out`.
+// Two data slots alternate by epoch, so a rank may run ahead into call e+1 while a peer still
+// reads call e; slot reuse at call e+2 is safe because every rank passed barrier e+1 only
+// after it finished reading call e.  The epoch lives in device memory (one counter per
+// block), so the launch is CUDA-graph capturable and replayable.  Nothing here allocates,
+// synchronises or touches NCCL.
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "w4a16_internal.h"
+
+namespace b200 {
+
+namespace {
+
+constexpr int kArThreads = 256;
+
+struct ArParams {
+  uint8_t* region[kArMaxRanks];   // peer-mapped base pointers, index = rank
+  const uint4* in;
+  uint4* out;
+  uint32_t nchunks;               // 16-byte chunks
+  uint32_t slot_bytes;
+  int rank, world;
+  int barrier;                    // 0 only in the single-GPU emulation test
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// Peer data changes between calls at the same address: never serve it from L1.
+__device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void add8(float (&acc)[8], uint4 v) {
+  const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __half22float2(h[i]);
+    acc[2 * i] += f.x;
+    acc[2 * i + 1] += f.y;
+  }
+}
+
+template <int WORLD>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_oneshot_kernel(const ArParams p) {
+  uint8_t* mine = p.region[p.rank];
+  uint32_t* my_flags = reinterpret_cast<uint32_t*>(mine) + blockIdx.x * kArMaxRanks;
+  uint32_t* my_epoch = reinterpret_cast<uint32_t*>(mine + kArFlagBytes) + blockIdx.x;
+  __shared__ uint32_t s_epoch;
+  // The input is the previous kernel's output (programmatic dependent launch aware).
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (threadIdx.x == 0) s_epoch = *my_epoch + 1;
+  __syncthreads();
+  const uint32_t epoch = s_epoch;
+  const uint32_t slot_off = kArHeaderBytes + (epoch & 1u) * p.slot_bytes;
+
+  // 1. stage this block's chunk set into the own slot
+  uint4* my_slot = reinterpret_cast<uint4*>(mine + slot_off);
+  for (uint32_t c = blockIdx.x * kArThreads + threadIdx.x; c < p.nchunks; c += gridDim.x * kArThreads)
+    my_slot[c] = p.in[c];
+  __threadfence_system();
+  __syncthreads();
+
+  // 2. cross-GPU barrier of block b
+  if (p.barrier) {
+    if (threadIdx.x < WORLD) {
+      const int q = threadIdx.x;
+      uint32_t* peer_flag = reinterpret_cast<uint32_t*>(p.region[q]) + blockIdx.x * kArMaxRanks + p.rank;
+      st_release_sys(peer_flag, epoch);
+      const long long t0 = clock64();
+      while (ld_acquire_sys(my_flags + q) != epoch) {
+        if (clock64() - t0 > 4000000000ll) {
+          printf("b200_w4a16: all-reduce barrier timeout rank %d block %d peer %d\n", p.rank,
+                 blockIdx.x, q);
+          __trap();
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *my_epoch = epoch;
+
+  // 3. reduce in rank order (identical on every rank), fp32 accumulate
+  for (uint32_t c = blockIdx.x * kArThreads + threadIdx.x; c < p.nchunks; c += gridDim.x * kArThreads) {
+    uint4 v[WORLD];
+#pragma unroll
+    for (int q = 0; q < WORLD; ++q)
+      v[q] = ld_volatile_v4(reinterpret_cast<const uint4*>(p.region[q] + slot_off) + c);
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int q = 0; q < WORLD; ++q) add8(acc, v[q]);
+    uint4 o;
+    __half2* oh = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(acc[2 * i], acc[2 * i + 1]);
+    p.out[c] = o;
+  }
+}
+
+template <int WORLD>
+int launch_ar(const ArParams& prm, int blocks, cudaStream_t stream) {
+  allreduce_oneshot_kernel<WORLD><<<blocks, kArThreads, 0, stream>>>(prm);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace
+
+size_t ar_region_bytes(size_t max_message_bytes) {
+  const size_t slot = (max_message_bytes + 255) / 256 * 256;
+  return kArHeaderBytes + 2 * slot;
+}
+
+int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* in, uint16_t* out,
+                     size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream) {
+  ArParams prm;
+  for (int q = 0; q < kArMaxRanks; ++q) prm.region[q] = q < world ? static_cast<uint8_t*>(regions[q]) : nullptr;
+  prm.in = reinterpret_cast<const uint4*>(in);
+  prm.out = reinterpret_cast<uint4*>(out);
+  prm.nchunks = (uint32_t)(n_halfs / 8);
+  prm.slot_bytes = (uint32_t)((max_message_bytes + 255) / 256 * 256);
+  prm.rank = rank;
+  prm.world = world;
+  prm.barrier = barrier;
+  int blocks = (int)((prm.nchunks + kArThreads - 1) / kArThreads);
+  if (blocks < 1) blocks = 1;
+  if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  switch (world) {
+    case 1: return launch_ar<1>(prm, blocks, stream);
+    case 2: return launch_ar<2>(prm, blocks, stream);
+    case 3: return launch_ar<3>(prm, blocks, stream);
+    case 4: return launch_ar<4>(prm, blocks, stream);
+    case 5: return launch_ar<5>(prm, blocks, stream);
+    case 6: return launch_ar<6>(prm, blocks, stream);
+    case 7: return launch_ar<7>(prm, blocks, stream);
+    case 8: return launch_ar<8>(prm, blocks, stream);
+    default: return (int)cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace b200

@@ -4,6 +4,7 @@
 // or throws.  There is no CPU path: without an sm_100 device every compute entry point
 // returns B200_ERR_NO_DEVICE.
 #include <stdlib.h>
+#include <string.h>
 
 #include "../../include/b200_w4a16.h"
 #include "w4a16_internal.h"
@@ -70,7 +71,7 @@ bool use_pdl() {
 
 extern "C" {
 
-int b200_w4a16_version(void) { return 101; }
+int b200_w4a16_version(void) { return 102; }
 
 const char* b200_w4a16_strerror(int status) {
   switch (status) {
@@ -208,6 +209,69 @@ int b200_w4a16_repack(const int32_t* src, int32_t* dst, int K, int N, int direct
   const DeviceInfo& dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_repack(src, dst, K, N, direction, reinterpret_cast<cudaStream_t>(stream));
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+size_t b200_w4a16_ar_region_bytes(size_t max_message_bytes) {
+  return b200::ar_region_bytes(max_message_bytes);
+}
+
+int b200_w4a16_ar_alloc(size_t bytes, void** dev_ptr) {
+  if (!dev_ptr || bytes == 0) return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  cudaError_t e = cudaMalloc(dev_ptr, bytes);
+  if (e != cudaSuccess) return cuda_fail((int)e);
+  e = cudaMemset(*dev_ptr, 0, bytes);
+  if (e != cudaSuccess) return cuda_fail((int)e);
+  e = cudaDeviceSynchronize();
+  return e == cudaSuccess ? B200_OK : cuda_fail((int)e);
+}
+
+int b200_w4a16_ar_free(void* dev_ptr) {
+  if (!dev_ptr) return B200_OK;
+  cudaError_t e = cudaFree(dev_ptr);
+  return e == cudaSuccess ? B200_OK : cuda_fail((int)e);
+}
+
+int b200_w4a16_ar_export(const void* dev_ptr, void* handle64) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (!dev_ptr || !handle64) return B200_ERR_BAD_ARG;
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, const_cast<void*>(dev_ptr));
+  if (e != cudaSuccess) return cuda_fail((int)e);
+  memcpy(handle64, &h, sizeof(h));
+  return B200_OK;
+}
+
+int b200_w4a16_ar_import(const void* handle64, void** dev_ptr) {
+  if (!handle64 || !dev_ptr) return B200_ERR_BAD_ARG;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  cudaError_t e = cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess);
+  return e == cudaSuccess ? B200_OK : cuda_fail((int)e);
+}
+
+int b200_w4a16_ar_unimport(void* dev_ptr) {
+  if (!dev_ptr) return B200_OK;
+  cudaError_t e = cudaIpcCloseMemHandle(dev_ptr);
+  return e == cudaSuccess ? B200_OK : cuda_fail((int)e);
+}
+
+int b200_w4a16_allreduce(void* const* regions, int rank, int world, const uint16_t* in,
+                         uint16_t* out, size_t n_halfs, size_t max_message_bytes, int barrier,
+                         b200_stream_t stream) {
+  if (world < 1 || world > b200::kArMaxRanks || rank < 0 || rank >= world) return B200_ERR_BAD_ARG;
+  if (n_halfs % 8 != 0 || n_halfs * 2 > max_message_bytes || n_halfs / 8 > 0xFFFFFFFFull)
+    return B200_ERR_BAD_SHAPE;
+  if (n_halfs == 0) return B200_OK;
+  if (!regions || !in || !out || !aligned16(in) || !aligned16(out)) return B200_ERR_BAD_ARG;
+  for (int q = 0; q < world; ++q)
+    if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_allreduce(regions, rank, world, in, out, n_halfs, max_message_bytes,
+                                 barrier, reinterpret_cast<cudaStream_t>(stream));
   return e == 0 ? B200_OK : cuda_fail(e);
 }
 

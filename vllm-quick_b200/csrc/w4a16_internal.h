@@ -48,6 +48,16 @@ int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* sca
                   const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
                   cudaStream_t stream);
 
+// NVLink peer-memory all-reduce (w4a16_allreduce.cu).  Region = header + two data slots.
+constexpr int kArMaxRanks = 8;
+constexpr int kArMaxBlocks = 64;
+constexpr int kArFlagBytes = kArMaxBlocks * kArMaxRanks * 4;   // flags[block][rank]
+constexpr int kArHeaderBytes = 4096;                          // flags + per-block epoch counters
+static_assert(kArFlagBytes + kArMaxBlocks * 4 <= kArHeaderBytes, "all-reduce header layout");
+size_t ar_region_bytes(size_t max_message_bytes);
+int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* in, uint16_t* out,
+                     size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream);
+
 // B200_TRACE builds: device buffer of 148 x 8 x 64 uint32 timestamps (nullptr = off).
 void set_trace_buffer(uint32_t* dev);
 uint32_t* trace_buffer();

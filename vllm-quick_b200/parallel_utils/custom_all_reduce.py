@@ -1,8 +1,114 @@
-"""NVLink peer-memory all-reduce (placeholder until the kernel lands): not initialised."""
-from typing import Optional
+"""NVLink peer-memory all-reduce for the row-parallel linears (Python side).
+
+Counterpart of the reference's vllm/model_executor/parallel_utils/custom_all_reduce.py:26-227
+(init / capture / CustomAllreduce) on top of ``b200_w4a16_allreduce`` (one-shot kernel,
+csrc/w4a16_allreduce.cu).  Differences that matter:
+
+* no buffer registration step at graph capture: inputs are staged into the rank's own
+  registered region by the kernel itself, so any tensor can be reduced, eagerly or inside a
+  CUDA graph, with the same call;
+* the cross-GPU epoch lives in device memory, so captured launches replay correctly;
+* one process per GPU under ``torchrun`` (the reference drives its workers through Ray).
+
+``init_custom_all_reduce`` is collective over the tensor-parallel group.  Messages that are
+not fp16, not a multiple of 16 bytes or larger than the registered size fall through to the
+group's ``torch.distributed`` backend (``communication_op.tensor_model_parallel_all_reduce``).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
 
 import torch
+import torch.distributed as dist
+
+from .. import _lib
+from .parallel_state import (get_tensor_model_parallel_group, get_tensor_model_parallel_rank,
+                             get_tensor_model_parallel_world_size)
+
+_MAX_WORLD = 8
+_handle: Optional["CustomAllreduce"] = None
+
+
+class CustomAllreduce:
+    """One registered region per rank, mapped by every peer of the tensor-parallel group."""
+
+    def __init__(self, max_bytes: int) -> None:
+        L = _lib.lib()
+        self.rank = get_tensor_model_parallel_rank()
+        self.world = get_tensor_model_parallel_world_size()
+        if not 2 <= self.world <= _MAX_WORLD:
+            raise ValueError(f"custom all-reduce supports 2..{_MAX_WORLD} ranks, got {self.world}")
+        self.max_bytes = (int(max_bytes) + 255) // 256 * 256
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        region_bytes = L.b200_w4a16_ar_region_bytes(self.max_bytes)
+        own = ctypes.c_void_p()
+        _lib.check(L.b200_w4a16_ar_alloc(region_bytes, ctypes.byref(own)), "all-reduce region")
+        self._own = own.value
+        handle = ctypes.create_string_buffer(64)
+        _lib.check(L.b200_w4a16_ar_export(self._own, handle), "all-reduce export")
+        handles: List[Optional[bytes]] = [None] * self.world
+        dist.all_gather_object(handles, handle.raw, group=get_tensor_model_parallel_group())
+        self._imported: List[int] = []
+        self._regions = (ctypes.c_void_p * self.world)()
+        for q, raw in enumerate(handles):
+            if q == self.rank:
+                self._regions[q] = self._own
+                continue
+            peer = ctypes.c_void_p()
+            _lib.check(L.b200_w4a16_ar_import(ctypes.create_string_buffer(raw, 64), ctypes.byref(peer)),
+                       f"all-reduce import of rank {q}")
+            self._regions[q] = peer.value
+            self._imported.append(peer.value)
+        dist.barrier(group=get_tensor_model_parallel_group())   # every region is mapped everywhere
+
+    def should(self, t: torch.Tensor) -> bool:
+        nbytes = t.numel() * t.element_size()
+        return (t.is_cuda and t.dtype == torch.float16 and t.is_contiguous()
+                and nbytes % 16 == 0 and 0 < nbytes <= self.max_bytes and t.data_ptr() % 16 == 0)
+
+    def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
+        out = torch.empty_like(t)
+        st = _lib.lib().b200_w4a16_allreduce(
+            self._regions, self.rank, self.world, t.data_ptr(), out.data_ptr(), t.numel(),
+            self.max_bytes, 1, torch.cuda.current_stream(t.device).cuda_stream)
+        _lib.check(st, "custom all-reduce")
+        return out
+
+    def close(self) -> None:
+        L = _lib.lib()
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=get_tensor_model_parallel_group())   # nobody still reads our region
+        for ptr in self._imported:
+            L.b200_w4a16_ar_unimport(ptr)
+        self._imported = []
+        if self._own:
+            L.b200_w4a16_ar_free(self._own)
+            self._own = None
+
+
+def init_custom_all_reduce(max_bytes: int = 8 << 20) -> None:
+    """Collective over the TP group: allocate, exchange and map the regions (default 8 MiB
+    messages, the reference's limit, custom_all_reduce.py:143)."""
+    global _handle
+    if _handle is not None or get_tensor_model_parallel_world_size() == 1:
+        return
+    _handle = CustomAllreduce(max_bytes)
+
+
+def is_initialized() -> bool:
+    return _handle is not None
+
+
+def destroy_custom_all_reduce() -> None:
+    global _handle
+    if _handle is not None:
+        _handle.close()
+        _handle = None
 
 
 def maybe_all_reduce(input_: torch.Tensor) -> Optional[torch.Tensor]:
-    return None
+    """The reduced tensor if the peer-memory kernel took the message, else ``None``."""
+    if _handle is None or not _handle.should(input_):
+        return None
+    return _handle.all_reduce(input_)
