@@ -193,6 +193,8 @@ def main():
     ap.add_argument("--model", default=None, help="llama2-7b | llama2-13b | llama2-70b")
     ap.add_argument("--layers", type=int, default=None, help="override layer count (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--unfused-allreduce", action="store_true",
+                    help="row-parallel GEMM and the peer-memory all-reduce as two kernels")
     ap.add_argument("--nccl-allreduce", action="store_true",
                     help="row-parallel all-reduce through NCCL instead of the NVLink peer-memory kernel")
     args = ap.parse_args()
@@ -226,7 +228,8 @@ def main():
     if world > 1:
         pu.initialize_model_parallel(world)
         if not args.nccl_allreduce:
-            pu.custom_all_reduce.init_custom_all_reduce(max_bytes=M * hidden * 2)
+            pu.custom_all_reduce.init_custom_all_reduce(
+                max_bytes=M * hidden * 2, fused_out_features=0 if args.unfused_allreduce else hidden)
     method = pkg.QuickConfig(4, GROUP, True).get_linear_method()
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
 
@@ -278,7 +281,9 @@ def main():
         with torch.cuda.graph(graph, stream=stream):
             y_static = step(x_dev)
         launches_per_step = n_layers * len(shapes)          # GEMM launches (roofline denominator)
-        ar_launches = 2 * n_layers if (world > 1 and pu.custom_all_reduce.is_initialized()) else 0
+        fused_ar = world > 1 and pu.custom_all_reduce.fused_handle(M, hidden, GROUP) is not None
+        ar_launches = 2 * n_layers if (world > 1 and pu.custom_all_reduce.is_initialized()
+                                       and not fused_ar) else 0
 
         def barrier():
             torch.cuda.synchronize(dev)
@@ -342,6 +347,7 @@ def main():
             "tokens_per_s": M / (ms_step * 1e-3),
             "gpu_launches": (launches_per_step + ar_launches) * args.steps,
             "allreduce": None if world == 1 else (
+                "fused into the row-parallel GEMM (b200_w4a16_gemm_allreduce)" if fused_ar else
                 "nvlink peer-memory kernel (b200_w4a16_allreduce)" if ar_launches else "nccl"),
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": M * hidden * 2,

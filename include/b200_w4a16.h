@@ -125,8 +125,10 @@ int b200_w4a16_gemm_variant(int M, int K, int N, int G);
  * region, exports it, imports the peers' and passes the `world` base pointers (index = rank)
  * to every call.  Larger messages go through NCCL in the Python layer. */
 
-/* Bytes of one rank's region for messages up to max_message_bytes. */
-size_t b200_w4a16_ar_region_bytes(size_t max_message_bytes);
+/* Bytes of one rank's region: all-reduce messages up to max_message_bytes, plus (when
+ * fused_out_features > 0) the slots of the fused row-parallel GEMM + all-reduce for outputs of
+ * up to fused_out_features channels x 16 tokens from `world` ranks.  0 on bad arguments. */
+size_t b200_w4a16_ar_region_bytes(size_t max_message_bytes, int world, int fused_out_features);
 /* cudaMalloc + zero-fill a region on the current device / free it. */
 int b200_w4a16_ar_alloc(size_t bytes, void **dev_ptr);
 int b200_w4a16_ar_free(void *dev_ptr);
@@ -145,6 +147,25 @@ int b200_w4a16_ar_unimport(void *dev_ptr);
 int b200_w4a16_allreduce(void *const *regions, int rank, int world, const uint16_t *in,
                          uint16_t *out, size_t n_halfs, size_t max_message_bytes, int barrier,
                          b200_stream_t stream);
+
+/* Row-parallel GEMM fused with its all-reduce, decode batches (M <= 16, G % 128 == 0):
+ *   y[M,N] = sum over ranks of  x_rank[M,K_rank] . dequant(qweight_rank, ...)      (fp16 out)
+ * ONE kernel per rank: a channel tile that finishes its K reduction is rounded to fp16 and
+ * pushed over NVLink into every rank's region (peer stores), its arrival is flagged per tile,
+ * and each rank sums the arrived copies in rank order with fp32 accumulation -- so the transfer
+ * of early tiles overlaps the weight stream of later ones, and the result is bit-identical on
+ * every rank and to b200_w4a16_gemm followed by b200_w4a16_allreduce.
+ * Replaces: RowParallelLinear.forward's apply_weights + tensor_model_parallel_all_reduce pair
+ * (vllm/model_executor/layers/linear.py:538-542).  qweight is in the B200 layout.  `regions`,
+ * `max_message_bytes`, `fused_out_features` as given to b200_w4a16_ar_region_bytes when the
+ * regions were sized (N <= fused_out_features).  Collective: every rank calls it for the same
+ * (M, N), in the same order.  CUDA-graph capturable. */
+int b200_w4a16_gemm_allreduce(const uint16_t *x, const int32_t *qweight, const uint16_t *scales,
+                              const int32_t *qzeros, uint16_t *y, int M, int K, int N, int G,
+                              int split_k_hint, void *workspace, size_t workspace_bytes,
+                              void *const *regions, int rank, int world,
+                              size_t max_message_bytes, int fused_out_features,
+                              b200_stream_t stream);
 
 #ifdef __cplusplus
 }

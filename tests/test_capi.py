@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol(pkg, cuda_lib):
 
 
 def test_version_and_strerror(cuda_lib):
-    assert cuda_lib.b200_w4a16_version() == 102
+    assert cuda_lib.b200_w4a16_version() == 103
     assert cuda_lib.b200_w4a16_strerror(0) == b"ok"
     assert b"shape" in cuda_lib.b200_w4a16_strerror(1)
     assert b"no sm_100" in cuda_lib.b200_w4a16_strerror(5)

@@ -11,6 +11,7 @@ import os
 import socket
 import sys
 
+import numpy as np
 import pytest
 import torch
 
@@ -19,7 +20,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 pytestmark = pytest.mark.gpu
-HEADER = 4096
+HEADER = 16384
 
 
 def _expected(parts):
@@ -34,7 +35,8 @@ def test_single_gpu_emulation_matches_rank_order_sum(pkg, cuda_lib, world, n):
     L = cuda_lib
     max_bytes = 2 * 16 * 8192
     slot = (max_bytes + 255) // 256 * 256
-    assert L.b200_w4a16_ar_region_bytes(max_bytes) == HEADER + 2 * slot
+    assert L.b200_w4a16_ar_region_bytes(max_bytes, world, 0) == HEADER + 2 * slot
+    assert L.b200_w4a16_ar_region_bytes(max_bytes, world, 8192) == HEADER + 2 * slot + 2 * world * 8192 * 32
     regions = [torch.zeros(HEADER + 2 * slot, dtype=torch.uint8, device="cuda") for _ in range(world)]
     ptrs = (ctypes.c_void_p * world)(*[r.data_ptr() for r in regions])
     g = torch.Generator(device="cuda").manual_seed(n + world)
@@ -49,6 +51,70 @@ def test_single_gpu_emulation_matches_rank_order_sum(pkg, cuda_lib, world, n):
         assert st == 0
         torch.cuda.synchronize()
         assert torch.equal(out, _expected(parts)), call
+
+
+def _to_fragment_order(Y, MT):
+    """[16, N] fp16 -> the fused path's slot layout: per 128-channel tile, MT x 128 threads x
+    uint4; thread ct = 32 w + 4 g + t holds tokens 8i+2t, 8i+2t+1 of channels
+    32 w + 16 b + 8 r + g (word 2 b + r), see push_tile in csrc/w4a16_decode.cu."""
+    N = Y.shape[1]
+    out = np.zeros((N // 128, MT, 128, 4, 2), dtype=np.float16)
+    for w in range(4):
+        for g in range(8):
+            for t in range(4):
+                ct = 32 * w + 4 * g + t
+                for i in range(MT):
+                    for b in range(2):
+                        for r in range(2):
+                            ch = 32 * w + 16 * b + 8 * r + g
+                            out[:, i, ct, 2 * b + r, 0] = Y[8 * i + 2 * t, ch::128]
+                            out[:, i, ct, 2 * b + r, 1] = Y[8 * i + 2 * t + 1, ch::128]
+    return out
+
+
+@pytest.mark.parametrize("M,K,N", [(16, 1024, 512), (5, 512, 256), (16, 4096, 4096)])
+def test_fused_gemm_allreduce_single_gpu_emulation(pkg, oracle, cuda_lib, M, K, N):
+    """Rank 0 of a world of two, both regions on cuda:0: rank 1's fp16 tiles and arrival flags
+    are pre-placed, so the kernel never waits on another launch.  Result must equal
+    fp16(float(fp16(y0)) + float(y1)) with y0 the unfused GEMM of the same inputs."""
+    from gpu_util import to_dev
+    L = cuda_lib
+    world, G, max_bytes, fused_n = 2, 128, 16 * 8192 * 2, 8192
+    region_bytes = L.b200_w4a16_ar_region_bytes(max_bytes, world, fused_n)
+    regions = [torch.zeros(region_bytes, dtype=torch.uint8, device="cuda") for _ in range(world)]
+    ptrs = (ctypes.c_void_p * world)(*[r.data_ptr() for r in regions])
+    x, qw, s, qz = oracle.make_inputs(M, K, N, G, seed=N + M)
+    dx, ds, dqz = to_dev(x), to_dev(s), to_dev(qz)
+    r = pkg.ops.quick_repack(to_dev(qw))
+    y0 = pkg.ops.quick_gemm(dx, r, ds, dqz, 8)
+    MT = 1 if M <= 8 else 2
+    data_off = HEADER + 2 * ((max_bytes + 255) // 256 * 256)
+    slot = fused_n * 32
+    ws = torch.zeros(L.b200_w4a16_workspace_bytes(M, K, N, 1), dtype=torch.uint8, device="cuda")
+    rng = np.random.default_rng(M)
+    for epoch in (1, 2, 3):
+        Y1 = np.zeros((16, N), dtype=np.float16)
+        Y1[:M] = rng.standard_normal((M, N)).astype(np.float16)
+        par = epoch & 1
+        frag = torch.from_numpy(_to_fragment_order(Y1, MT).view(np.uint8).reshape(-1)).cuda()
+        off = data_off + par * world * slot + 1 * slot
+        regions[0][off: off + frag.numel()] = frag
+        flags = regions[0][4096: 4096 + 2 * 128 * 8 * 4].view(torch.int32).view(2, 128, 8)
+        flags[par, : N // 128, 1] = epoch
+        y = torch.empty((M, N), dtype=torch.float16, device="cuda")
+        st = L.b200_w4a16_gemm_allreduce(dx.data_ptr(), r.data_ptr(), ds.data_ptr(), dqz.data_ptr(),
+                                         y.data_ptr(), M, K, N, G, 0, ws.data_ptr(), ws.numel(), ptrs,
+                                         0, world, max_bytes, fused_n,
+                                         torch.cuda.current_stream().cuda_stream)
+        assert st == 0
+        torch.cuda.synchronize()
+        want = (y0.float() + torch.from_numpy(Y1[:M].astype(np.float32)).cuda()).half()
+        assert torch.equal(y, want), epoch
+        # the tile copies it pushed to the "peer" are its own fp16 GEMM output
+        peer = regions[1][data_off + par * world * slot: data_off + par * world * slot + (N // 128) * MT * 2048]
+        mine = _to_fragment_order(np.pad(y0.cpu().numpy(), ((0, 16 - M), (0, 0))), MT).view(np.uint8).reshape(-1)
+        assert np.array_equal(peer.cpu().numpy(), mine)
+        assert int(regions[0][3072:3076].view(torch.int32).item()) == epoch     # call closed
 
 
 def test_allreduce_rejects_bad_arguments(pkg, cuda_lib):
@@ -81,7 +147,7 @@ def _rank_main(rank, world, port, q):
         pkg = importlib.import_module("vllm-quick_b200")
         pu = pkg.parallel_utils
         pu.initialize_model_parallel(world)
-        pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2)
+        pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2, fused_out_features=8192)
         g = torch.Generator(device=dev).manual_seed(100 + rank)
         for shape in [(1, 8192), (16, 8192), (256, 8192), (3, 4096)]:
             x = torch.randn(shape, device=dev, generator=g).half()
@@ -93,6 +159,43 @@ def _rank_main(rank, world, port, q):
             gathered = [torch.empty_like(y) for _ in range(world)]
             dist.all_gather(gathered, y)
             assert all(torch.equal(gathered[0], t) for t in gathered)   # bit-identical on every rank
+        # row-parallel layer: the fused GEMM + all-reduce kernel vs GEMM, then all-reduce kernel
+        K, N = 2048 * world, 4096
+        method = pkg.QuickConfig(4, 128, True).get_linear_method()
+        row = pkg.RowParallelLinear(K, N, bias=False, input_is_parallel=True, linear_method=method,
+                                    params_dtype=torch.float16).to(dev)
+        gw = torch.Generator(device=dev).manual_seed(7 + rank)
+        w = row.linear_weights
+        w["qweight"].data = torch.randint(-2**31, 2**31 - 1, tuple(w["qweight"].shape), dtype=torch.int32, device=dev, generator=gw)
+        w["qzeros"].data = torch.randint(-2**31, 2**31 - 1, tuple(w["qzeros"].shape), dtype=torch.int32, device=dev, generator=gw)
+        w["scales"].data = (torch.rand(tuple(w["scales"].shape), device=dev, generator=gw) * 0.019 + 0.001).half()
+        for Mtok in (1, 8, 16):
+            xin = torch.randn(Mtok, K // world, device=dev, generator=gw).half()
+            assert pu.custom_all_reduce.fused_handle(Mtok, N, 128) is not None
+            fused, _ = row(xin)
+            two_step = pu.tensor_model_parallel_all_reduce(method.apply_weights(w, xin))
+            assert torch.equal(fused, two_step), Mtok
+            ref = method.apply_weights(w, xin).float()
+            dist.all_reduce(ref)
+            assert torch.allclose(fused.float(), ref, rtol=2e-3, atol=3e-2)
+        xin = torch.randn(64, K // world, device=dev, generator=gw).half()       # M > 16: two kernels
+        assert pu.custom_all_reduce.fused_handle(64, N, 128) is None
+        out64, _ = row(xin)
+        assert torch.equal(out64, pu.tensor_model_parallel_all_reduce(method.apply_weights(w, xin)))
+        # fused path under CUDA-graph replay
+        xin = torch.randn(16, K // world, device=dev, generator=gw).half()
+        st2 = torch.cuda.Stream(device=dev)
+        with torch.cuda.stream(st2):
+            eager, _ = row(xin)
+            st2.synchronize()
+            g2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g2, stream=st2):
+                o1, _ = row(xin)
+                o2, _ = row(xin)
+            for _ in range(3):
+                g2.replay()
+            st2.synchronize()
+            assert torch.equal(o1, eager) and torch.equal(o2, eager)
         big = torch.randn(2048, 8192, device=dev).half()            # above the registered size: NCCL
         assert pu.tensor_model_parallel_all_reduce(big).data_ptr() == big.data_ptr()
         # CUDA-graph capture + replay with fresh inputs

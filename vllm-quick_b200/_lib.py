@@ -29,7 +29,7 @@ EXPORTS = (
     "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan", "b200_w4a16_gemm_variant",
     "b200_w4a16_ar_region_bytes", "b200_w4a16_ar_alloc", "b200_w4a16_ar_free",
     "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
-    "b200_w4a16_allreduce",
+    "b200_w4a16_allreduce", "b200_w4a16_gemm_allreduce",
 )
 
 
@@ -80,7 +80,10 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_gemm_plan.restype = i32
     L.b200_w4a16_gemm_plan.argtypes = [i32, i32, i32, i32, i32] + [ctypes.POINTER(i32)] * 4
     L.b200_w4a16_ar_region_bytes.restype = sz
-    L.b200_w4a16_ar_region_bytes.argtypes = [sz]
+    L.b200_w4a16_ar_region_bytes.argtypes = [sz, i32, i32]
+    L.b200_w4a16_gemm_allreduce.restype = i32
+    L.b200_w4a16_gemm_allreduce.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, sz,
+                                            ctypes.POINTER(vp), i32, i32, sz, i32, vp]
     L.b200_w4a16_ar_alloc.restype = i32
     L.b200_w4a16_ar_alloc.argtypes = [sz, ctypes.POINTER(vp)]
     L.b200_w4a16_ar_free.restype = i32

@@ -59,6 +59,11 @@ bool gemm_shape_ok(int M, int K, int N, int G) {
   return true;
 }
 
+// one rank's fp16 copy of a fused GEMM output: 16 tokens x N, N rounded up to whole tiles
+size_t fused_slot_bytes(int out_features) {
+  return (size_t)((out_features + b200::kTileN - 1) / b200::kTileN) * b200::kTileN * 32;
+}
+
 bool use_pdl() {
   static const bool on = [] {
     const char* e = getenv("B200_W4A16_NO_PDL");
@@ -71,7 +76,7 @@ bool use_pdl() {
 
 extern "C" {
 
-int b200_w4a16_version(void) { return 102; }
+int b200_w4a16_version(void) { return 103; }
 
 const char* b200_w4a16_strerror(int status) {
   switch (status) {
@@ -212,8 +217,51 @@ int b200_w4a16_repack(const int32_t* src, int32_t* dst, int K, int N, int direct
   return e == 0 ? B200_OK : cuda_fail(e);
 }
 
-size_t b200_w4a16_ar_region_bytes(size_t max_message_bytes) {
-  return b200::ar_region_bytes(max_message_bytes);
+size_t b200_w4a16_ar_region_bytes(size_t max_message_bytes, int world, int fused_out_features) {
+  if (world < 1 || world > b200::kArMaxRanks || fused_out_features < 0) return 0;
+  return b200::ar_region_bytes(max_message_bytes) +
+         2 * (size_t)world * fused_slot_bytes(fused_out_features);
+}
+
+int b200_w4a16_gemm_allreduce(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
+                              const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
+                              int split_k_hint, void* workspace, size_t workspace_bytes,
+                              void* const* regions, int rank, int world, size_t max_message_bytes,
+                              int fused_out_features, b200_stream_t stream) {
+  if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
+  if (M > b200::kDecodeMaxTokens || G % b200::kTileK != 0 || N > fused_out_features ||
+      (N + b200::kTileN - 1) / b200::kTileN > b200::kArMaxTiles)
+    return B200_ERR_BAD_SHAPE;
+  if (world < 2 || world > b200::kArMaxRanks || rank < 0 || rank >= world) return B200_ERR_BAD_ARG;
+  if (M == 0) return B200_OK;
+  if (!x || !qweight || !scales || !qzeros || !y || !regions) return B200_ERR_BAD_ARG;
+  if (!aligned16(x) || !aligned16(qweight) || !aligned16(scales) || !aligned16(qzeros) || !aligned16(y))
+    return B200_ERR_BAD_ARG;
+  for (int q = 0; q < world; ++q)
+    if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  b200::GemmPlan plan;
+  if (b200::make_gemm_plan(M, K, N, G, split_k_hint, sm_count_or_default(), &plan)) return B200_ERR_BAD_SHAPE;
+  if (plan.kind != b200::kKindDecode) return B200_ERR_BAD_SHAPE;   // pinned to the tcgen05 variant
+  const size_t part_bytes = align_up(plan.ws_partial_bytes, 256);
+  if (!workspace || workspace_bytes < kCounterBytes + part_bytes || !aligned16(workspace))
+    return B200_ERR_WORKSPACE;
+  if (plan.ws_counter_bytes > kCounterBytes) return B200_ERR_WORKSPACE;
+  b200::FusedArParams ar;
+  for (int q = 0; q < b200::kArMaxRanks; ++q)
+    ar.region[q] = q < world ? static_cast<uint8_t*>(regions[q]) : nullptr;
+  ar.rank = rank;
+  ar.world = world;
+  ar.ctr_off = b200::kArFusedCtrOff;
+  ar.flag_off = b200::kArFusedFlagOff;
+  ar.data_off = (uint32_t)b200::ar_region_bytes(max_message_bytes);
+  ar.slot_bytes = (uint32_t)fused_slot_bytes(fused_out_features);
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  int e = b200::launch_decode(x, qweight, scales, qzeros, y, M, K, N, G, plan, ws + kCounterBytes,
+                              reinterpret_cast<int*>(ws), use_pdl(),
+                              reinterpret_cast<cudaStream_t>(stream), &ar);
+  return e == 0 ? B200_OK : cuda_fail(e);
 }
 
 int b200_w4a16_ar_alloc(size_t bytes, void** dev_ptr) {

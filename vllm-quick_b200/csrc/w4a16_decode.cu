@@ -29,6 +29,7 @@
 #include "w4a16_streamk.cuh"
 
 #include <stdlib.h>
+#include <string.h>
 
 namespace b200 {
 
@@ -83,6 +84,9 @@ struct DecodeParams {
   int Gdiv;     // K blocks per quantization group (G / 128)
   int flags;
   uint32_t* trace;  // B200_TRACE builds only: 16 globaltimer stamps per CTA
+  // Row-parallel fusion (ar.world > 1): finished tiles are pushed to every rank's region and
+  // reduced there; y then holds the all-reduced result (see the file header).
+  FusedArParams ar;
 };
 
 #ifdef B200_TRACE
@@ -112,6 +116,25 @@ __device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, uint3
 }
 __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void st_release_sys_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_volatile_u4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t pack_half2(float a, float b) {
+  const __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&h);
 }
 
 // D (+)= A[16x16, row] . B[16x8, col], fp16 operands, fp32 accumulate.
@@ -262,6 +285,43 @@ w4a16_decode_kernel(const DecodeParams p) {
         }
       }
     };
+    // ---- row-parallel fusion: a finished tile goes to every rank's region instead of y
+    const bool fused = p.ar.world > 1;
+    uint32_t epoch = 0, ar_slot = 0;
+    if (fused && grp == 0) {
+      // previous fused launch has fully completed (griddepcontrol.wait above): its bump is visible
+      epoch = *reinterpret_cast<volatile uint32_t*>(p.ar.region[p.ar.rank] + p.ar.ctr_off) + 1;
+      ar_slot = p.ar.data_off + (epoch & 1u) * (uint32_t)p.ar.world * p.ar.slot_bytes;
+    }
+    // tile nt of source rank r, slot layout [nt][2 MT quarters][128 threads] x 8 bytes... kept
+    // thread-private: thread ct owns MT uint4 (tokens 8i+2t, +1 of four channels) per tile
+    auto push_tile = [&](int nt, const float (&v)[2][MT][4]) {
+      uint4 frag[MT];
+#pragma unroll
+      for (int i = 0; i < MT; ++i)
+        frag[i] = make_uint4(pack_half2(v[0][i][0], v[0][i][1]), pack_half2(v[0][i][2], v[0][i][3]),
+                             pack_half2(v[1][i][0], v[1][i][1]), pack_half2(v[1][i][2], v[1][i][3]));
+      const uint32_t off = ar_slot + (uint32_t)p.ar.rank * p.ar.slot_bytes +
+                           ((uint32_t)nt * MT * kGroupThreads + ct) * 16u;
+#pragma unroll
+      for (int q = 0; q < kArMaxRanks; ++q) {
+        if (q < p.ar.world) {
+          uint4* dst = reinterpret_cast<uint4*>(p.ar.region[q] + off);
+#pragma unroll
+          for (int i = 0; i < MT; ++i) dst[i * kGroupThreads] = frag[i];
+        }
+      }
+      __threadfence_system();
+      named_bar_sync(1, kGroupThreads);                       // the whole tile is on its way
+      if (ct < p.ar.world) {
+        uint32_t* flag = reinterpret_cast<uint32_t*>(p.ar.region[ct] + p.ar.flag_off) +
+                         (((epoch & 1u) * kArMaxTiles + nt) * kArMaxRanks + p.ar.rank);
+        st_release_sys_u32(flag, epoch);
+      }
+    };
+    auto emit_tile = [&](int nt, const float (&v)[2][MT][4]) {
+      if (fused) push_tile(nt, v); else write_y(nt, v);
+    };
     int base = 0;                                             // walk index of the segment's first tile
     for (int idx = 0; idx < walk.nseg; ++idx) {
       int t0, n;
@@ -371,7 +431,7 @@ w4a16_decode_kernel(const DecodeParams p) {
       // ---- group 0: a whole tile goes straight to y; a partial one is published as fp32 and
       // finished later by the CTA that owns the tile's first K block (stream-K fix-up)
       if (n == p.KB) {
-        write_y(nt, tot);
+        emit_tile(nt, tot);
       } else {
         const int slot = idx == 0 ? 0 : 1;
         float4* part = reinterpret_cast<float4*>(p.partials) +
@@ -455,7 +515,65 @@ w4a16_decode_kernel(const DecodeParams p) {
             }
         }
       }
-      write_y(own_nt, tot);
+      emit_tile(own_nt, tot);
+    }
+
+    // ---- fused all-reduce: CTA b reduces channel tiles b, b + P, ... once every rank's copy
+    // has landed in OUR region (local reads), rank order, fp32 accumulate -> bit-identical on
+    // every rank and identical to GEMM-then-all-reduce of fp16 outputs.
+    if (fused && grp == 0) {
+      uint8_t* mine = p.ar.region[p.ar.rank];
+      for (int nt = blockIdx.x; nt < p.NT; nt += gridDim.x) {
+        if (ct < p.ar.world) {
+          const uint32_t* flag = reinterpret_cast<const uint32_t*>(mine + p.ar.flag_off) +
+                                 (((epoch & 1u) * kArMaxTiles + nt) * kArMaxRanks + ct);
+          const long long t0 = clock64();
+          while (ld_acquire_sys_u32(flag) != epoch) {
+            if (clock64() - t0 > B200_WATCHDOG_CYCLES) {
+              printf("b200_w4a16: fused all-reduce timeout rank %d tile %d peer %d\n", p.ar.rank, nt, ct);
+              __trap();
+            }
+          }
+        }
+        named_bar_sync(1, kGroupThreads);
+        float sum[2][MT][4];
+#pragma unroll
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+          for (int i = 0; i < MT; ++i)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) sum[b][i][e] = 0.f;
+        const uint32_t off = ar_slot + ((uint32_t)nt * MT * kGroupThreads + ct) * 16u;
+#pragma unroll
+        for (int q = 0; q < kArMaxRanks; ++q) {
+          if (q < p.ar.world) {
+            const uint4* src = reinterpret_cast<const uint4*>(mine + off + (uint32_t)q * p.ar.slot_bytes);
+#pragma unroll
+            for (int i = 0; i < MT; ++i) {
+              const uint4 f = ld_volatile_u4(src + i * kGroupThreads);
+              const uint32_t w[4] = {f.x, f.y, f.z, f.w};
+#pragma unroll
+              for (int h = 0; h < 4; ++h) {
+                const float2 g2 = __half22float2(*reinterpret_cast<const __half2*>(&w[h]));
+                sum[h >> 1][i][(h & 1) * 2] += g2.x;
+                sum[h >> 1][i][(h & 1) * 2 + 1] += g2.y;
+              }
+            }
+          }
+        }
+        write_y(nt, sum);
+      }
+      // the last CTA to get here closes the call: bump the epoch for the next fused launch
+      named_bar_sync(1, kGroupThreads);
+      if (ct == 0) {
+        uint32_t* ctr = reinterpret_cast<uint32_t*>(mine + p.ar.ctr_off);
+        __threadfence();
+        if (atomicAdd(ctr + 1, 1u) == gridDim.x - 1) {
+          ctr[1] = 0;
+          ctr[0] = epoch;
+          __threadfence();
+        }
+      }
     }
     if (grp == 0 && ct == 0) TD(7);
   }
@@ -507,7 +625,7 @@ void fill_decode_plan(int M, GemmPlan* plan) {
 int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                   const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
                   const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
-                  cudaStream_t stream) {
+                  cudaStream_t stream, const FusedArParams* ar) {
   DecodeParams prm;
   prm.qw = reinterpret_cast<const uint32_t*>(qw_b200);
   prm.x = x;
@@ -523,6 +641,12 @@ int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* sca
   prm.Gdiv = G / kTileK;
   prm.flags = decode_flags();
   prm.trace = trace_buffer();
+  if (ar) {
+    prm.ar = *ar;
+  } else {
+    memset(&prm.ar, 0, sizeof(prm.ar));
+    prm.ar.world = 1;
+  }
   return plan.tok_tile <= 8 ? launch_decode_impl<1>(prm, pdl, stream)
                             : launch_decode_impl<2>(prm, pdl, stream);
 }

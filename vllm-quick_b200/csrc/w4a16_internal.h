@@ -41,19 +41,37 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
                 const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
                 cudaStream_t stream);
 
+// Row-parallel fusion of the decode kernel with the all-reduce (w4a16_decode.cu): where in the
+// ranks' peer-mapped regions the fused path keeps its epoch counter, per-tile flags and slots.
+constexpr int kArMaxRanks = 8;
+constexpr int kArMaxTiles = 128;       // channel tiles of a fused GEMM: N <= 16384
+struct FusedArParams {
+  uint8_t* region[kArMaxRanks];        // index = rank; own region at [rank]
+  int rank, world;                     // world <= 1: not fused
+  uint32_t ctr_off;                    // two u32: epoch of the last fused call, CTA done counter
+  uint32_t flag_off;                   // flags[2 parities][kArMaxTiles][kArMaxRanks] u32
+  uint32_t data_off;                   // slots [2 parities][world][slot_bytes]
+  uint32_t slot_bytes;                 // one rank's fp16 copy of the output, 16 tokens: N * 32
+};
+
 // Decode variant (M <= 16, G % 128 == 0): same layout, workspace protocol and semantics.
 void fill_decode_plan(int M, GemmPlan* plan);
 int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                   const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
                   const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
-                  cudaStream_t stream);
+                  cudaStream_t stream, const FusedArParams* ar = nullptr);
 
 // NVLink peer-memory all-reduce (w4a16_allreduce.cu).  Region = header + two data slots.
-constexpr int kArMaxRanks = 8;
+// Region layout: [0, 2 KiB) flags[block][rank] | [2 KiB, +256) per-block epochs |
+// [3 KiB, +8) fused epoch + done counter | [4 KiB, 12 KiB) fused flags | [16 KiB ...) two
+// all-reduce slots, then (fused_bytes > 0) 2 x world fused slots.
 constexpr int kArMaxBlocks = 64;
 constexpr int kArFlagBytes = kArMaxBlocks * kArMaxRanks * 4;   // flags[block][rank]
-constexpr int kArHeaderBytes = 4096;                          // flags + per-block epoch counters
-static_assert(kArFlagBytes + kArMaxBlocks * 4 <= kArHeaderBytes, "all-reduce header layout");
+constexpr int kArFusedCtrOff = 3072;
+constexpr int kArFusedFlagOff = 4096;
+constexpr int kArHeaderBytes = 16384;
+static_assert(kArFlagBytes + kArMaxBlocks * 4 <= kArFusedCtrOff, "all-reduce header layout");
+static_assert(kArFusedFlagOff + 2 * kArMaxTiles * kArMaxRanks * 4 <= kArHeaderBytes, "fused flags");
 size_t ar_region_bytes(size_t max_message_bytes);
 int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* in, uint16_t* out,
                      size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream);

@@ -102,6 +102,25 @@ def quick_gemm(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_factors: to
     return _gemm(in_feats, kernel, scaling_factors, zeros, split_k_iters, LAYOUT_B200)
 
 
+def quick_gemm_all_reduce(in_feats: torch.Tensor, kernel: torch.Tensor,
+                          scaling_factors: torch.Tensor, zeros: torch.Tensor, handle) -> torch.Tensor:
+    """Row-parallel ``quick_gemm`` fused with the tensor-parallel all-reduce (one kernel per
+    rank, tiles pushed over NVLink as they finish): ``handle`` is the CustomAllreduce whose
+    ``can_fuse(M, N, G)`` accepted this shape.  Collective over the TP group."""
+    dev = _check_cuda(in_feats, kernel, scaling_factors, zeros)
+    if in_feats.dtype != torch.float16 or scaling_factors.dtype != torch.float16:
+        raise ValueError("in_feats and scaling_factors must be float16")
+    M, K = in_feats.shape
+    N = scaling_factors.shape[1]
+    G = K // scaling_factors.shape[0]
+    L = _lib.lib()
+    if kernel.numel() != L.b200_w4a16_repacked_words(K, N):
+        raise ValueError("kernel does not have the B200 layout size for these shapes")
+    with torch.cuda.device(dev):
+        ws = _workspace(dev, L.b200_w4a16_workspace_bytes(M, K, N, LAYOUT_B200))
+        return handle.gemm_all_reduce(in_feats, kernel, scaling_factors, zeros, ws, G)
+
+
 def _dequant(kernel, scaling_factors, zeros, layout) -> torch.Tensor:
     dev = _check_cuda(kernel, scaling_factors, zeros)
     if kernel.dtype != torch.int32 or zeros.dtype != torch.int32:

@@ -273,9 +273,16 @@ class RowParallelLinear(_LinearBase):
         if not self.input_is_parallel:
             input_ = split_tensor_along_last_dim(input_, self.tp_size)[
                 get_tensor_model_parallel_rank()].contiguous()
-        out = self.linear_method.apply_weights(self.linear_weights, input_)
+        out = None
         if self.reduce_results and self.tp_size > 1:
-            out = tensor_model_parallel_all_reduce(out)
+            fused = getattr(self.linear_method, "apply_weights_all_reduce", None)
+            if fused is not None:                 # GEMM + all-reduce in one kernel where it applies
+                out = fused(self.linear_weights, input_)
+            if out is None:
+                out = tensor_model_parallel_all_reduce(
+                    self.linear_method.apply_weights(self.linear_weights, input_))
+        else:
+            out = self.linear_method.apply_weights(self.linear_weights, input_)
         if self.skip_bias_add:
             return out, self.bias
         return (out + self.bias if self.bias is not None else out), None

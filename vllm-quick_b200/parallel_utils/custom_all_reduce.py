@@ -33,7 +33,7 @@ _handle: Optional["CustomAllreduce"] = None
 class CustomAllreduce:
     """One registered region per rank, mapped by every peer of the tensor-parallel group."""
 
-    def __init__(self, max_bytes: int) -> None:
+    def __init__(self, max_bytes: int, fused_out_features: int = 0) -> None:
         L = _lib.lib()
         self.rank = get_tensor_model_parallel_rank()
         self.world = get_tensor_model_parallel_world_size()
@@ -41,7 +41,8 @@ class CustomAllreduce:
             raise ValueError(f"custom all-reduce supports 2..{_MAX_WORLD} ranks, got {self.world}")
         self.max_bytes = (int(max_bytes) + 255) // 256 * 256
         self.device = torch.device("cuda", torch.cuda.current_device())
-        region_bytes = L.b200_w4a16_ar_region_bytes(self.max_bytes)
+        self.fused_out_features = int(fused_out_features)
+        region_bytes = L.b200_w4a16_ar_region_bytes(self.max_bytes, self.world, self.fused_out_features)
         own = ctypes.c_void_p()
         _lib.check(L.b200_w4a16_ar_alloc(region_bytes, ctypes.byref(own)), "all-reduce region")
         self._own = own.value
@@ -75,6 +76,23 @@ class CustomAllreduce:
         _lib.check(st, "custom all-reduce")
         return out
 
+    def can_fuse(self, M: int, N: int, G: int) -> bool:
+        """Fused row-parallel GEMM + all-reduce: decode batches whose output fits the slots."""
+        return 0 < M <= 16 and G % 128 == 0 and N <= self.fused_out_features and N <= 128 * 128
+
+    def gemm_all_reduce(self, x: torch.Tensor, qweight: torch.Tensor, scales: torch.Tensor,
+                        qzeros: torch.Tensor, workspace: torch.Tensor, G: int) -> torch.Tensor:
+        M, K = x.shape
+        N = scales.shape[1]
+        out = torch.empty((M, N), dtype=torch.float16, device=x.device)
+        st = _lib.lib().b200_w4a16_gemm_allreduce(
+            x.data_ptr(), qweight.data_ptr(), scales.data_ptr(), qzeros.data_ptr(), out.data_ptr(),
+            M, K, N, G, 0, workspace.data_ptr(), workspace.numel(), self._regions, self.rank,
+            self.world, self.max_bytes, self.fused_out_features,
+            torch.cuda.current_stream(x.device).cuda_stream)
+        _lib.check(st, "fused gemm + all-reduce")
+        return out
+
     def close(self) -> None:
         L = _lib.lib()
         torch.cuda.synchronize(self.device)
@@ -87,13 +105,22 @@ class CustomAllreduce:
             self._own = None
 
 
-def init_custom_all_reduce(max_bytes: int = 8 << 20) -> None:
+def init_custom_all_reduce(max_bytes: int = 8 << 20, fused_out_features: int = 0) -> None:
     """Collective over the TP group: allocate, exchange and map the regions (default 8 MiB
-    messages, the reference's limit, custom_all_reduce.py:143)."""
+    messages, the reference's limit, custom_all_reduce.py:143).  ``fused_out_features`` > 0
+    also reserves the slots of the fused row-parallel GEMM + all-reduce (the model's hidden
+    size: the output width of o_proj / down_proj)."""
     global _handle
     if _handle is not None or get_tensor_model_parallel_world_size() == 1:
         return
-    _handle = CustomAllreduce(max_bytes)
+    _handle = CustomAllreduce(max_bytes, fused_out_features)
+
+
+def fused_handle(M: int, N: int, G: int) -> Optional["CustomAllreduce"]:
+    """The handle if a row-parallel GEMM of this shape can run fused with its all-reduce."""
+    if _handle is not None and _handle.can_fuse(M, N, G):
+        return _handle
+    return None
 
 
 def is_initialized() -> bool:

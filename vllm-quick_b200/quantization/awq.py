@@ -110,6 +110,25 @@ class AWQLinearMethod(LinearMethodBase):
             weights["qweight_layout"] = LAYOUT_INTERLEAVED
         return qweight
 
+    def apply_weights_all_reduce(self, weights: Dict[str, Any],
+                                 x: torch.Tensor) -> Optional[torch.Tensor]:
+        """Row-parallel hook: GEMM on this rank's K shard fused with the tensor-parallel
+        all-reduce (one kernel; decode batches).  Returns None when the fused kernel does not
+        apply -- the caller then runs ``apply_weights`` + ``tensor_model_parallel_all_reduce``
+        as the reference does (linear.py:538-542)."""
+        from ..parallel_utils import custom_all_reduce
+        scales = weights["scales"]
+        reshaped_x = x.reshape(-1, x.shape[-1])
+        if scales.shape[0] == 0:
+            return None
+        handle = custom_all_reduce.fused_handle(reshaped_x.shape[0], scales.shape[-1],
+                                                reshaped_x.shape[1] // scales.shape[0])
+        if handle is None:
+            return None
+        qweight = self._interleave_once(weights)
+        out = ops.quick_gemm_all_reduce(reshaped_x, qweight, scales, weights["qzeros"], handle)
+        return out.reshape(x.shape[:-1] + (scales.shape[-1], ))
+
     def apply_weights(self, weights: Dict[str, Any], x: torch.Tensor,
                       bias: Optional[torch.Tensor] = None) -> torch.Tensor:
         scales = weights["scales"]
