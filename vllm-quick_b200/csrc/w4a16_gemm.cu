@@ -268,7 +268,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_f16_m128(MTOK);
       int stage = 0, buf = 0, itg = 0;
-      uint32_t fphase = 0, aphase = 0;
+      uint32_t aphase = 0;
       for (int idx = 0; idx < walk.nseg; ++idx) {
         int t0, n;
         walk.seg(idx, t0, n);
@@ -277,7 +277,11 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
         tc_fence_after();
         const uint32_t dcol = tmem + C::kDCol + d * C::kDStride;
         for (int i = 0; i < n; ++i) {
-          mbar_wait(bar_full + 8 * stage, fphase);
+          // One wait per tile: the dequant group arrives on bar_afull only after it has seen
+          // this stage's bar_full complete (weights, scales, zeros AND the activation TMA
+          // share that barrier), so the activations are covered transitively -- a second
+          // ~100-cycle try_wait here made the issuing thread, not the tensor pipe, the
+          // bottleneck at small token tiles.
           mbar_wait(bar_afull + 8 * buf, aphase);
           tc_fence_after();
           TR(4, itg);
@@ -293,7 +297,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           }
           TR(5, itg);
           ++itg;
-          if (++stage == C::kStages) { stage = 0; fphase ^= 1u; }
+          if (++stage == C::kStages) stage = 0;
           if (++buf == C::kABufs) { buf = 0; aphase ^= 1u; }
         }
         tc_commit(bar_dfull + 8 * d);
