@@ -167,6 +167,19 @@ def run_reference(args, model, tp):
     }))
 
 
+def measured_traffic(model, tp, M):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/traffic_decode16.json: one Llama-2-7B layer at M = 16), or None for any other
+    workload -- never an estimate."""
+    if model != "llama2-7b" or tp != 1 or M != 16:
+        return None
+    try:
+        return float(json.load(open(os.path.join(ROOT, "profiles", "traffic_decode16.json")))[
+            "avg_dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def kernel_name(pkg, M, K, N):
     plan = pkg._lib.gemm_plan(M, K, N)
     if plan["variant"] == "decode":
@@ -353,7 +366,8 @@ def main():
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": M * hidden * 2,
                     "d2h_bytes_per_step": M * hidden * 2, "ms_per_step": ms_e2e / args.steps},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": measured_traffic(model, tp, M),
+                         "peak_source": peak_src,
                          "kernel": kernel_name(pkg, M, shapes[0][1], shapes[0][2]),
                          "alg_bytes_per_launch": alg_per_launch, "us_per_launch": us_per_launch},
         }
