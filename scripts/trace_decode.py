@@ -70,6 +70,19 @@ def main():
             v = ta[i, :, e] - g0
             row.append(f"{nm} {v.min()}/{int(np.median(v))}/{v.max()}")
         print(f"launch {i}: " + " | ".join(row))
+        cyc = (ta[i, :, 12] - ta[i, :, 11]) % (1 << 32)
+        ns = ta[i, :, 7] - ta[i, :, 3]
+        mhz = 1e3 * cyc / np.maximum(ns, 1)
+        print(f"          SM clock inside the kernel (clock64 / globaltimer): {mhz.min():.0f}/{np.median(mhz):.0f}/{mhz.max():.0f} MHz")
+    # the slowest CTAs of the last launch: who makes the dependents wait?
+    last = ta[nl - 1]
+    rel0 = int(np.median(last[:, 3]))
+    order = np.argsort(-last[:, 7])
+    print(f"== launch {nl - 1}: CTAs by exit time (ns after the median dependency release)")
+    for cta in list(order[:10]) + list(order[-3:]):
+        r = last[cta]
+        print(f"   cta {cta:3d} tiles {r[9]:3d} segs {r[10]} entry {r[0] - rel0:6d} dep {r[3] - rel0:6d} tile0 {r[4] - rel0:6d} "
+              f"seg0_done {r[5] - rel0:6d} seg0_out {r[6] - rel0:6d} lastseg_done {r[8] - rel0:6d} exit {r[7] - rel0:6d}")
     # per-tile stamps of group 0 / warp 0 in the last launch, three CTAs
     for cta in (0, grid // 2, grid - 1):
         rel = ta[nl - 1, cta, 3]  # consumer past griddepcontrol.wait

@@ -13,8 +13,9 @@ from typing import Optional
 _PKG = os.path.dirname(os.path.abspath(__file__))
 # B200_W4A16_TRACE=1 selects the instrumented build (`make -C csrc trace`), a tuning aid only.
 _TRACE = os.environ.get("B200_W4A16_TRACE") == "1"
-LIB_PATH = os.path.join(_PKG, "lib",
-                        "libb200_w4a16_trace.so" if _TRACE else "libb200_w4a16.so")
+# B200_W4A16_LIB=<file name under lib/> selects a tuning build (`make -C csrc diag DIAG=n`).
+LIB_PATH = os.path.join(_PKG, "lib", os.environ.get("B200_W4A16_LIB") or
+                        ("libb200_w4a16_trace.so" if _TRACE else "libb200_w4a16.so"))
 CSRC = os.path.join(_PKG, "csrc")
 
 B200_OK, B200_ERR_BAD_SHAPE, B200_ERR_BAD_ARG, B200_ERR_WORKSPACE, B200_ERR_CUDA, \
