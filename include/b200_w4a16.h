@@ -82,6 +82,20 @@ int b200_w4a16_gemm(const uint16_t *x, const int32_t *qweight, const uint16_t *s
                     int layout, int split_k_hint, void *workspace, size_t workspace_bytes,
                     b200_stream_t stream);
 
+/* b200_w4a16_gemm for ONE routed expert of a mixture-of-experts block.  `gate` (device
+ * pointer, may be NULL = always compute) holds the number of tokens of this batch routed to
+ * the expert, written by the router earlier on the same stream.  Decode batches (M <= 16):
+ * when *gate == 0 the launch streams no weights and writes y = 0 -- the caller multiplies the
+ * expert's output by a zero routing weight anyway -- which removes the weight traffic of
+ * every expert no token selected (6 of 8 at one token, top-2).  Larger batches ignore the
+ * gate and compute.  CUDA-graph capturable (the flag is read on the device).
+ * Replaces: the dense "every local expert on every token" loop of MixtralMoE.forward
+ *           (vllm/model_executor/models/mixtral_quant.py:143-154), expert by expert. */
+int b200_w4a16_gemm_gated(const uint16_t *x, const int32_t *qweight, const uint16_t *scales,
+                          const int32_t *qzeros, uint16_t *y, int M, int K, int N, int G,
+                          int layout, int split_k_hint, const int32_t *gate, void *workspace,
+                          size_t workspace_bytes, b200_stream_t stream);
+
 /* W[K,N] half = fp16((q - z) * s), bit-exact with the reference.
  * Replaces: awq_dequantize(kernel, scaling_factors, zeros, split_k_iters, thx, thy)
  *           (csrc/ops.h:76-82, csrc/quantization/awq/gemm_kernels.cu:274-381); the three

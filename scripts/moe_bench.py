@@ -1,0 +1,103 @@
+#!/usr/bin/env python
+"""BASELINE configs[4]: Mixtral-8x7B AWQ expert MLP GEMMs at mixed batch sizes, one GPU
+holding `--experts-per-rank` of the 8 experts (8 = TP 1, 1 = one rank of TP 8).
+Times one MoE block (router + experts; CUDA graph over `--layers` distinct blocks so the
+weights exceed L2) with idle experts skipped on the device (b200_w4a16_gemm_gated) and with
+the reference's dense loop (every local expert streams its weights for every batch).
+Usage: python scripts/moe_bench.py [--tokens 1,4,16] [--layers 3] [--experts-per-rank 8]
+"""
+import argparse
+import importlib
+import json
+import os
+import sys
+import types
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+pkg = importlib.import_module("vllm-quick_b200")
+G = 128
+
+
+def fill(moe, gen):
+    for mlp in moe.experts:
+        if mlp is None:
+            continue
+        for lin in (mlp.w1, mlp.w2, mlp.w3):
+            lin.qweight.data.copy_(torch.randint(-2**31, 2**31 - 1, lin.qweight.shape, dtype=torch.int32,
+                                                 device="cuda", generator=gen))
+            lin.qzeros.data.copy_(torch.randint(-2**31, 2**31 - 1, lin.qzeros.shape, dtype=torch.int32,
+                                                device="cuda", generator=gen))
+            lin.scales.data.copy_((torch.rand(lin.scales.shape, device="cuda", generator=gen) * 0.004
+                                   + 0.001).half())
+    moe.gate.weight.data.copy_(torch.randn(moe.gate.weight.shape, device="cuda", generator=gen).half())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--tokens", default="1,4,16")
+    ap.add_argument("--layers", type=int, default=3)
+    ap.add_argument("--experts-per-rank", type=int, default=8)
+    ap.add_argument("--iters", type=int, default=20)
+    args = ap.parse_args()
+    hidden, ffn, experts, top_k = 4096, 14336, 8, 2
+    cfg = types.SimpleNamespace(num_local_experts=experts, num_experts_per_tok=top_k,
+                                hidden_size=hidden, intermediate_size=ffn)
+    gen = torch.Generator(device="cuda").manual_seed(0)
+    method = pkg.QuickConfig(4, G, True).get_linear_method()
+    torch.set_default_dtype(torch.float16)
+    blocks = []
+    with torch.device("cuda"):
+        for _ in range(args.layers):
+            moe = pkg.MixtralMoE(cfg, method)
+            # one rank of a wider tensor-parallel group: keep the first n experts only
+            moe.expert_indicies = list(range(args.experts_per_rank))
+            for e in range(args.experts_per_rank, experts):
+                moe.experts[e] = None
+            blocks.append(moe)
+    torch.set_default_dtype(torch.float32)
+    for moe in blocks:
+        fill(moe, gen)
+    bytes_expert = 3 * (hidden * ffn // 2 + (hidden // G) * ffn * 5 // 2)   # packed + scales + zeros (approx.)
+    for T in (int(v) for v in args.tokens.split(",")):
+        x = torch.randn(1, T, hidden, device="cuda", generator=gen).half()
+        res = {}
+        for skip in (True, False):
+            for moe in blocks:
+                moe.skip_idle_experts = skip
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                for moe in blocks:
+                    moe(x)
+                st.synchronize()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=st):
+                    for moe in blocks:
+                        moe(x)
+                for _ in range(3):
+                    graph.replay()
+                st.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(st)
+                for _ in range(args.iters):
+                    graph.replay()
+                e1.record(st)
+                st.synchronize()
+            res[skip] = e0.elapsed_time(e1) * 1e3 / (args.iters * len(blocks))
+        active = []
+        for moe in blocks:
+            _, _, counts = moe.route(x.view(-1, hidden))
+            active.append(int((counts[:args.experts_per_rank] > 0).sum()))
+        mean_active = sum(active) / len(active)
+        print(json.dumps({"tokens": T, "local_experts": args.experts_per_rank,
+                          "active_experts_mean": round(mean_active, 2),
+                          "us_per_block_skip_idle": round(res[True], 1),
+                          "us_per_block_dense_reference_loop": round(res[False], 1),
+                          "speedup": round(res[False] / res[True], 2),
+                          "GBps_active_weights": round(mean_active * bytes_expert / res[True] / 1e3, 1)}))
+
+
+if __name__ == "__main__":
+    main()

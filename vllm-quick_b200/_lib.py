@@ -30,7 +30,7 @@ EXPORTS = (
     "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan", "b200_w4a16_gemm_variant",
     "b200_w4a16_ar_region_bytes", "b200_w4a16_ar_alloc", "b200_w4a16_ar_free",
     "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
-    "b200_w4a16_allreduce", "b200_w4a16_gemm_allreduce",
+    "b200_w4a16_allreduce", "b200_w4a16_gemm_allreduce", "b200_w4a16_gemm_gated",
 )
 
 
@@ -74,6 +74,8 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_workspace_bytes.argtypes = [i32, i32, i32, i32]
     L.b200_w4a16_gemm.restype = i32
     L.b200_w4a16_gemm.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, sz, vp]
+    L.b200_w4a16_gemm_gated.restype = i32
+    L.b200_w4a16_gemm_gated.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, sz, vp]
     L.b200_w4a16_dequant.restype = i32
     L.b200_w4a16_dequant.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, vp]
     L.b200_w4a16_repack.restype = i32

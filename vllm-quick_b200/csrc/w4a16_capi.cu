@@ -137,7 +137,16 @@ int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* s
                     const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G, int layout,
                     int split_k_hint, void* workspace, size_t workspace_bytes,
                     b200_stream_t stream) {
+  return b200_w4a16_gemm_gated(x, qweight, scales, qzeros, y, M, K, N, G, layout, split_k_hint,
+                               nullptr, workspace, workspace_bytes, stream);
+}
+
+int b200_w4a16_gemm_gated(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
+                          const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
+                          int layout, int split_k_hint, const int32_t* gate, void* workspace,
+                          size_t workspace_bytes, b200_stream_t stream) {
   if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
+  if (gate && (reinterpret_cast<uintptr_t>(gate) & 3u)) return B200_ERR_BAD_ARG;
   if (layout != B200_LAYOUT_AWQ && layout != B200_LAYOUT_B200) return B200_ERR_BAD_ARG;
   if (M == 0) return B200_OK;
   if (!x || !qweight || !scales || !qzeros || !y) return B200_ERR_BAD_ARG;
@@ -173,7 +182,7 @@ int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* s
   }
   int e = plan.kind == b200::kKindDecode
               ? b200::launch_decode(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters,
-                                    pdl, s)
+                                    pdl, s, nullptr, gate)
               : b200::launch_gemm(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters,
                                   pdl, s);
   if (e != 0) return cuda_fail(e);

@@ -99,6 +99,9 @@ struct DecodeParams {
   int T, P;
   int Gdiv;     // K blocks per quantization group (G / 128)
   int flags;
+  // Routed-expert gate (b200_w4a16_gemm_gated): when non-null and *gate == 0 no token of the
+  // batch is routed to this expert -- the launch streams nothing and zero-fills y.
+  const int* gate;
   uint32_t* trace;  // B200_TRACE builds only: 16 globaltimer stamps per CTA
   // Row-parallel fusion (ar.world > 1): finished tiles are pushed to every rank's region and
   // reduced there; y then holds the all-reduced result (see the file header).
@@ -217,6 +220,11 @@ w4a16_decode_kernel(const DecodeParams p) {
     // the activations of those tiles, then runs the steady loop.
     const int pw = warp - kWProducerWarp;
     if (pw == 0 && lane == 0) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (p.gate) {
+      // the flag is the previous kernel's output (the router): no weight prefetch before it
+      asm volatile("griddepcontrol.wait;" ::: "memory");
+      if (*reinterpret_cast<const volatile int*>(p.gate) == 0) return;
+    }
     const uint64_t pol_w = (p.flags & 1) ? policy_evict_normal() : policy_evict_first();
     const uint32_t srow = (uint32_t)p.N;                      // halfs per scale row
     const uint32_t zrow = (uint32_t)p.N >> 3;                 // words per zero row
@@ -311,6 +319,7 @@ w4a16_decode_kernel(const DecodeParams p) {
   } else if (warp == kHelperWarp) {
     // ---------------- helper: publishes group 0's partial tiles and waits for the contributors
     asm volatile("griddepcontrol.wait;" ::: "memory");        // the counters belong to earlier work until now
+    if (p.gate && *reinterpret_cast<const volatile int*>(p.gate) == 0) return;   // expert without tokens
     const bool fused = p.ar.world > 1;
     int own_nt = -1, own_last = 0;
     bool own_local = false;
@@ -357,6 +366,17 @@ w4a16_decode_kernel(const DecodeParams p) {
     float4* xchg = reinterpret_cast<float4*>(smem_gen + C::kXchgOff);
     asm volatile("griddepcontrol.wait;" ::: "memory");        // y / workspace may alias earlier work
     if (grp == 0 && ct == 0) { TD(3); TDV(9, n_total); TDV(10, walk.nseg); TDV(11, (uint32_t)clock64()); }
+    if (p.gate && *reinterpret_cast<const volatile int*>(p.gate) == 0) {
+      // expert without tokens: y = 0 (the caller scales it by a zero routing weight), CTA b
+      // clears channel tiles b, b + P, ...: 16-byte stores, 16 per token row and tile
+      const int tid = threadIdx.x - kFirstConsumerWarp * 32;
+      for (int nt = blockIdx.x; nt < p.NT; nt += gridDim.x)
+        for (int v = tid; v < p.M * 16; v += kConsumerThreads) {
+          const int m = v >> 4, n0 = nt * kTileN + (v & 15) * 8;
+          if (n0 < p.N) *reinterpret_cast<uint4*>(p.y + (size_t)m * p.N + n0) = make_uint4(0u, 0u, 0u, 0u);
+        }
+      return;
+    }
     int own_nt = -1, own_slot = 0, own_last = 0;              // tile this CTA finishes, if any
     bool own_local = false;                                   // its own piece is handed over in shared memory
     auto write_y = [&](int nt, const float (&v)[2][MT][4]) {
@@ -805,7 +825,7 @@ void fill_decode_plan(int M, GemmPlan* plan) {
 int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                   const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
                   const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
-                  cudaStream_t stream, const FusedArParams* ar) {
+                  cudaStream_t stream, const FusedArParams* ar, const int* gate) {
   DecodeParams prm;
   prm.qw = reinterpret_cast<const uint32_t*>(qw_b200);
   prm.x = x;
@@ -821,6 +841,7 @@ int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* sca
   prm.Gdiv = G / kTileK;
   prm.flags = decode_flags();
   prm.trace = trace_buffer();
+  prm.gate = gate;
   if (ar) {
     prm.ar = *ar;
   } else {

@@ -59,7 +59,8 @@ void fill_decode_plan(int M, GemmPlan* plan);
 int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                   const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
                   const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
-                  cudaStream_t stream, const FusedArParams* ar = nullptr);
+                  cudaStream_t stream, const FusedArParams* ar = nullptr,
+                  const int* gate = nullptr);
 
 // NVLink peer-memory all-reduce (w4a16_allreduce.cu).  Region = header + two data slots.
 // Region layout: [0, 2 KiB) flags[block][rank] | [2 KiB, +256) per-block epochs |

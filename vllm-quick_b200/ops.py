@@ -11,7 +11,9 @@ PyTorch is used for device memory and streams only; all arithmetic is in
 """
 from __future__ import annotations
 
-from typing import Dict, Tuple
+import contextlib
+import threading
+from typing import Dict, Optional, Tuple
 
 import torch
 
@@ -52,6 +54,25 @@ def _check_cuda(*tensors: torch.Tensor) -> torch.device:
     return dev
 
 
+# Routed-expert gate: inside ``with expert_gate(flag):`` every GEMM issued by this thread
+# carries ``flag`` (int32 device scalar: tokens of the batch routed to the expert) down to
+# b200_w4a16_gemm_gated.  A context instead of an argument because the plugin interface
+# (LinearMethodBase.apply_weights(weights, x, bias), linear.py:30-37) has no room for one.
+_gate = threading.local()
+
+
+@contextlib.contextmanager
+def expert_gate(flag: Optional[torch.Tensor]):
+    if flag is not None and (flag.dtype != torch.int32 or not flag.is_cuda or flag.numel() != 1):
+        raise ValueError("expert_gate needs an int32 CUDA scalar")
+    prev = getattr(_gate, "flag", None)
+    _gate.flag = flag
+    try:
+        yield
+    finally:
+        _gate.flag = prev
+
+
 def _gemm(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_factors: torch.Tensor,
           zeros: torch.Tensor, split_k_iters: int, layout: int) -> torch.Tensor:
     dev = _check_cuda(in_feats, kernel, scaling_factors, zeros)
@@ -78,9 +99,12 @@ def _gemm(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_factors: torch.T
     with torch.cuda.device(dev):
         need = L.b200_w4a16_workspace_bytes(M, K, N, layout)
         ws = _workspace(dev, need)
-        st = L.b200_w4a16_gemm(in_feats.data_ptr(), kernel.data_ptr(), scaling_factors.data_ptr(),
-                               zeros.data_ptr(), out.data_ptr(), M, K, N, G, layout,
-                               int(split_k_iters), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+        flag = getattr(_gate, "flag", None)
+        st = L.b200_w4a16_gemm_gated(in_feats.data_ptr(), kernel.data_ptr(),
+                                     scaling_factors.data_ptr(), zeros.data_ptr(), out.data_ptr(),
+                                     M, K, N, G, layout, int(split_k_iters),
+                                     flag.data_ptr() if flag is not None else None,
+                                     ws.data_ptr(), ws.numel(), _stream_ptr(dev))
     _lib.check(st, "w4a16 gemm")
     return out
 
