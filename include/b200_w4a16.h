@@ -181,6 +181,37 @@ int b200_w4a16_gemm_allreduce(const uint16_t *x, const int32_t *qweight, const u
                               size_t max_message_bytes, int fused_out_features,
                               b200_stream_t stream);
 
+/* ---- residual add + RMSNorm around the row-parallel linears ---------------
+ * out[rows, hidden] = half(float(half(x)) * rsqrt(mean(x^2) + eps)) * weight,
+ *   x = float(in) + float(residual_in)  (residual_in == NULL: x = in),
+ *   residual_out = half(x)              (residual_out == NULL: not written),
+ * fp16 storage, fp32 statistics taken from x BEFORE it is rounded -- the reference's
+ * arithmetic.  out may alias in, residual_out may alias residual_in (the reference works in
+ * place).  hidden % 8 == 0, hidden <= 16384; rows == 0 is a no-op.
+ * Replaces: rms_norm(out, input, weight, eps)            (csrc/ops.h, csrc/layernorm_kernels.cu:78-102)
+ *           fused_add_rms_norm(input, residual, weight, eps)      (csrc/layernorm_kernels.cu:104-129)
+ *           as called by RMSNorm.forward (vllm/model_executor/layers/layernorm.py:46-66). */
+int b200_w4a16_add_rms_norm(const uint16_t *in, const uint16_t *residual_in, const uint16_t *weight,
+                      uint16_t *out, uint16_t *residual_out, float eps, size_t rows, int hidden,
+                      b200_stream_t stream);
+
+/* The same with x = all-reduce(in) over the ranks (rounded to fp16 exactly as
+ * b200_w4a16_allreduce rounds it): ONE kernel for the "row-parallel all-reduce, then
+ * fused_add_rms_norm" pair of a decoder layer -- the reduced rows never travel through HBM
+ * between the two and the second launch disappears.  Result is bit-identical on every rank
+ * and to b200_w4a16_allreduce followed by b200_w4a16_add_rms_norm.  `in` is this rank's partial sum
+ * (RowParallelLinear with reduce_results=False); rows * hidden * 2 <= max_message_bytes.
+ * Collective; shares regions, flags and epochs with b200_w4a16_allreduce (calls of both kinds
+ * may be mixed on one stream).  CUDA-graph capturable.  `barrier` as in b200_w4a16_allreduce.
+ * Replaces: tensor_model_parallel_all_reduce (vllm/model_executor/layers/linear.py:541-542)
+ *           + post_attention_layernorm / next layer's input_layernorm
+ *           (vllm/model_executor/models/llama.py:205-222). */
+int b200_w4a16_allreduce_add_rms_norm(void *const *regions, int rank, int world, const uint16_t *in,
+                                const uint16_t *residual_in, const uint16_t *weight,
+                                uint16_t *out, uint16_t *residual_out, float eps, size_t rows,
+                                int hidden, size_t max_message_bytes, int barrier,
+                                b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

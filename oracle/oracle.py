@@ -221,3 +221,51 @@ def make_inputs(M: int, K: int, N: int, G: int = 128, seed: int = 0, signed_scal
     if signed_scales:
         scales = (scales * rng.choice([-1.0, 1.0], size=scales.shape)).astype(np.float16)
     return x, qweight, scales, qzeros
+
+
+# ---- residual add + RMSNorm ---------------------------------------------------
+# The reference has its own CPU statement of this op -- RMSNorm._forward,
+# vllm/model_executor/layers/layernorm.py:26-44 -- and tests its kernel against it with
+# atol = rtol = 1e-2 (tests/kernels/test_layernorm.py:30-59).  `np_rms_norm_forward` restates
+# `_forward`; `np_rms_norm_kernel` restates the CUDA kernels' arithmetic
+# (csrc/layernorm_kernels.cu:12-76): statistics from the UNROUNDED fp32 sum, the scaling pass
+# from the ROUNDED residual, half x half product rounded once.  The sum of squares is taken in
+# float64 here (the kernels' shuffle-tree order is not part of the contract): tolerance parity.
+# Parity pin: the reference's kernel cannot run in this container and its test holds no
+# vectors; the two restatements are checked against each other and against the reference's
+# tolerance ("parity unpinned" beyond that).
+
+def np_rms_norm_forward(x: np.ndarray, weight: np.ndarray, eps: float, residual=None):
+    """RMSNorm._forward (layernorm.py:26-44) for fp16 arrays."""
+    x32 = x.astype(np.float32)
+    res_out = None
+    if residual is not None:
+        x32 = x32 + residual.astype(np.float32)
+        res_out = x32.astype(np.float16)
+    var = np.mean(x32 * x32, axis=-1, keepdims=True, dtype=np.float32)
+    y = x32 * (np.float32(1.0) / np.sqrt(var + np.float32(eps)))
+    out = (y.astype(np.float16).astype(np.float32) * weight.astype(np.float32)).astype(np.float16)
+    return out if residual is None else (out, res_out)
+
+
+def np_rms_norm_kernel(x: np.ndarray, weight: np.ndarray, eps: float, residual=None):
+    """rms_norm_kernel / fused_add_rms_norm_kernel (csrc/layernorm_kernels.cu:12-76)."""
+    x32 = x.astype(np.float32)
+    if residual is not None:
+        x32 = x32 + residual.astype(np.float32)            # :49-50
+    res_out = x32.astype(np.float16)                        # :52 (== x without a residual)
+    hidden = x.shape[-1]
+    var = (x32.astype(np.float64) ** 2).sum(axis=-1, keepdims=True)          # :51,54
+    inv = (np.float32(1.0) / np.sqrt((var / hidden).astype(np.float32) + np.float32(eps))).astype(np.float32)  # :56
+    y = (res_out.astype(np.float32) * inv).astype(np.float16)               # :61-62
+    out = (y.astype(np.float32) * weight.astype(np.float32)).astype(np.float16)
+    return out if residual is None else (out, res_out)
+
+
+def np_allreduce_f16(parts) -> np.ndarray:
+    """fp16 all-reduce as the peer-memory kernel defines it: fp32 sum in rank order, one
+    rounding (custom_all_reduce.cuh:204-232 accumulates 16-bit types in fp32 likewise)."""
+    acc = np.zeros(parts[0].shape, dtype=np.float32)
+    for p in parts:
+        acc = acc + p.astype(np.float32)
+    return acc.astype(np.float16)

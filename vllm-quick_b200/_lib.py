@@ -31,6 +31,7 @@ EXPORTS = (
     "b200_w4a16_ar_region_bytes", "b200_w4a16_ar_alloc", "b200_w4a16_ar_free",
     "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
     "b200_w4a16_allreduce", "b200_w4a16_gemm_allreduce", "b200_w4a16_gemm_gated",
+    "b200_w4a16_add_rms_norm", "b200_w4a16_allreduce_add_rms_norm",
 )
 
 
@@ -101,6 +102,12 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_allreduce.argtypes = [ctypes.POINTER(vp), i32, i32, vp, vp, sz, sz, i32, vp]
     L.b200_w4a16_gemm_variant.restype = i32
     L.b200_w4a16_gemm_variant.argtypes = [i32, i32, i32, i32]
+    f32 = ctypes.c_float
+    L.b200_w4a16_add_rms_norm.restype = i32
+    L.b200_w4a16_add_rms_norm.argtypes = [vp, vp, vp, vp, vp, f32, sz, i32, vp]
+    L.b200_w4a16_allreduce_add_rms_norm.restype = i32
+    L.b200_w4a16_allreduce_add_rms_norm.argtypes = [ctypes.POINTER(vp), i32, i32, vp, vp, vp, vp, vp, f32,
+                                              sz, i32, sz, i32, vp]
     _lib = L
     return L
 

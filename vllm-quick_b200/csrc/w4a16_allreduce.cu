@@ -111,6 +111,13 @@ allreduce_oneshot_kernel(const ArParams p) {
     __syncthreads();
   }
   if (threadIdx.x == 0) *my_epoch = epoch;
+  // Every block's epoch advances on every call (block 0 covers the blocks this grid does not
+  // have): the slot parity is then a property of the CALL, so calls of different sizes -- and
+  // the all-reduce + RMSNorm kernel of w4a16_norm.cu, which maps chunks to blocks differently
+  // -- may be mixed on one stream: rank r reaches call e+2 only after a peer's block 0 arrived
+  // at call e+1, i.e. after that peer's call e (all of its blocks) had finished reading.
+  if (blockIdx.x == 0 && threadIdx.x >= gridDim.x && threadIdx.x < kArMaxBlocks)
+    reinterpret_cast<uint32_t*>(mine + kArFlagBytes)[threadIdx.x] = epoch;
 
   // 3. reduce in rank order (identical on every rank), fp32 accumulate
   for (uint32_t c = blockIdx.x * kArThreads + threadIdx.x; c < p.nchunks; c += gridDim.x * kArThreads) {

@@ -77,6 +77,18 @@ size_t ar_region_bytes(size_t max_message_bytes);
 int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* in, uint16_t* out,
                      size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream);
 
+// Residual add + RMSNorm, standalone and fused behind the one-shot all-reduce (w4a16_norm.cu).
+// hidden % 8 == 0, hidden <= norm_max_hidden(); residual_in / residual_out may be nullptr.
+int norm_max_hidden();
+int launch_add_rmsnorm(const uint16_t* in, const uint16_t* residual_in, const uint16_t* weight,
+                       uint16_t* out, uint16_t* residual_out, float eps, size_t rows, int hidden,
+                       cudaStream_t stream);
+int launch_allreduce_add_rmsnorm(void* const* regions, int rank, int world, const uint16_t* in,
+                                 const uint16_t* residual_in, const uint16_t* weight,
+                                 uint16_t* out, uint16_t* residual_out, float eps, size_t rows,
+                                 int hidden, size_t max_message_bytes, int barrier,
+                                 cudaStream_t stream);
+
 // B200_TRACE builds: device buffer of 148 x 8 x 64 uint32 timestamps (nullptr = off).
 void set_trace_buffer(uint32_t* dev);
 uint32_t* trace_buffer();

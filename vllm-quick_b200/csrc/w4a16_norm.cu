@@ -1,0 +1,308 @@
+// w4a16_norm.cu -- residual add + RMSNorm, standalone and fused with the one-shot NVLink
+// all-reduce that follows every row-parallel W4A16 GEMM.
+//
+// Replaces:
+//   rms_norm / fused_add_rms_norm          csrc/layernorm_kernels.cu:12-76, 78-129
+//   RMSNorm.forward                        vllm/model_executor/layers/layernorm.py:46-66
+//   and, fused, the sequence of a Llama decoder layer
+//       o_proj / down_proj all-reduce  ->  fused_add_rms_norm
+//   (vllm/model_executor/models/llama.py:205-222, layers/linear.py:541-542).
+//
+// Arithmetic (same as the reference, fp16 storage):
+//   x   = float(in) [+ float(residual)]          residual_out = half(x)
+//   var = sum(x * x) / hidden                    (x before rounding, fp32)
+//   out = half(float(half(x)) * rsqrt(var + eps)) * weight        (half multiply, RNE)
+// Without a residual half(x) == in.  The sum of squares is a fixed-order tree (lane shuffle,
+// warps, cluster ranks), so results are deterministic; it is not the reference's
+// blockReduceSum order (floating point: tolerance parity, see tests/test_gpu_norm.py).
+//
+// Layout: a token row of `hidden` halfs is cut into 16-byte chunks; a thread-block CLUSTER of
+// C = ceil(hidden / 2048) CTAs x 256 threads owns a row, CTA j holding chunks [256 j, 256 j +
+// 256): every value stays in registers between the statistics pass and the scaling pass, and
+// the C partial sums of squares meet through distributed shared memory -- no second read of
+// the row, no global scratch.  Row clusters stride over the rows.
+//
+// Fused variant: the all-reduce protocol of w4a16_allreduce.cu (same region, flags and epochs,
+// so both kernels may be mixed on one stream): block b stages ITS chunks of every row it owns
+// into the rank's slot, crosses the per-block NVLink barrier, then sums the peers' copies in
+// rank order, rounds to fp16 (== the unfused all-reduce result, bit for bit) and continues
+// into the add + norm above without the [rows, hidden] round trip through HBM and without a
+// second launch.
+#include <cooperative_groups.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "w4a16_internal.h"
+
+namespace cg = cooperative_groups;
+
+namespace b200 {
+
+namespace {
+
+constexpr int kNormThreads = 256;
+constexpr int kNormMaxCluster = 8;     // hidden <= 8 * 256 * 8 = 16384
+
+struct NormParams {
+  uint8_t* region[kArMaxRanks];   // fused variant: peer-mapped regions, index = rank
+  const uint4* in;                // [rows, hidden] half
+  const uint4* residual_in;       // [rows, hidden] half or nullptr
+  const uint4* weight;            // [hidden] half
+  uint4* out;                     // [rows, hidden] half (may alias in)
+  uint4* residual_out;            // [rows, hidden] half or nullptr (may alias residual_in)
+  float eps;
+  float inv_hidden;
+  uint32_t rows;
+  uint32_t chunks_per_row;        // hidden / 8
+  uint32_t slot_bytes;
+  int rank;
+  int barrier;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void unpack8(float (&f)[8], const uint4& v) {
+  const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __half22float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+// WORLD == 0: plain (x read from `in`); WORLD >= 1: x = all-reduce over WORLD ranks of `in`.
+template <int WORLD>
+__global__ void __launch_bounds__(kNormThreads)
+add_rmsnorm_kernel(const NormParams p) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const uint32_t csize = cluster.num_blocks();
+  const uint32_t crank = cluster.block_rank();
+  const uint32_t row0 = blockIdx.x / csize;
+  const uint32_t row_step = gridDim.x / csize;
+  const uint32_t ch = crank * kNormThreads + threadIdx.x;     // chunk of the row this thread owns
+  const bool active = ch < p.chunks_per_row;
+
+  __shared__ float s_warp[kNormThreads / 32];
+  __shared__ float s_part[2];                                  // per-CTA partial, double buffered
+  __shared__ uint32_t s_epoch;
+
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+
+  uint32_t slot_off = 0;
+  if constexpr (WORLD > 0) {
+    uint8_t* mine = p.region[p.rank];
+    uint32_t* my_flags = reinterpret_cast<uint32_t*>(mine) + blockIdx.x * kArMaxRanks;
+    uint32_t* epochs = reinterpret_cast<uint32_t*>(mine + kArFlagBytes);
+    if (threadIdx.x == 0) s_epoch = epochs[blockIdx.x] + 1;
+    __syncthreads();
+    const uint32_t epoch = s_epoch;
+    slot_off = kArHeaderBytes + (epoch & 1u) * p.slot_bytes;
+    // 1. stage this thread's chunk of every row of this cluster into the own slot
+    if (active) {
+      uint4* my_slot = reinterpret_cast<uint4*>(mine + slot_off);
+      for (uint32_t r = row0; r < p.rows; r += row_step) {
+        const size_t c = (size_t)r * p.chunks_per_row + ch;
+        my_slot[c] = p.in[c];
+      }
+    }
+    __threadfence_system();
+    __syncthreads();
+    // 2. cross-GPU barrier of block b (peers' block b staged exactly the chunks read below)
+    if (p.barrier) {
+      if (threadIdx.x < WORLD) {
+        const int q = threadIdx.x;
+        uint32_t* peer_flag =
+            reinterpret_cast<uint32_t*>(p.region[q]) + blockIdx.x * kArMaxRanks + p.rank;
+        st_release_sys(peer_flag, epoch);
+        const long long t0 = clock64();
+        while (ld_acquire_sys(my_flags + q) != epoch) {
+          if (clock64() - t0 > 4000000000ll) {
+            printf("b200_w4a16: all-reduce+norm barrier timeout rank %d block %d peer %d\n",
+                   p.rank, blockIdx.x, q);
+            __trap();
+          }
+        }
+      }
+      __syncthreads();
+    }
+    // every block's epoch advances on every call (block 0 covers the idle ones): the slot
+    // parity is then a property of the call, whatever grid the previous calls used.
+    if (threadIdx.x == 0) epochs[blockIdx.x] = epoch;
+    if (blockIdx.x == 0 && threadIdx.x >= gridDim.x && threadIdx.x < kArMaxBlocks)
+      epochs[threadIdx.x] = epoch;
+  }
+
+  uint4 wv = make_uint4(0, 0, 0, 0);
+  if (active) wv = p.weight[ch];
+
+  uint32_t it = 0;
+  for (uint32_t r = row0; r < p.rows; r += row_step, ++it) {
+    const size_t c = (size_t)r * p.chunks_per_row + ch;
+    float x[8];
+    uint4 xr = make_uint4(0, 0, 0, 0);      // half(x): the residual stream
+    float ssq = 0.f;
+    if (active) {
+      uint4 xin;
+      if constexpr (WORLD > 0) {
+        uint4 v[WORLD];
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q)
+          v[q] = ld_volatile_v4(reinterpret_cast<const uint4*>(p.region[q] + slot_off) + c);
+        float acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q) {
+          float f[8];
+          unpack8(f, v[q]);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] += f[i];
+        }
+        __half2* xh = reinterpret_cast<__half2*>(&xin);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) xh[i] = __floats2half2_rn(acc[2 * i], acc[2 * i + 1]);
+      } else {
+        xin = p.in[c];
+      }
+      unpack8(x, xin);
+      if (p.residual_in) {
+        float res[8];
+        unpack8(res, p.residual_in[c]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] += res[i];
+        __half2* h = reinterpret_cast<__half2*>(&xr);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) h[i] = __floats2half2_rn(x[2 * i], x[2 * i + 1]);
+      } else {
+        xr = xin;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ssq = fmaf(x[i], x[i], ssq);
+      if (p.residual_out) p.residual_out[c] = xr;
+    }
+    // fixed-order tree: lanes, warps, cluster ranks
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = ssq;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < kNormThreads / 32; ++w) t += s_warp[w];
+      s_part[it & 1] = t;
+    }
+    cluster.sync();
+    float total = 0.f;
+    for (uint32_t j = 0; j < csize; ++j) total += *cluster.map_shared_rank(&s_part[it & 1], j);
+    const float inv = rsqrtf(total * p.inv_hidden + p.eps);
+    if (active) {
+      float xf[8];
+      unpack8(xf, xr);
+      uint4 o;
+      __half2* oh = reinterpret_cast<__half2*>(&o);
+      const __half2* wh = reinterpret_cast<const __half2*>(&wv);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        oh[i] = __hmul2(__floats2half2_rn(xf[2 * i] * inv, xf[2 * i + 1] * inv), wh[i]);
+      p.out[c] = o;
+    }
+  }
+  cluster.sync();   // nobody leaves while a peer CTA may still read its partial
+}
+
+template <int WORLD>
+int launch_norm(const NormParams& prm, int cluster, int row_clusters, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(cluster * row_clusters));
+  cfg.blockDim = dim3(kNormThreads);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)cluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return (int)cudaLaunchKernelEx(&cfg, add_rmsnorm_kernel<WORLD>, prm);
+}
+
+int fill_params(NormParams* prm, const uint16_t* in, const uint16_t* residual_in,
+                const uint16_t* weight, uint16_t* out, uint16_t* residual_out, float eps,
+                size_t rows, int hidden) {
+  for (int q = 0; q < kArMaxRanks; ++q) prm->region[q] = nullptr;
+  prm->in = reinterpret_cast<const uint4*>(in);
+  prm->residual_in = reinterpret_cast<const uint4*>(residual_in);
+  prm->weight = reinterpret_cast<const uint4*>(weight);
+  prm->out = reinterpret_cast<uint4*>(out);
+  prm->residual_out = reinterpret_cast<uint4*>(residual_out);
+  prm->eps = eps;
+  prm->inv_hidden = 1.0f / (float)hidden;
+  prm->rows = (uint32_t)rows;
+  prm->chunks_per_row = (uint32_t)(hidden / 8);
+  prm->slot_bytes = 0;
+  prm->rank = 0;
+  prm->barrier = 0;
+  return (int)((prm->chunks_per_row + kNormThreads - 1) / kNormThreads);   // cluster size
+}
+
+}  // namespace
+
+int norm_max_hidden() { return kNormMaxCluster * kNormThreads * 8; }
+
+int launch_add_rmsnorm(const uint16_t* in, const uint16_t* residual_in, const uint16_t* weight,
+                       uint16_t* out, uint16_t* residual_out, float eps, size_t rows, int hidden,
+                       cudaStream_t stream) {
+  NormParams prm;
+  const int cluster = fill_params(&prm, in, residual_in, weight, out, residual_out, eps, rows, hidden);
+  // 4 resident 256-thread CTAs per SM are plenty for a row-per-cluster kernel
+  size_t row_clusters = (size_t)(kMaxCtas * 4 / cluster);
+  if (row_clusters > rows) row_clusters = rows;
+  return launch_norm<0>(prm, cluster, (int)row_clusters, stream);
+}
+
+int launch_allreduce_add_rmsnorm(void* const* regions, int rank, int world, const uint16_t* in,
+                                 const uint16_t* residual_in, const uint16_t* weight,
+                                 uint16_t* out, uint16_t* residual_out, float eps, size_t rows,
+                                 int hidden, size_t max_message_bytes, int barrier,
+                                 cudaStream_t stream) {
+  NormParams prm;
+  const int cluster = fill_params(&prm, in, residual_in, weight, out, residual_out, eps, rows, hidden);
+  for (int q = 0; q < world; ++q) prm.region[q] = static_cast<uint8_t*>(regions[q]);
+  prm.slot_bytes = (uint32_t)((max_message_bytes + 255) / 256 * 256);
+  prm.rank = rank;
+  prm.barrier = barrier;
+  size_t row_clusters = (size_t)(kArMaxBlocks / cluster);      // one barrier flag set per block
+  if (row_clusters > rows) row_clusters = rows;
+  switch (world) {
+    case 1: return launch_norm<1>(prm, cluster, (int)row_clusters, stream);
+    case 2: return launch_norm<2>(prm, cluster, (int)row_clusters, stream);
+    case 3: return launch_norm<3>(prm, cluster, (int)row_clusters, stream);
+    case 4: return launch_norm<4>(prm, cluster, (int)row_clusters, stream);
+    case 5: return launch_norm<5>(prm, cluster, (int)row_clusters, stream);
+    case 6: return launch_norm<6>(prm, cluster, (int)row_clusters, stream);
+    case 7: return launch_norm<7>(prm, cluster, (int)row_clusters, stream);
+    case 8: return launch_norm<8>(prm, cluster, (int)row_clusters, stream);
+    default: return (int)cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace b200

@@ -214,3 +214,42 @@ def quick_repack(kernel: torch.Tensor) -> torch.Tensor:
 def quick_unrepack(kernel: torch.Tensor, in_features: int, out_features: int) -> torch.Tensor:
     """Inverse of ``quick_repack``."""
     return _repack(kernel, in_features, out_features, _lib.REPACK_B200_TO_AWQ)
+
+
+def _norm_args(x: torch.Tensor, weight: torch.Tensor, *others: Optional[torch.Tensor]) -> Tuple[torch.device, int, int]:
+    dev = _check_cuda(x, weight, *[t for t in others if t is not None])
+    for t in (x, weight) + tuple(o for o in others if o is not None):
+        if t.dtype != torch.float16:
+            raise ValueError("the B200 RMSNorm kernels take float16 tensors only")
+        if not t.is_contiguous():
+            raise ValueError("RMSNorm tensors must be contiguous")
+    hidden = x.shape[-1]
+    if weight.numel() != hidden:
+        raise ValueError("weight must have hidden_size elements")
+    for o in others:
+        if o is not None and o.shape != x.shape:
+            raise ValueError("tensors of an RMSNorm call must have the same shape")
+    return dev, (x.numel() // hidden if hidden else 0), hidden
+
+
+def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+    """``out = rms_norm(input) * weight`` -- the reference op ``ops.rms_norm(out, input,
+    weight, epsilon)`` (csrc/layernorm_kernels.cu:78-102)."""
+    dev, rows, hidden = _norm_args(input, weight, out)
+    with torch.cuda.device(dev):
+        st = _lib.lib().b200_w4a16_add_rms_norm(input.data_ptr(), None, weight.data_ptr(), out.data_ptr(),
+                                          None, float(epsilon), rows, hidden, _stream_ptr(dev))
+    _lib.check(st, "rms_norm")
+
+
+def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor,
+                       epsilon: float) -> None:
+    """In place: ``residual += input; input = rms_norm(residual) * weight`` -- the reference op
+    ``ops.fused_add_rms_norm(input, residual, weight, epsilon)``
+    (csrc/layernorm_kernels.cu:104-129)."""
+    dev, rows, hidden = _norm_args(input, weight, residual)
+    with torch.cuda.device(dev):
+        st = _lib.lib().b200_w4a16_add_rms_norm(input.data_ptr(), residual.data_ptr(), weight.data_ptr(),
+                                          input.data_ptr(), residual.data_ptr(), float(epsilon),
+                                          rows, hidden, _stream_ptr(dev))
+    _lib.check(st, "fused_add_rms_norm")

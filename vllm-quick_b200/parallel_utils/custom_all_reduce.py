@@ -76,6 +76,20 @@ class CustomAllreduce:
         _lib.check(st, "custom all-reduce")
         return out
 
+    def all_reduce_add_rms_norm(self, partial: torch.Tensor, residual: torch.Tensor,
+                                weight: torch.Tensor, eps: float) -> torch.Tensor:
+        """``residual += all_reduce(partial)`` (in place) and the RMSNorm of it (returned), one
+        kernel: all-reduce (linear.py:541-542) + fused_add_rms_norm (llama.py:205-222)."""
+        hidden = partial.shape[-1]
+        out = torch.empty_like(partial)
+        st = _lib.lib().b200_w4a16_allreduce_add_rms_norm(
+            self._regions, self.rank, self.world, partial.data_ptr(), residual.data_ptr(),
+            weight.data_ptr(), out.data_ptr(), residual.data_ptr(), float(eps),
+            partial.numel() // hidden, hidden, self.max_bytes, 1,
+            torch.cuda.current_stream(partial.device).cuda_stream)
+        _lib.check(st, "all-reduce + add + rms_norm")
+        return out
+
     def can_fuse(self, M: int, N: int, G: int) -> bool:
         """Fused row-parallel GEMM + all-reduce: decode batches whose output fits the slots."""
         return 0 < M <= 16 and G % 128 == 0 and N <= self.fused_out_features and N <= 128 * 128
@@ -119,6 +133,14 @@ def init_custom_all_reduce(max_bytes: int = 8 << 20, fused_out_features: int = 0
 def fused_handle(M: int, N: int, G: int) -> Optional["CustomAllreduce"]:
     """The handle if a row-parallel GEMM of this shape can run fused with its all-reduce."""
     if _handle is not None and _handle.can_fuse(M, N, G):
+        return _handle
+    return None
+
+
+def norm_handle(partial: torch.Tensor) -> Optional["CustomAllreduce"]:
+    """The handle if the all-reduce of this tensor can run fused with the add + RMSNorm after it."""
+    if (_handle is not None and _handle.should(partial) and partial.shape[-1] % 8 == 0
+            and partial.shape[-1] <= 16384):
         return _handle
     return None
 
