@@ -181,6 +181,30 @@ int b200_w4a16_gemm_allreduce(const uint16_t *x, const int32_t *qweight, const u
                               size_t max_message_bytes, int fused_out_features,
                               b200_stream_t stream);
 
+/* ---- SiLU-and-multiply behind the gate_up projection ----------------------
+ * out[rows, d] = half(silu(gate)) * up, silu(x) = half(float(x) / (1 + expf(-float(x)))), the
+ * reference's arithmetic.  paired == 0: in[rows, 2 d] = [gate | up] halves, the reference's
+ * layout.  paired == 1: every 16 input channels are 8 gate channels followed by the 8 up
+ * channels of the same indices (channel-paired gate_up weight, see below).  d % 8 == 0.
+ * Replaces: silu_and_mul(out, input)   (csrc/activation_kernels.cu:17-52; SiluAndMul.forward,
+ *           vllm/model_executor/layers/activation.py:14-38; llama.py:76-80). */
+int b200_w4a16_silu_and_mul(const uint16_t *in, uint16_t *out, size_t rows, int d, int paired,
+                            b200_stream_t stream);
+
+/* gate_up GEMM with the SiLU-and-multiply in its epilogue, decode batches (M <= 16,
+ * G % 128 == 0):  y[M, N/2] = silu_and_mul(x[M,K] . dequant(W[K,N])) without the [M, N]
+ * round trip and the second launch.  W (B200 layout), scales and qzeros hold the merged
+ * gate_up projection with its output channels PAIRED: channel block 16 j..16 j + 15 = gate
+ * channels 8 j..8 j + 7, then up channels 8 j..8 j + 7 -- a permutation of whole packed words
+ * done once at load time (MergedColumnParallelLinear.pair_gate_up, before the repack).  The
+ * two then sit in one thread's accumulator fragment.  Bit-identical to b200_w4a16_gemm on the
+ * same weights followed by b200_w4a16_silu_and_mul(paired = 1).  N % 16 == 0.
+ * Replaces: gate_up_proj + act_fn of LlamaMLP.forward (vllm/model_executor/models/llama.py:76-80). */
+int b200_w4a16_gemm_silu_mul(const uint16_t *x, const int32_t *qweight, const uint16_t *scales,
+                             const int32_t *qzeros, uint16_t *y, int M, int K, int N, int G,
+                             int split_k_hint, void *workspace, size_t workspace_bytes,
+                             b200_stream_t stream);
+
 /* ---- residual add + RMSNorm around the row-parallel linears ---------------
  * out[rows, hidden] = half(float(half(x)) * rsqrt(mean(x^2) + eps)) * weight,
  *   x = float(in) + float(residual_in)  (residual_in == NULL: x = in),

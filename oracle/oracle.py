@@ -269,3 +269,27 @@ def np_allreduce_f16(parts) -> np.ndarray:
     for p in parts:
         acc = acc + p.astype(np.float32)
     return acc.astype(np.float16)
+
+
+# ---- SiLU-and-multiply --------------------------------------------------------
+# np_silu_and_mul restates silu_and_mul_kernel (csrc/activation_kernels.cu:10-28):
+# half(float(x) / (1 + expf(-float(x)))) * y as a half multiply; the reference's own CPU
+# statement is SiluAndMul._forward = F.silu(x[..., :d]) * x[..., d:] (activation.py:25-28) and
+# its test accepts atol = rtol = 1e-3 for fp16 (tests/kernels/allclose_default.py).  expf is a
+# library function (device expf vs NumPy exp differ by an fp32 ulp at most): tolerance parity,
+# one fp16 ulp.  No vectors in the reference: "parity unpinned" beyond its tolerance.
+
+def np_silu_and_mul(x: np.ndarray) -> np.ndarray:
+    d = x.shape[-1] // 2
+    g = x[..., :d].astype(np.float32)
+    s = (g / (np.float32(1.0) + np.exp(-g, dtype=np.float32))).astype(np.float16)     # :10-14
+    return (s.astype(np.float32) * x[..., d:].astype(np.float32)).astype(np.float16)  # :26
+
+
+def np_pair_gate_up(a: np.ndarray, block: int) -> np.ndarray:
+    """Column permutation of a merged [gate | up] tensor into the paired order: blocks of
+    `block` columns (1 for packed int32 words, 8 for per-channel tensors) alternate gate / up."""
+    n = a.shape[-1] // block
+    half = np.arange(n // 2)
+    order = np.stack([half, half + n // 2], axis=1).reshape(-1)
+    return np.ascontiguousarray(a.reshape(a.shape[:-1] + (n, block))[..., order, :].reshape(a.shape))

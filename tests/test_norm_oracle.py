@@ -94,3 +94,36 @@ def test_rmsnorm_layer_host_logic():
         pkg.ops.fused_add_rms_norm(torch.zeros(2, 64, dtype=torch.float16),
                                    torch.zeros(2, 64, dtype=torch.float16),
                                    torch.ones(64, dtype=torch.float16), 1e-6)
+
+
+# ---- SiLU-and-multiply oracle ---------------------------------------------------
+
+@pytest.mark.parametrize("tokens,d", [(7, 512), (83, 5120)])
+def test_silu_restatement_matches_torch_forward(tokens, d):
+    """oracle.np_silu_and_mul (the kernel's arithmetic) against SiluAndMul._forward written
+    with torch ops (activation.py:25-28), at the reference's tolerance for fp16."""
+    rng = np.random.default_rng(d)
+    x = rng.standard_normal((tokens, 2 * d)).astype(np.float16)
+    tx = torch.from_numpy(x.copy())
+    ref = torch.nn.functional.silu(tx[..., :d].float()).half() * tx[..., d:]
+    got = oracle.np_silu_and_mul(x)
+    assert np.allclose(got.astype(np.float32), ref.float().numpy(), atol=1e-3, rtol=1e-3)
+
+
+def test_silu_known_answers_and_pairing():
+    x = np.array([[0.0, 65504.0, -65504.0, 1.0, 2.0, 3.0, 4.0, -5.0]], dtype=np.float16)
+    out = oracle.np_silu_and_mul(x)
+    assert out[0, 0] == 0 and np.isposinf(out[0, 1]) and out[0, 2] == 0
+    assert np.isclose(float(out[0, 3]), -5.0 * 1.0 / (1.0 + np.exp(-1.0)), rtol=2e-3)
+    # pairing is a permutation that alternates gate / up blocks and keeps each half's order
+    a = np.arange(32, dtype=np.int32).reshape(1, 32)
+    p = oracle.np_pair_gate_up(a, 8)
+    assert p[0].tolist() == list(range(0, 8)) + list(range(16, 24)) + list(range(8, 16)) + list(range(24, 32))
+    w = oracle.np_pair_gate_up(np.arange(6, dtype=np.int32).reshape(1, 6), 1)
+    assert w[0].tolist() == [0, 3, 1, 4, 2, 5]
+    # dequantize commutes with the pairing: channel-paired packed tensors are the paired matrix
+    _, qw, s, qz = oracle.make_inputs(1, 256, 128, 128, seed=3)
+    W = oracle.np_dequantize(qw, s, qz)
+    Wp = oracle.np_dequantize(oracle.np_pair_gate_up(qw, 1), oracle.np_pair_gate_up(s, 8),
+                              oracle.np_pair_gate_up(qz, 1))
+    assert np.array_equal(Wp.view(np.uint16), oracle.np_pair_gate_up(W, 8).view(np.uint16))

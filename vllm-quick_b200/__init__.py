@@ -11,6 +11,7 @@ from . import parallel_linear, parallel_utils  # noqa: F401
 from .parallel_linear import (ColumnParallelLinear, MergedColumnParallelLinear,  # noqa: F401
                               QKVParallelLinear, ReplicatedLinear, RowParallelLinear)
 from .layernorm import RMSNorm  # noqa: F401
+from .activation import LlamaMLP, SiluAndMul  # noqa: F401
 from .mixtral_moe import MixtralMLP, MixtralMoE  # noqa: F401
 from .quantization import (AWQConfig, AWQLinearMethod, QuantizationConfig, QuickConfig,  # noqa: F401
                            QuickLinearMethod, get_quantization_config)

@@ -141,10 +141,44 @@ int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* s
                                nullptr, workspace, workspace_bytes, stream);
 }
 
+static int gemm_impl(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
+                     const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G, int layout,
+                     int split_k_hint, const int32_t* gate, int act, void* workspace,
+                     size_t workspace_bytes, b200_stream_t stream);
+
 int b200_w4a16_gemm_gated(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
                           const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
                           int layout, int split_k_hint, const int32_t* gate, void* workspace,
                           size_t workspace_bytes, b200_stream_t stream) {
+  return gemm_impl(x, qweight, scales, qzeros, y, M, K, N, G, layout, split_k_hint, gate, 0,
+                   workspace, workspace_bytes, stream);
+}
+
+int b200_w4a16_gemm_silu_mul(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
+                             const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
+                             int split_k_hint, void* workspace, size_t workspace_bytes,
+                             b200_stream_t stream) {
+  if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
+  if (M > b200::kDecodeMaxTokens || G % b200::kTileK != 0 || N % 16 != 0) return B200_ERR_BAD_SHAPE;
+  return gemm_impl(x, qweight, scales, qzeros, y, M, K, N, G, B200_LAYOUT_B200, split_k_hint,
+                   nullptr, 1, workspace, workspace_bytes, stream);
+}
+
+int b200_w4a16_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int d, int paired,
+                            b200_stream_t stream) {
+  if (d <= 0 || d % 8 != 0 || (paired != 0 && paired != 1)) return B200_ERR_BAD_SHAPE;
+  if (rows == 0) return B200_OK;
+  if (!in || !out || !aligned16(in) || !aligned16(out)) return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_silu_and_mul(in, out, rows, d, paired, reinterpret_cast<cudaStream_t>(stream));
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+static int gemm_impl(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
+                     const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G, int layout,
+                     int split_k_hint, const int32_t* gate, int act, void* workspace,
+                     size_t workspace_bytes, b200_stream_t stream) {
   if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
   if (gate && (reinterpret_cast<uintptr_t>(gate) & 3u)) return B200_ERR_BAD_ARG;
   if (layout != B200_LAYOUT_AWQ && layout != B200_LAYOUT_B200) return B200_ERR_BAD_ARG;
@@ -164,6 +198,7 @@ int b200_w4a16_gemm_gated(const uint16_t* x, const int32_t* qweight, const uint1
   if (layout == B200_LAYOUT_AWQ) need += align_up(b200_w4a16_repacked_words(K, N) * 4, 256);
   if (!workspace || workspace_bytes < need || !aligned16(workspace)) return B200_ERR_WORKSPACE;
   if (plan.ws_counter_bytes > kCounterBytes) return B200_ERR_WORKSPACE;
+  if (act && plan.kind != b200::kKindDecode) return B200_ERR_BAD_SHAPE;
 
   uint8_t* ws = static_cast<uint8_t*>(workspace);
   int* counters = reinterpret_cast<int*>(ws);
@@ -182,7 +217,7 @@ int b200_w4a16_gemm_gated(const uint16_t* x, const int32_t* qweight, const uint1
   }
   int e = plan.kind == b200::kKindDecode
               ? b200::launch_decode(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters,
-                                    pdl, s, nullptr, gate)
+                                    pdl, s, nullptr, gate, act)
               : b200::launch_gemm(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters,
                                   pdl, s);
   if (e != 0) return cuda_fail(e);

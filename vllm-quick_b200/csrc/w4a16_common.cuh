@@ -350,4 +350,15 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* addr) {
   return v;
 }
 
+// silu(gate) * up on two GEMM outputs, exactly as the unfused pair computes it: the GEMM rounds
+// both to fp16, then csrc/activation_kernels.cu:10-27 of the reference --
+// (half)(float(x) / (1 + expf(-float(x)))) * y, a half multiply.  Shared by the standalone
+// kernel and the decode GEMM's epilogue so the two agree bit for bit.
+__device__ __forceinline__ uint16_t silu_mul_f16(float gate, float up) {
+  const __half gh = __float2half_rn(gate), uh = __float2half_rn(up);
+  const float gf = __half2float(gh);
+  const __half sh = __float2half_rn(gf / (1.0f + expf(-gf)));
+  return __half_as_ushort(__hmul(sh, uh));
+}
+
 }  // namespace b200

@@ -99,6 +99,9 @@ struct DecodeParams {
   int T, P;
   int Gdiv;     // K blocks per quantization group (G / 128)
   int flags;
+  // 1: the weight's channels are paired (every 16-channel block = 8 gate channels, then the 8
+  // up channels of the same indices) and the epilogue writes silu(gate) * up into y[M, N/2].
+  int act;
   // Routed-expert gate (b200_w4a16_gemm_gated): when non-null and *gate == 0 no token of the
   // batch is routed to this expert -- the launch streams nothing and zero-fills y.
   const int* gate;
@@ -380,6 +383,23 @@ w4a16_decode_kernel(const DecodeParams p) {
     int own_nt = -1, own_slot = 0, own_last = 0;              // tile this CTA finishes, if any
     bool own_local = false;                                   // its own piece is handed over in shared memory
     auto write_y = [&](int nt, const float (&v)[2][MT][4]) {
+      if (p.act) {
+        // rows g / g + 8 of the MMA tile are the gate / up channel of one output channel: both
+        // live in this thread (e, e + 2)
+        const int NO = p.N >> 1;
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          const int no = ((nt * kTileN + cw_ * 32 + 16 * b) >> 1) + g;
+#pragma unroll
+          for (int i = 0; i < MT; ++i)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int m = 8 * i + 2 * t + e;
+              if (m < p.M && no < NO) p.y[(size_t)m * NO + no] = silu_mul_f16(v[b][i][e], v[b][i][e + 2]);
+            }
+        }
+        return;
+      }
 #pragma unroll
       for (int b = 0; b < 2; ++b) {
         const int n_lo = nt * kTileN + cbase + 16 * b;
@@ -652,6 +672,14 @@ w4a16_decode_kernel(const DecodeParams p) {
         const int n0 = own_nt * kTileN + (et >> 5) * 32 + ((et & 31) >> 2) + 16 * eb;
         const int m0 = 8 * ei + 2 * (et & 3);
         const float v[4] = {sum.x, sum.y, sum.z, sum.w};
+        if (p.act) {
+          const int NO = p.N >> 1;
+          const int no = ((own_nt * kTileN + (et >> 5) * 32 + 16 * eb) >> 1) + ((et & 31) >> 2);
+#pragma unroll
+          for (int k = 0; k < 2; ++k)
+            if (m0 + k < p.M && no < NO) p.y[(size_t)(m0 + k) * NO + no] = silu_mul_f16(v[k], v[k + 2]);
+          continue;
+        }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const int m = m0 + (k & 1), nn = n0 + (k >> 1) * 8;
@@ -825,8 +853,9 @@ void fill_decode_plan(int M, GemmPlan* plan) {
 int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                   const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
                   const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
-                  cudaStream_t stream, const FusedArParams* ar, const int* gate) {
+                  cudaStream_t stream, const FusedArParams* ar, const int* gate, int act) {
   DecodeParams prm;
+  prm.act = act;
   prm.qw = reinterpret_cast<const uint32_t*>(qw_b200);
   prm.x = x;
   prm.scales = scales;

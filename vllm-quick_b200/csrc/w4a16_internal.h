@@ -60,7 +60,12 @@ int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* sca
                   const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
                   const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
                   cudaStream_t stream, const FusedArParams* ar = nullptr,
-                  const int* gate = nullptr);
+                  const int* gate = nullptr, int act = 0);
+
+// silu(x[:, :d]) * x[:, d:] (paired == 0: the reference's [gate | up] halves) or, paired == 1,
+// the channel-paired order the fused gate_up GEMM uses (every 16 channels = 8 gate + 8 up).
+int launch_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int d, int paired,
+                        cudaStream_t stream);
 
 // NVLink peer-memory all-reduce (w4a16_allreduce.cu).  Region = header + two data slots.
 // Region layout: [0, 2 KiB) flags[block][rank] | [2 KiB, +256) per-block epochs |

@@ -34,6 +34,7 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include "w4a16_common.cuh"
 #include "w4a16_internal.h"
 
 namespace cg = cooperative_groups;
@@ -100,7 +101,7 @@ add_rmsnorm_kernel(const NormParams p) {
   const uint32_t ch = crank * kNormThreads + threadIdx.x;     // chunk of the row this thread owns
   const bool active = ch < p.chunks_per_row;
 
-  __shared__ float s_warp[kNormThreads / 32];
+  __shared__ float s_warp[2 * (kNormThreads / 32)];             // double buffered by row parity
   __shared__ float s_part[2];                                  // per-CTA partial, double buffered
   __shared__ uint32_t s_epoch;
 
@@ -153,26 +154,41 @@ add_rmsnorm_kernel(const NormParams p) {
   uint4 wv = make_uint4(0, 0, 0, 0);
   if (active) wv = p.weight[ch];
 
+  // Raw operands of one row chunk: the next row's are requested before the current row's
+  // statistics meet at the cluster barrier (twice the bytes in flight per thread).
+  constexpr int NV = WORLD > 0 ? WORLD : 1;
+  uint4 cur[NV], nxt[NV];
+  uint4 cur_res = make_uint4(0, 0, 0, 0), nxt_res = make_uint4(0, 0, 0, 0);
+  auto fetch = [&](uint32_t r, uint4 (&v)[NV], uint4& res) {
+    const size_t c = (size_t)r * p.chunks_per_row + ch;
+    if constexpr (WORLD > 0) {
+#pragma unroll
+      for (int q = 0; q < WORLD; ++q)
+        v[q] = ld_volatile_v4(reinterpret_cast<const uint4*>(p.region[q] + slot_off) + c);
+    } else {
+      v[0] = p.in[c];
+    }
+    if (p.residual_in) res = p.residual_in[c];
+  };
+  if (active && row0 < p.rows) fetch(row0, cur, cur_res);
+
   uint32_t it = 0;
   for (uint32_t r = row0; r < p.rows; r += row_step, ++it) {
     const size_t c = (size_t)r * p.chunks_per_row + ch;
+    if (active && r + row_step < p.rows) fetch(r + row_step, nxt, nxt_res);
     float x[8];
     uint4 xr = make_uint4(0, 0, 0, 0);      // half(x): the residual stream
     float ssq = 0.f;
     if (active) {
       uint4 xin;
       if constexpr (WORLD > 0) {
-        uint4 v[WORLD];
-#pragma unroll
-        for (int q = 0; q < WORLD; ++q)
-          v[q] = ld_volatile_v4(reinterpret_cast<const uint4*>(p.region[q] + slot_off) + c);
         float acc[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[i] = 0.f;
 #pragma unroll
         for (int q = 0; q < WORLD; ++q) {
           float f[8];
-          unpack8(f, v[q]);
+          unpack8(f, cur[q]);
 #pragma unroll
           for (int i = 0; i < 8; ++i) acc[i] += f[i];
         }
@@ -180,12 +196,12 @@ add_rmsnorm_kernel(const NormParams p) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) xh[i] = __floats2half2_rn(acc[2 * i], acc[2 * i + 1]);
       } else {
-        xin = p.in[c];
+        xin = cur[0];
       }
       unpack8(x, xin);
       if (p.residual_in) {
         float res[8];
-        unpack8(res, p.residual_in[c]);
+        unpack8(res, cur_res);
 #pragma unroll
         for (int i = 0; i < 8; ++i) x[i] += res[i];
         __half2* h = reinterpret_cast<__half2*>(&xr);
@@ -201,12 +217,12 @@ add_rmsnorm_kernel(const NormParams p) {
     // fixed-order tree: lanes, warps, cluster ranks
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
-    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = ssq;
+    if ((threadIdx.x & 31) == 0) s_warp[(it & 1) * (kNormThreads / 32) + (threadIdx.x >> 5)] = ssq;
     __syncthreads();
     if (threadIdx.x == 0) {
       float t = 0.f;
 #pragma unroll
-      for (int w = 0; w < kNormThreads / 32; ++w) t += s_warp[w];
+      for (int w = 0; w < kNormThreads / 32; ++w) t += s_warp[(it & 1) * (kNormThreads / 32) + w];
       s_part[it & 1] = t;
     }
     cluster.sync();
@@ -224,6 +240,9 @@ add_rmsnorm_kernel(const NormParams p) {
         oh[i] = __hmul2(__floats2half2_rn(xf[2 * i] * inv, xf[2 * i + 1] * inv), wh[i]);
       p.out[c] = o;
     }
+#pragma unroll
+    for (int q = 0; q < NV; ++q) cur[q] = nxt[q];
+    cur_res = nxt_res;
   }
   cluster.sync();   // nobody leaves while a peer CTA may still read its partial
 }
@@ -266,6 +285,46 @@ int fill_params(NormParams* prm, const uint16_t* in, const uint16_t* residual_in
 
 }  // namespace
 
+namespace {
+
+// out[r, n..n+7] = silu(gate) * up, 16 bytes out per thread.  Plain: gate = in[r, n], up =
+// in[r, d + n] (csrc/activation_kernels.cu:17-28).  Paired: gate = in[r, 2 n'..], the 16-byte
+// chunk 2 j of the row, up = chunk 2 j + 1 -- the order the gate_up GEMM produces when its
+// weight was channel-paired for the fused epilogue (used for batches above the decode kernel).
+__global__ void __launch_bounds__(256)
+silu_and_mul_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, size_t total_chunks,
+                    uint32_t chunks_per_row, int paired) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const size_t r = i / chunks_per_row;
+    const uint32_t j = (uint32_t)(i - r * chunks_per_row);
+    const uint4* row = in + r * 2 * chunks_per_row;
+    const uint4 gv = paired ? row[2 * j] : row[j];
+    const uint4 uv = paired ? row[2 * j + 1] : row[chunks_per_row + j];
+    float gf[8], uf[8];
+    unpack8(gf, gv);
+    unpack8(uf, uv);
+    uint4 o;
+    uint16_t* oh = reinterpret_cast<uint16_t*>(&o);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) oh[k] = silu_mul_f16(gf[k], uf[k]);
+    out[i] = o;
+  }
+}
+
+}  // namespace
+
+int launch_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int d, int paired,
+                        cudaStream_t stream) {
+  const size_t total = rows * (size_t)(d / 8);
+  size_t blocks = (total + 255) / 256;
+  if (blocks > (size_t)kMaxCtas * 8) blocks = (size_t)kMaxCtas * 8;
+  silu_and_mul_kernel<<<(unsigned)blocks, 256, 0, stream>>>(
+      reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), total, (uint32_t)(d / 8), paired);
+  return (int)cudaGetLastError();
+}
+
 int norm_max_hidden() { return kNormMaxCluster * kNormThreads * 8; }
 
 int launch_add_rmsnorm(const uint16_t* in, const uint16_t* residual_in, const uint16_t* weight,
@@ -273,8 +332,8 @@ int launch_add_rmsnorm(const uint16_t* in, const uint16_t* residual_in, const ui
                        cudaStream_t stream) {
   NormParams prm;
   const int cluster = fill_params(&prm, in, residual_in, weight, out, residual_out, eps, rows, hidden);
-  // 4 resident 256-thread CTAs per SM are plenty for a row-per-cluster kernel
-  size_t row_clusters = (size_t)(kMaxCtas * 4 / cluster);
+  // up to 8 resident 256-thread CTAs per SM: bytes in flight are what this kernel lives on
+  size_t row_clusters = (size_t)(kMaxCtas * 8 / cluster);
   if (row_clusters > rows) row_clusters = rows;
   return launch_norm<0>(prm, cluster, (int)row_clusters, stream);
 }

@@ -253,3 +253,61 @@ def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torc
                                           input.data_ptr(), residual.data_ptr(), float(epsilon),
                                           rows, hidden, _stream_ptr(dev))
     _lib.check(st, "fused_add_rms_norm")
+
+
+def _silu(out: torch.Tensor, input: torch.Tensor, paired: int) -> None:
+    dev = _check_cuda(out, input)
+    if out.dtype != torch.float16 or input.dtype != torch.float16:
+        raise ValueError("the B200 activation kernels take float16 tensors only")
+    d = input.shape[-1] // 2
+    if input.shape[-1] != 2 * d or out.shape != input.shape[:-1] + (d,):
+        raise ValueError("silu_and_mul: out must be [..., d] for input [..., 2 * d]")
+    with torch.cuda.device(dev):
+        st = _lib.lib().b200_w4a16_silu_and_mul(input.data_ptr(), out.data_ptr(),
+                                                input.numel() // (2 * d) if d else 0, d, paired,
+                                                _stream_ptr(dev))
+    _lib.check(st, "silu_and_mul")
+
+
+def silu_and_mul(out: torch.Tensor, input: torch.Tensor) -> None:
+    """``out = silu(input[..., :d]) * input[..., d:]`` -- the reference op
+    ``ops.silu_and_mul(out, input)`` (csrc/activation_kernels.cu:17-52)."""
+    _silu(out, input, 0)
+
+
+def silu_and_mul_paired(out: torch.Tensor, input: torch.Tensor) -> None:
+    """The same on the channel-paired order a paired gate_up weight produces (every 16
+    channels = 8 gate + the 8 up channels of the same indices)."""
+    _silu(out, input, 1)
+
+
+def quick_gemm_silu_mul(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_factors: torch.Tensor,
+                        zeros: torch.Tensor) -> torch.Tensor:
+    """``silu_and_mul(in_feats @ dequant(W))`` for a channel-paired, interleaved gate_up weight:
+    one kernel for decode batches (``b200_w4a16_gemm_silu_mul``), GEMM + paired activation
+    kernel above them.  Returns ``[M, N / 2]``."""
+    M = in_feats.shape[0]
+    N = scaling_factors.shape[1]
+    K = in_feats.shape[1]
+    G = K // scaling_factors.shape[0] if scaling_factors.shape[0] else 0
+    L = _lib.lib()
+    if M == 0 or G == 0 or G % 128 != 0 or L.b200_w4a16_gemm_variant(M, K, N, G) != 1:
+        full = quick_gemm(in_feats, kernel, scaling_factors, zeros, PACK_FACTOR)
+        out = torch.empty((M, N // 2), dtype=torch.float16, device=in_feats.device)
+        silu_and_mul_paired(out, full)
+        return out
+    dev = _check_cuda(in_feats, kernel, scaling_factors, zeros)
+    if in_feats.dtype != torch.float16 or scaling_factors.dtype != torch.float16:
+        raise ValueError("in_feats and scaling_factors must be float16")
+    if kernel.dtype != torch.int32 or zeros.dtype != torch.int32:
+        raise ValueError("kernel and zeros must be int32")
+    if kernel.numel() != L.b200_w4a16_repacked_words(K, N) or zeros.shape != (K // G, N // PACK_FACTOR):
+        raise ValueError("kernel / zeros do not match the B200 layout for these shapes")
+    out = torch.empty((M, N // 2), dtype=torch.float16, device=dev)
+    with torch.cuda.device(dev):
+        ws = _workspace(dev, L.b200_w4a16_workspace_bytes(M, K, N, LAYOUT_B200))
+        st = L.b200_w4a16_gemm_silu_mul(in_feats.data_ptr(), kernel.data_ptr(),
+                                        scaling_factors.data_ptr(), zeros.data_ptr(), out.data_ptr(),
+                                        M, K, N, G, 0, ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _lib.check(st, "w4a16 gemm + silu_and_mul")
+    return out

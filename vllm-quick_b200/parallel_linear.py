@@ -192,6 +192,20 @@ class MergedColumnParallelLinear(ColumnParallelLinear):
     def _pieces(self):
         return list(enumerate(self.output_sizes))
 
+    def forward_silu_and_mul(self, input_: torch.Tensor) -> torch.Tensor:
+        """``SiluAndMul()(self(input_)[0])`` -- the two lines of LlamaMLP.forward
+        (vllm/model_executor/models/llama.py:77-78) as one call, so that the activation can run
+        in the GEMM's epilogue.  The first call channel-pairs the loaded weight; from then on
+        the layer serves this method only."""
+        if len(self.output_sizes) != 2 or self.output_sizes[0] != self.output_sizes[1]:
+            raise ValueError("forward_silu_and_mul needs a [gate, up] pair of equal widths")
+        if self.bias is not None or self.gather_output:
+            raise ValueError("forward_silu_and_mul: no bias, no gathered output")
+        method = self.linear_method
+        if not hasattr(method, "apply_weights_silu_and_mul"):
+            raise ValueError("the linear method has no fused SiLU-and-multiply path")
+        return method.apply_weights_silu_and_mul(self.linear_weights, input_)
+
     def _piece_plan(self, piece_id):
         if not 0 <= piece_id < len(self.output_sizes):
             raise AssertionError(f"shard id {piece_id} out of range")

@@ -110,6 +110,40 @@ class AWQLinearMethod(LinearMethodBase):
             weights["qweight_layout"] = LAYOUT_INTERLEAVED
         return qweight
 
+    def pair_gate_up(self, weights: Dict[str, Any]) -> None:
+        """Channel-pair a merged [gate | up] projection for the fused SiLU-and-multiply
+        epilogue: packed word column 2 j = gate word j, 2 j + 1 = up word j (a permutation of
+        whole int32 columns of qweight / qzeros and of 8-column blocks of scales, done once on
+        the checkpoint layout, before the interleave).  Idempotent."""
+        if weights.get("gate_up_paired", False):
+            return
+        qweight, qzeros, scales = weights["qweight"], weights["qzeros"], weights["scales"]
+        if weights.get("qweight_layout", LAYOUT_CHECKPOINT) != LAYOUT_CHECKPOINT:
+            qweight.data = ops.quick_unrepack(qweight.data, qweight.shape[0] if qweight.dim() == 2
+                                              else scales.shape[0] * self.quant_config.group_size,
+                                              scales.shape[1])
+            weights["qweight_layout"] = LAYOUT_CHECKPOINT
+        words = scales.shape[1] // self.quant_config.pack_factor
+        if words % 2 != 0:
+            raise ValueError("gate and up projections must have the same, 8-aligned, width")
+        half = torch.arange(words // 2, device=qweight.device)
+        order = torch.stack([half, half + words // 2], dim=1).reshape(-1)
+        qweight.data = qweight.data.reshape(-1, words)[:, order].contiguous()
+        qzeros.data = qzeros.data[:, order].contiguous()
+        groups = scales.shape[0]
+        scales.data = scales.data.reshape(groups, words, -1)[:, order].reshape(groups, -1).contiguous()
+        weights["gate_up_paired"] = True
+
+    def apply_weights_silu_and_mul(self, weights: Dict[str, Any], x: torch.Tensor) -> torch.Tensor:
+        """``SiluAndMul(apply_weights(weights, x))`` for a merged gate_up projection
+        (llama.py:76-80), the activation in the GEMM's epilogue for decode batches."""
+        self.pair_gate_up(weights)
+        qweight = self._interleave_once(weights)
+        scales = weights["scales"]
+        reshaped_x = x.reshape(-1, x.shape[-1])
+        out = ops.quick_gemm_silu_mul(reshaped_x, qweight, scales, weights["qzeros"])
+        return out.reshape(x.shape[:-1] + (scales.shape[-1] // 2, ))
+
     def apply_weights_all_reduce(self, weights: Dict[str, Any],
                                  x: torch.Tensor) -> Optional[torch.Tensor]:
         """Row-parallel hook: GEMM on this rank's K shard fused with the tensor-parallel
@@ -133,6 +167,9 @@ class AWQLinearMethod(LinearMethodBase):
                       bias: Optional[torch.Tensor] = None) -> torch.Tensor:
         scales = weights["scales"]
         qzeros = weights["qzeros"]
+        if weights.get("gate_up_paired", False):
+            raise RuntimeError("this gate_up weight was channel-paired for the fused activation: "
+                               "call apply_weights_silu_and_mul / forward_silu_and_mul")
         qweight = self._interleave_once(weights)
         pack_factor = self.quant_config.pack_factor
         out_shape = x.shape[:-1] + (scales.shape[-1], )
