@@ -204,8 +204,11 @@ def _rank_main(rank, world, port, q):
             r_two = residual.clone()
             two, r_two = norm(pu.tensor_model_parallel_all_reduce(partial), r_two)
             r_one = residual.clone()
-            one, r_one = norm.forward_reduced(partial, r_one)
+            one, r_one = norm.forward_reduced(partial, r_one)        # dispatch (fused up to 32 rows)
             assert torch.equal(one, two) and torch.equal(r_one, r_two), (rows, hidden)
+            r_k = residual.clone()                                   # the fused kernel itself, any rows
+            k = pu.custom_all_reduce._handle.all_reduce_add_rms_norm(partial, r_k, norm.weight.data, 1e-5)
+            assert torch.equal(k, two) and torch.equal(r_k, r_two), (rows, hidden)
             ref = partial.float()
             dist.all_reduce(ref)
             assert torch.allclose(r_one.float(), ref + residual.float(), rtol=2e-3, atol=2e-2)

@@ -27,6 +27,7 @@ from .parallel_state import (get_tensor_model_parallel_group, get_tensor_model_p
                              get_tensor_model_parallel_world_size)
 
 _MAX_WORLD = 8
+_FUSED_NORM_MAX_ROWS = 32
 _handle: Optional["CustomAllreduce"] = None
 
 
@@ -139,8 +140,11 @@ def fused_handle(M: int, N: int, G: int) -> Optional["CustomAllreduce"]:
 
 def norm_handle(partial: torch.Tensor) -> Optional["CustomAllreduce"]:
     """The handle if the all-reduce of this tensor can run fused with the add + RMSNorm after it."""
-    if (_handle is not None and _handle.should(partial) and partial.shape[-1] % 8 == 0
-            and partial.shape[-1] <= 16384):
+    hidden = partial.shape[-1]
+    # decode batches: above ~32 rows the 64-block grid of the fused kernel (one NVLink barrier
+    # flag set per block) is slower than all-reduce + norm as two kernels (scripts/norm_bench.py)
+    if (_handle is not None and _handle.should(partial) and hidden % 8 == 0 and hidden <= 16384
+            and partial.numel() // hidden <= _FUSED_NORM_MAX_ROWS):
         return _handle
     return None
 
