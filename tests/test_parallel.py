@@ -131,6 +131,74 @@ def _free_port():
         return s.getsockname()[1]
 
 
+def _tiles(oracle, qw):
+    """AWQ qweight [K, N/8] (torch) -> pre-interleaved checkpoint tensor [N/128, K/128, 2048]."""
+    K, N = qw.shape[0], qw.shape[1] * 8
+    return torch.from_numpy(oracle.np_b200_repack(qw.numpy()).reshape(N // 128, K // 128, 2048).copy())
+
+
+def _pre_interleaved_checks(pkg, pl, oracle, rank, world):
+    """a ``"version": "quick"`` checkpoint (qweight already in the B200 layout,
+    [N/128, K/128, 2048]) loads shard by shard through the same loaders; what every rank ends
+    up with is, word for word, the interleave of its own AWQ shard."""
+    cfg = pkg.QuickConfig.from_config({"w_bit": 4, "q_group_size": G, "zero_point": True,
+                                       "version": "QUICK"})
+    assert cfg.pre_interleaved and not pkg.QuickConfig(4, G, True).pre_interleaved
+    with pytest.raises(ValueError):
+        pkg.QuickConfig(4, G, True, "gemv")
+    method = cfg.get_linear_method()
+    K, N = 512, 512
+    qw, s, qz = _checkpoint(oracle, K, N, 21)
+    nh, kh = N // world, K // world
+    col = pl.ColumnParallelLinear(K, N, bias=False, linear_method=method, params_dtype=torch.float16)
+    assert tuple(col.qweight.shape) == (nh // 128, K // 128, 2048)
+    assert col.linear_weights["qweight_layout"] == "b200"
+    _load(col, _tiles(oracle, qw), s, qz)
+    assert torch.equal(col.qweight.data, _tiles(oracle, qw[:, rank * nh // 8:(rank + 1) * nh // 8].contiguous()))
+    assert torch.equal(col.scales.data, s[:, rank * nh:(rank + 1) * nh])
+    row = pl.RowParallelLinear(K, N, bias=False, linear_method=method, params_dtype=torch.float16)
+    _load(row, _tiles(oracle, qw), s, qz)
+    assert torch.equal(row.qweight.data, _tiles(oracle, qw[rank * kh:(rank + 1) * kh].contiguous()))
+    assert torch.equal(row.qzeros.data, qz[rank * kh // G:(rank + 1) * kh // G])
+    # merged gate_up from two checkpoint tensors, and from one already-fused tensor
+    a, c = _checkpoint(oracle, K, 256, 22), _checkpoint(oracle, K, 256, 23)
+    want = _tiles(oracle, torch.cat([a[0][:, rank * 128 // 8 * (2 // world):][:, :256 // world // 8],
+                                     c[0][:, rank * 128 // 8 * (2 // world):][:, :256 // world // 8]], 1).contiguous())
+    gu = pl.MergedColumnParallelLinear(K, [256, 256], bias=False, linear_method=method, params_dtype=torch.float16)
+    for sid, t in ((0, a), (1, c)):
+        _load(gu, _tiles(oracle, t[0]), t[1], t[2], shard_id=sid)
+    assert torch.equal(gu.qweight.data, want)
+    gu2 = pl.MergedColumnParallelLinear(K, [256, 256], bias=False, linear_method=method, params_dtype=torch.float16)
+    _load(gu2, _tiles(oracle, torch.cat([a[0], c[0]], 1).contiguous()), torch.cat([a[1], c[1]], 1),
+          torch.cat([a[2], c[2]], 1))
+    assert torch.equal(gu2.qweight.data, want) and torch.equal(gu2.scales.data, gu.scales.data)
+    # QKV, kv heads replicated when tp >= kv heads; head size 128 keeps pieces on tile borders
+    qkv = pl.QKVParallelLinear(K, 128, 2, 1, bias=False, linear_method=method, params_dtype=torch.float16)
+    qt, kt, vt = _checkpoint(oracle, K, 256, 24), _checkpoint(oracle, K, 128, 25), _checkpoint(oracle, K, 128, 26)
+    for sid, t in (("q", qt), ("k", kt), ("v", vt)):
+        _load(qkv, _tiles(oracle, t[0]), t[1], t[2], shard_id=sid)
+    qn = 256 // world
+    want = _tiles(oracle, torch.cat([qt[0][:, rank * qn // 8:(rank + 1) * qn // 8] if world > 1 else qt[0],
+                                     kt[0], vt[0]], 1).contiguous())
+    assert torch.equal(qkv.qweight.data, want)
+    # pieces that do not fall on tile borders are refused, as is a misaligned partition
+    bad = pl.QKVParallelLinear(K, 64, 4, 1, bias=False, linear_method=method, params_dtype=torch.float16) \
+        if world == 1 else None
+    with pytest.raises((ValueError, AssertionError)):
+        if bad is None:
+            pl.QKVParallelLinear(K, 64, 2, 2, bias=False, linear_method=method, params_dtype=torch.float16)
+        else:
+            bad.scales.weight_loader(bad.scales, _checkpoint(oracle, K, 64, 27)[1], "k")     # fine: per channel
+            bad.qweight.weight_loader(bad.qweight, _tiles(oracle, _checkpoint(oracle, K, 128, 27)[0]), "k")
+    with pytest.raises(ValueError):
+        pl.ColumnParallelLinear(K, 192 * world, bias=False, linear_method=method, params_dtype=torch.float16)
+
+
+def test_pre_interleaved_checkpoint_world_of_one():
+    pkg, pl, pu, oracle = _mods()
+    _pre_interleaved_checks(pkg, pl, oracle, 0, 1)
+
+
 def _worker(rank, world, port, q):
     try:
         os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -207,6 +275,7 @@ def _worker(rank, world, port, q):
 
         with pytest.raises(ValueError):
             pl.RowParallelLinear(128, N, bias=False, linear_method=method)  # K/tp not a multiple of G
+        _pre_interleaved_checks(pkg, pl, oracle, rank, world)
         pu.destroy_model_parallel()
         assert pu.get_tensor_model_parallel_world_size() == 1
         dist.destroy_process_group()

@@ -42,6 +42,9 @@ def divide(numerator: int, denominator: int) -> int:
 def _packed(param: torch.Tensor, dim: Optional[int], value: int) -> int:
     """``value`` output features expressed in elements of ``param`` along ``dim``."""
     if dim is not None and getattr(param, "packed_dim", None) == dim:
+        if value % param.pack_factor != 0:
+            raise AssertionError(f"{value} output features do not fall on a boundary of the "
+                                 f"packed dimension (pack factor {param.pack_factor})")
         return value // param.pack_factor
     return value
 
