@@ -181,6 +181,20 @@ int b200_w4a16_gemm_allreduce(const uint16_t *x, const int32_t *qweight, const u
                               size_t max_message_bytes, int fused_out_features,
                               b200_stream_t stream);
 
+/* ---- routed mixture-of-experts: token gather / weighted scatter-add --------
+ * out[i, :] = x[idx[i], :] for i < rows (idx: int32 device array of token rows).
+ * acc[idx[i], :] = half(float(acc[idx[i], :]) + float(half(float(y[i, :]) * w[i]))), w fp32 --
+ * the arithmetic of `current_hidden_states.mul_(expert_weights)` followed by
+ * `final_hidden_states.add_(current_hidden_states)`.  The rows named by idx must be distinct
+ * (a token selects an expert at most once).  hidden % 8 == 0.
+ * Replaces: the dense all-tokens expert loop of MixtralMoE.forward
+ *           (vllm/model_executor/models/mixtral_quant.py:143-157) together with
+ *           b200_w4a16_gemm on the gathered [rows, hidden] batch. */
+int b200_w4a16_moe_gather(const uint16_t *x, const int32_t *idx, uint16_t *out, size_t rows,
+                          int hidden, b200_stream_t stream);
+int b200_w4a16_moe_scatter_add(const uint16_t *y, const int32_t *idx, const float *w,
+                               uint16_t *acc, size_t rows, int hidden, b200_stream_t stream);
+
 /* ---- SiLU-and-multiply behind the gate_up projection ----------------------
  * out[rows, d] = half(silu(gate)) * up, silu(x) = half(float(x) / (1 + expf(-float(x)))), the
  * reference's arithmetic.  paired == 0: in[rows, 2 d] = [gate | up] halves, the reference's

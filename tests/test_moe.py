@@ -178,3 +178,71 @@ def test_moe_block_parity_and_idle_expert_skipping(pkg, oracle, cuda_lib, tokens
         graph.replay()
         st.synchronize()
     assert torch.equal(static_y, dense_moe(x2))
+
+
+@pytest.mark.gpu
+def test_moe_gather_scatter_kernels(pkg, oracle, cuda_lib):
+    """b200_w4a16_moe_gather / _scatter_add against NumPy: gather is a byte copy (exact), the
+    scatter follows mul_ (fp32 product, one rounding) then add_ (fp16 sum, one rounding)
+    of mixtral_quant.py:152-157 -- exact as well."""
+    from gpu_util import bits, to_dev
+    rng = np.random.default_rng(0)
+    T, H = 300, 1024
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    idx = np.sort(rng.choice(T, 77, replace=False)).astype(np.int32)
+    g = pkg.ops.moe_gather(to_dev(x), torch.from_numpy(idx).cuda())
+    assert np.array_equal(bits(g), x[idx].view(np.uint16))
+    acc = rng.standard_normal((T, H)).astype(np.float16)
+    y = rng.standard_normal((77, H)).astype(np.float16)
+    w = rng.random(77).astype(np.float32)
+    dacc = to_dev(acc)
+    pkg.ops.moe_scatter_add(dacc, to_dev(y), torch.from_numpy(idx).cuda(), torch.from_numpy(w).cuda())
+    want = acc.copy()
+    scaled = (y.astype(np.float32) * w[:, None]).astype(np.float16)
+    want[idx] = (acc[idx].astype(np.float32) + scaled.astype(np.float32)).astype(np.float16)
+    assert np.array_equal(bits(dacc), want.view(np.uint16))
+    # empty selection, bad arguments
+    e = torch.zeros(0, dtype=torch.int32, device="cuda")
+    assert pkg.ops.moe_gather(to_dev(x), e).shape == (0, H)
+    with pytest.raises(ValueError):
+        pkg.ops.moe_gather(to_dev(x), torch.zeros(3, dtype=torch.int64, device="cuda"))
+    s = torch.cuda.current_stream().cuda_stream
+    assert cuda_lib.b200_w4a16_moe_gather(dacc.data_ptr(), e.data_ptr(), dacc.data_ptr(), 1, 12, s) == pkg._lib.B200_ERR_BAD_SHAPE
+    assert cuda_lib.b200_w4a16_moe_gather(None, e.data_ptr(), dacc.data_ptr(), 1, 16, s) == pkg._lib.B200_ERR_BAD_ARG
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tokens", [17, 64, 333])
+def test_moe_block_routed_matches_dense_and_reference(pkg, oracle, cuda_lib, tokens):
+    """Prefill batches take the gather -> per-expert M_e -> scatter-add path; it must agree
+    with the dense all-tokens loop (the reference's structure) and with the CPU block."""
+    torch.set_default_dtype(torch.float16)
+    try:
+        method = pkg.QuickConfig(4, G, True).get_linear_method()
+        with torch.device("cuda"):
+            moe = pkg.MixtralMoE(_cfg(), method)
+            dense_moe = pkg.MixtralMoE(_cfg(), method, skip_idle_experts=False)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    dense = _fill(moe, oracle, seed=9)
+    _fill(dense_moe, oracle, seed=9)
+    g = torch.Generator().manual_seed(tokens)
+    x = torch.randn(1, tokens, 256, generator=g).half()
+    want, _ = _reference_block(x.reshape(tokens, 256).float(), moe.gate.weight.data.float().cpu(),
+                               dense, list(range(8)), 2, True)
+    calls = []
+    orig = pkg.ops.moe_gather
+    pkg.ops.moe_gather = lambda *a: (calls.append(a[1].numel()), orig(*a))[1]
+    try:
+        got = moe(x.cuda()).reshape(tokens, 256)
+    finally:
+        pkg.ops.moe_gather = orig
+    assert sum(calls) == 2 * tokens and len(calls) <= 8        # top-2: every token in two batches
+    got_dense = dense_moe(x.cuda()).reshape(tokens, 256)
+    # the expert GEMMs run at another batch size (other tile plan, other fp32 summation order):
+    # agreement to the GEMM bar, not bits
+    ref = got_dense.float()
+    assert bool(((got.float() - ref).abs() <= 2e-2 * ref.abs().clamp(min=1.0)).all())
+    err = (got.float().cpu() - want).abs()
+    assert bool((err <= 2e-2 * want.abs().clamp(min=1.0)).all())
+    assert torch.equal(got, moe(x.cuda()).reshape(tokens, 256))   # deterministic

@@ -367,6 +367,31 @@ int b200_w4a16_allreduce(void* const* regions, int rank, int world, const uint16
   return e == 0 ? B200_OK : cuda_fail(e);
 }
 
+int b200_w4a16_moe_gather(const uint16_t* x, const int32_t* idx, uint16_t* out, size_t rows,
+                          int hidden, b200_stream_t stream) {
+  if (hidden <= 0 || hidden % 8 != 0) return B200_ERR_BAD_SHAPE;
+  if (rows == 0) return B200_OK;
+  if (!x || !idx || !out || !aligned16(x) || !aligned16(out) || (reinterpret_cast<uintptr_t>(idx) & 3u))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_moe_gather(x, idx, out, rows, hidden, reinterpret_cast<cudaStream_t>(stream));
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+int b200_w4a16_moe_scatter_add(const uint16_t* y, const int32_t* idx, const float* w, uint16_t* acc,
+                               size_t rows, int hidden, b200_stream_t stream) {
+  if (hidden <= 0 || hidden % 8 != 0) return B200_ERR_BAD_SHAPE;
+  if (rows == 0) return B200_OK;
+  if (!y || !idx || !w || !acc || !aligned16(y) || !aligned16(acc) ||
+      (reinterpret_cast<uintptr_t>(idx) & 3u) || (reinterpret_cast<uintptr_t>(w) & 3u))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_moe_scatter_add(y, idx, w, acc, rows, hidden, reinterpret_cast<cudaStream_t>(stream));
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
 int b200_w4a16_add_rms_norm(const uint16_t* in, const uint16_t* residual_in, const uint16_t* weight,
                       uint16_t* out, uint16_t* residual_out, float eps, size_t rows, int hidden,
                       b200_stream_t stream) {

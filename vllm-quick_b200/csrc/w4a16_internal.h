@@ -94,6 +94,13 @@ int launch_allreduce_add_rmsnorm(void* const* regions, int rank, int world, cons
                                  int hidden, size_t max_message_bytes, int barrier,
                                  cudaStream_t stream);
 
+// Routed mixture-of-experts plumbing (w4a16_moe.cu): out[i] = x[idx[i]];
+// acc[idx[i]] = half(acc[idx[i]] + half(y[i] * w[i])).  hidden % 8 == 0, idx rows distinct.
+int launch_moe_gather(const uint16_t* x, const int32_t* idx, uint16_t* out, size_t rows, int hidden,
+                      cudaStream_t stream);
+int launch_moe_scatter_add(const uint16_t* y, const int32_t* idx, const float* w, uint16_t* acc,
+                           size_t rows, int hidden, cudaStream_t stream);
+
 // B200_TRACE builds: device buffer of 148 x 8 x 64 uint32 timestamps (nullptr = off).
 void set_trace_buffer(uint32_t* dev);
 uint32_t* trace_buffer();

@@ -125,10 +125,38 @@ class MixtralMoE(nn.Module):
                             torch.ones_like(selected_experts.reshape(-1), dtype=torch.int32))
         return routing_weights, selected_experts, counts
 
+    # Batches above the decode kernel's 16 tokens, outside CUDA-graph capture (prefill): the
+    # tokens of each local expert are gathered, the expert runs on M_e rows instead of T, the
+    # weighted result is scattered back.  Needs the per-expert counts on the host
+    # (one sync), which a captured decode step cannot have -- that one keeps the dense loop with
+    # device-side gates below.
+    routed_min_tokens = 17
+
+    def _forward_routed(self, hidden_states, routing_weights, selected_experts):
+        final = torch.zeros_like(hidden_states)
+        for expert_idx in self.expert_indicies:
+            mask = (selected_experts == expert_idx)
+            rows = mask.any(dim=-1).nonzero(as_tuple=False).reshape(-1)       # host sync: M_e
+            if rows.numel() == 0:
+                continue
+            idx = rows.to(torch.int32)
+            weights = (routing_weights * mask).sum(dim=-1)[rows].contiguous()  # fp32 [M_e]
+            out = self.experts[expert_idx](ops.moe_gather(hidden_states, idx))
+            ops.moe_scatter_add(final, out, idx, weights)
+        return final
+
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
         batch_size, sequence_length, hidden_dim = hidden_states.shape
         hidden_states = hidden_states.view(-1, hidden_dim)
         routing_weights, selected_experts, counts = self.route(hidden_states)
+
+        if (self.skip_idle_experts and hidden_states.is_cuda
+                and hidden_states.shape[0] >= self.routed_min_tokens
+                and not torch.cuda.is_current_stream_capturing()):
+            final_hidden_states = self._forward_routed(hidden_states.contiguous(), routing_weights,
+                                                       selected_experts)
+            return tensor_model_parallel_all_reduce(final_hidden_states).view(
+                batch_size, sequence_length, hidden_dim)
 
         final_hidden_states = None
         for expert_idx in self.expert_indicies:

@@ -311,3 +311,32 @@ def quick_gemm_silu_mul(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_fa
                                         M, K, N, G, 0, ws.data_ptr(), ws.numel(), _stream_ptr(dev))
     _lib.check(st, "w4a16 gemm + silu_and_mul")
     return out
+
+
+def moe_gather(x: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """``x[idx]`` for an int32 index vector: the tokens routed to one expert as a dense batch."""
+    dev = _check_cuda(x, idx)
+    if x.dtype != torch.float16 or idx.dtype != torch.int32 or x.dim() != 2 or idx.dim() != 1:
+        raise ValueError("moe_gather: x [tokens, hidden] float16, idx [rows] int32")
+    out = torch.empty((idx.numel(), x.shape[1]), dtype=torch.float16, device=dev)
+    with torch.cuda.device(dev):
+        st = _lib.lib().b200_w4a16_moe_gather(x.data_ptr(), idx.data_ptr(), out.data_ptr(),
+                                              idx.numel(), x.shape[1], _stream_ptr(dev))
+    _lib.check(st, "moe_gather")
+    return out
+
+
+def moe_scatter_add(acc: torch.Tensor, y: torch.Tensor, idx: torch.Tensor, w: torch.Tensor) -> None:
+    """In place: ``acc[idx[i]] += half(y[i] * w[i])`` (w fp32; rows of idx distinct)."""
+    dev = _check_cuda(acc, y, idx, w)
+    if (acc.dtype != torch.float16 or y.dtype != torch.float16 or idx.dtype != torch.int32
+            or w.dtype != torch.float32):
+        raise ValueError("moe_scatter_add: acc / y float16, idx int32, w float32")
+    if y.dim() != 2 or acc.dim() != 2 or y.shape[1] != acc.shape[1] or idx.numel() != y.shape[0] \
+            or w.numel() != y.shape[0]:
+        raise ValueError("moe_scatter_add: y [rows, hidden], idx [rows], w [rows], acc [tokens, hidden]")
+    with torch.cuda.device(dev):
+        st = _lib.lib().b200_w4a16_moe_scatter_add(y.data_ptr(), idx.data_ptr(), w.data_ptr(),
+                                                   acc.data_ptr(), y.shape[0], y.shape[1],
+                                                   _stream_ptr(dev))
+    _lib.check(st, "moe_scatter_add")
