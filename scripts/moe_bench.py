@@ -41,6 +41,9 @@ def main():
     ap.add_argument("--layers", type=int, default=3)
     ap.add_argument("--experts-per-rank", type=int, default=8)
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--prefill", action="store_true",
+                    help="eager launches (no CUDA graph): batches above 16 tokens take the routed "
+                         "gather -> per-expert GEMM -> scatter-add path; compared with the dense loop")
     args = ap.parse_args()
     hidden, ffn, experts, top_k = 4096, 14336, 8, 2
     cfg = types.SimpleNamespace(num_local_experts=experts, num_experts_per_tok=top_k,
@@ -61,6 +64,31 @@ def main():
     for moe in blocks:
         fill(moe, gen)
     bytes_expert = 3 * (hidden * ffn // 2 + (hidden // G) * ffn * 5 // 2)   # packed + scales + zeros (approx.)
+    if args.prefill:
+        for moe in blocks:
+            moe.routed_min_tokens = 17        # show the crossover; the product threshold is 512
+        for T in (int(v) for v in args.tokens.split(",")):
+            x = torch.randn(1, T, hidden, device="cuda", generator=gen).half()
+            res = {}
+            for skip in (True, False):
+                for moe in blocks:
+                    moe.skip_idle_experts = skip
+                for moe in blocks:
+                    moe(x)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(args.iters):
+                    for moe in blocks:
+                        moe(x)
+                e1.record()
+                torch.cuda.synchronize()
+                res[skip] = e0.elapsed_time(e1) * 1e3 / (args.iters * len(blocks))
+            print(json.dumps({"mode": "prefill_eager", "tokens": T, "local_experts": args.experts_per_rank,
+                              "us_per_block_routed": round(res[True], 1),
+                              "us_per_block_dense_reference_loop": round(res[False], 1),
+                              "speedup": round(res[False] / res[True], 2)}), flush=True)
+        return
     for T in (int(v) for v in args.tokens.split(",")):
         x = torch.randn(1, T, hidden, device="cuda", generator=gen).half()
         res = {}

@@ -50,7 +50,10 @@ def single():
         peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     except Exception:
         pass
-    for rows, hidden in [(16, 4096), (16, 8192), (256, 8192), (4096, 8192), (16384, 8192)]:
+    shapes = [(16, 4096), (16, 8192), (256, 8192), (4096, 8192), (16384, 8192)]
+    if len(sys.argv) > 1:                      # e.g. 4096x8192 (ncu captures)
+        shapes = [tuple(int(v) for v in a.split("x")) for a in sys.argv[1:]]
+    for rows, hidden in shapes:
         nbytes = rows * hidden * 2
         sets = max(2, min(64, (512 << 20) // (4 * nbytes) + 1))
         xs = [torch.randn(rows, hidden, device="cuda").half() for _ in range(sets)]

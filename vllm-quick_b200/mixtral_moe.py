@@ -125,24 +125,28 @@ class MixtralMoE(nn.Module):
                             torch.ones_like(selected_experts.reshape(-1), dtype=torch.int32))
         return routing_weights, selected_experts, counts
 
-    # Batches above the decode kernel's 16 tokens, outside CUDA-graph capture (prefill): the
-    # tokens of each local expert are gathered, the expert runs on M_e rows instead of T, the
-    # weighted result is scattered back.  Needs the per-expert counts on the host
-    # (one sync), which a captured decode step cannot have -- that one keeps the dense loop with
-    # device-side gates below.
-    routed_min_tokens = 17
+    # Large batches outside CUDA-graph capture (prefill): the tokens of each local expert are
+    # gathered, the expert runs on M_e rows instead of T, the weighted result is scattered back
+    # (SURVEY 8f-4).  Needs the per-expert counts on the host (ONE sync per block), which a
+    # captured decode step cannot have -- that one keeps the dense loop with device-side gates
+    # below.  Threshold: where the routed path overtakes the dense loop on B200
+    # (profiles/r1e_moe_prefill_bench.jsonl).
+    routed_min_tokens = 512
 
-    def _forward_routed(self, hidden_states, routing_weights, selected_experts):
+    def _forward_routed(self, hidden_states, routing_weights, selected_experts, counts):
         final = torch.zeros_like(hidden_states)
-        for expert_idx in self.expert_indicies:
-            mask = (selected_experts == expert_idx)
-            rows = mask.any(dim=-1).nonzero(as_tuple=False).reshape(-1)       # host sync: M_e
-            if rows.numel() == 0:
-                continue
-            idx = rows.to(torch.int32)
-            weights = (routing_weights * mask).sum(dim=-1)[rows].contiguous()  # fp32 [M_e]
-            out = self.experts[expert_idx](ops.moe_gather(hidden_states, idx))
-            ops.moe_scatter_add(final, out, idx, weights)
+        order = torch.argsort(selected_experts.reshape(-1), stable=True)   # by expert, token order kept
+        tokens = (order // self.top_k).to(torch.int32)
+        weights = routing_weights.reshape(-1)[order].contiguous()          # fp32, one per (token, choice)
+        host_counts = counts.tolist()                                      # the one host sync
+        start = 0
+        for expert_idx in range(self.num_total_experts):
+            n = host_counts[expert_idx]
+            if n and expert_idx in self.expert_indicies:
+                idx = tokens[start:start + n]
+                out = self.experts[expert_idx](ops.moe_gather(hidden_states, idx))
+                ops.moe_scatter_add(final, out, idx, weights[start:start + n])
+            start += n
         return final
 
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
@@ -154,7 +158,7 @@ class MixtralMoE(nn.Module):
                 and hidden_states.shape[0] >= self.routed_min_tokens
                 and not torch.cuda.is_current_stream_capturing()):
             final_hidden_states = self._forward_routed(hidden_states.contiguous(), routing_weights,
-                                                       selected_experts)
+                                                       selected_experts, counts)
             return tensor_model_parallel_all_reduce(final_hidden_states).view(
                 batch_size, sequence_length, hidden_dim)
 
