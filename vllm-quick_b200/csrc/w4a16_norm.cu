@@ -33,6 +33,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "w4a16_common.cuh"
 #include "w4a16_internal.h"
@@ -90,7 +91,11 @@ __device__ __forceinline__ void unpack8(float (&f)[8], const uint4& v) {
 }
 
 // WORLD == 0: plain (x read from `in`); WORLD >= 1: x = all-reduce over WORLD ranks of `in`.
-template <int WORLD>
+// CPT: 16-byte chunks per thread (chunk j of a thread = cta_base + j * 256 + tid: coalesced).
+// CPT = 1 spreads a row over the most CTAs (decode: few rows, latency); CPT = 4 puts up to
+// 8192 halfs in ONE CTA, so the per-row cluster barrier (a membar + barrier pair that was 40 %
+// of the stall samples, profiles/r1e_ncu_full_add_rmsnorm.txt) shrinks to a __syncthreads.
+template <int WORLD, int CPT>
 __global__ void __launch_bounds__(kNormThreads)
 add_rmsnorm_kernel(const NormParams p) {
   cg::cluster_group cluster = cg::this_cluster();
@@ -98,8 +103,13 @@ add_rmsnorm_kernel(const NormParams p) {
   const uint32_t crank = cluster.block_rank();
   const uint32_t row0 = blockIdx.x / csize;
   const uint32_t row_step = gridDim.x / csize;
-  const uint32_t ch = crank * kNormThreads + threadIdx.x;     // chunk of the row this thread owns
-  const bool active = ch < p.chunks_per_row;
+  uint32_t ch[CPT];                                            // chunks of the row this thread owns
+  bool active[CPT];
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) {
+    ch[j] = (crank * CPT + j) * kNormThreads + threadIdx.x;
+    active[j] = ch[j] < p.chunks_per_row;
+  }
 
   __shared__ float s_warp[2 * (kNormThreads / 32)];             // double buffered by row parity
   __shared__ float s_part[2];                                  // per-CTA partial, double buffered
@@ -109,6 +119,7 @@ add_rmsnorm_kernel(const NormParams p) {
 
   uint32_t slot_off = 0;
   if constexpr (WORLD > 0) {
+    static_assert(WORLD == 0 || CPT == 1, "the fused variant maps one chunk per thread");
     uint8_t* mine = p.region[p.rank];
     uint32_t* my_flags = reinterpret_cast<uint32_t*>(mine) + blockIdx.x * kArMaxRanks;
     uint32_t* epochs = reinterpret_cast<uint32_t*>(mine + kArFlagBytes);
@@ -117,10 +128,10 @@ add_rmsnorm_kernel(const NormParams p) {
     const uint32_t epoch = s_epoch;
     slot_off = kArHeaderBytes + (epoch & 1u) * p.slot_bytes;
     // 1. stage this thread's chunk of every row of this cluster into the own slot
-    if (active) {
+    if (active[0]) {
       uint4* my_slot = reinterpret_cast<uint4*>(mine + slot_off);
       for (uint32_t r = row0; r < p.rows; r += row_step) {
-        const size_t c = (size_t)r * p.chunks_per_row + ch;
+        const size_t c = (size_t)r * p.chunks_per_row + ch[0];
         my_slot[c] = p.in[c];
       }
     }
@@ -151,35 +162,44 @@ add_rmsnorm_kernel(const NormParams p) {
       epochs[threadIdx.x] = epoch;
   }
 
-  uint4 wv = make_uint4(0, 0, 0, 0);
-  if (active) wv = p.weight[ch];
-
-  // Raw operands of one row chunk: the next row's are requested before the current row's
-  // statistics meet at the cluster barrier (twice the bytes in flight per thread).
-  constexpr int NV = WORLD > 0 ? WORLD : 1;
-  uint4 cur[NV], nxt[NV];
-  uint4 cur_res = make_uint4(0, 0, 0, 0), nxt_res = make_uint4(0, 0, 0, 0);
-  auto fetch = [&](uint32_t r, uint4 (&v)[NV], uint4& res) {
-    const size_t c = (size_t)r * p.chunks_per_row + ch;
-    if constexpr (WORLD > 0) {
+  uint4 wv[CPT];
 #pragma unroll
-      for (int q = 0; q < WORLD; ++q)
-        v[q] = ld_volatile_v4(reinterpret_cast<const uint4*>(p.region[q] + slot_off) + c);
-    } else {
-      v[0] = p.in[c];
+  for (int j = 0; j < CPT; ++j) wv[j] = active[j] ? p.weight[ch[j]] : make_uint4(0, 0, 0, 0);
+
+  // Raw operands of one row: the next row's are requested before the current row's statistics
+  // meet at the barrier (twice the bytes in flight per thread).
+  constexpr int NV = WORLD > 0 ? WORLD : 1;
+  uint4 cur[CPT][NV], nxt[CPT][NV];
+  uint4 cur_res[CPT], nxt_res[CPT];
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) cur_res[j] = nxt_res[j] = make_uint4(0, 0, 0, 0);
+  auto fetch = [&](uint32_t r, uint4 (&v)[CPT][NV], uint4 (&res)[CPT]) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      if (!active[j]) continue;
+      const size_t c = (size_t)r * p.chunks_per_row + ch[j];
+      if constexpr (WORLD > 0) {
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q)
+          v[j][q] = ld_volatile_v4(reinterpret_cast<const uint4*>(p.region[q] + slot_off) + c);
+      } else {
+        v[j][0] = p.in[c];
+      }
+      if (p.residual_in) res[j] = p.residual_in[c];
     }
-    if (p.residual_in) res = p.residual_in[c];
   };
-  if (active && row0 < p.rows) fetch(row0, cur, cur_res);
+  if (row0 < p.rows) fetch(row0, cur, cur_res);
 
   uint32_t it = 0;
   for (uint32_t r = row0; r < p.rows; r += row_step, ++it) {
-    const size_t c = (size_t)r * p.chunks_per_row + ch;
-    if (active && r + row_step < p.rows) fetch(r + row_step, nxt, nxt_res);
-    float x[8];
-    uint4 xr = make_uint4(0, 0, 0, 0);      // half(x): the residual stream
+    if (r + row_step < p.rows) fetch(r + row_step, nxt, nxt_res);
+    uint4 xr[CPT];                          // half(x): the residual stream
     float ssq = 0.f;
-    if (active) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      xr[j] = make_uint4(0, 0, 0, 0);
+      if (!active[j]) continue;
+      float x[8];
       uint4 xin;
       if constexpr (WORLD > 0) {
         float acc[8];
@@ -188,7 +208,7 @@ add_rmsnorm_kernel(const NormParams p) {
 #pragma unroll
         for (int q = 0; q < WORLD; ++q) {
           float f[8];
-          unpack8(f, cur[q]);
+          unpack8(f, cur[j][q]);
 #pragma unroll
           for (int i = 0; i < 8; ++i) acc[i] += f[i];
         }
@@ -196,58 +216,68 @@ add_rmsnorm_kernel(const NormParams p) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) xh[i] = __floats2half2_rn(acc[2 * i], acc[2 * i + 1]);
       } else {
-        xin = cur[0];
+        xin = cur[j][0];
       }
       unpack8(x, xin);
       if (p.residual_in) {
         float res[8];
-        unpack8(res, cur_res);
+        unpack8(res, cur_res[j]);
 #pragma unroll
         for (int i = 0; i < 8; ++i) x[i] += res[i];
-        __half2* h = reinterpret_cast<__half2*>(&xr);
+        __half2* h = reinterpret_cast<__half2*>(&xr[j]);
 #pragma unroll
         for (int i = 0; i < 4; ++i) h[i] = __floats2half2_rn(x[2 * i], x[2 * i + 1]);
       } else {
-        xr = xin;
+        xr[j] = xin;
       }
 #pragma unroll
       for (int i = 0; i < 8; ++i) ssq = fmaf(x[i], x[i], ssq);
-      if (p.residual_out) p.residual_out[c] = xr;
+      if (p.residual_out) p.residual_out[(size_t)r * p.chunks_per_row + ch[j]] = xr[j];
     }
-    // fixed-order tree: lanes, warps, cluster ranks
+    // fixed-order tree: chunks of the thread, lanes, warps, cluster ranks
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
     if ((threadIdx.x & 31) == 0) s_warp[(it & 1) * (kNormThreads / 32) + (threadIdx.x >> 5)] = ssq;
     __syncthreads();
-    if (threadIdx.x == 0) {
-      float t = 0.f;
-#pragma unroll
-      for (int w = 0; w < kNormThreads / 32; ++w) t += s_warp[(it & 1) * (kNormThreads / 32) + w];
-      s_part[it & 1] = t;
-    }
-    cluster.sync();
     float total = 0.f;
-    for (uint32_t j = 0; j < csize; ++j) total += *cluster.map_shared_rank(&s_part[it & 1], j);
+    if (csize == 1) {                       // the whole row lives in this CTA
+#pragma unroll
+      for (int w = 0; w < kNormThreads / 32; ++w) total += s_warp[(it & 1) * (kNormThreads / 32) + w];
+    } else {
+      if (threadIdx.x == 0) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < kNormThreads / 32; ++w) t += s_warp[(it & 1) * (kNormThreads / 32) + w];
+        s_part[it & 1] = t;
+      }
+      cluster.sync();
+      for (uint32_t j = 0; j < csize; ++j) total += *cluster.map_shared_rank(&s_part[it & 1], j);
+    }
     const float inv = rsqrtf(total * p.inv_hidden + p.eps);
-    if (active) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      if (!active[j]) continue;
       float xf[8];
-      unpack8(xf, xr);
+      unpack8(xf, xr[j]);
       uint4 o;
       __half2* oh = reinterpret_cast<__half2*>(&o);
-      const __half2* wh = reinterpret_cast<const __half2*>(&wv);
+      const __half2* wh = reinterpret_cast<const __half2*>(&wv[j]);
 #pragma unroll
       for (int i = 0; i < 4; ++i)
         oh[i] = __hmul2(__floats2half2_rn(xf[2 * i] * inv, xf[2 * i + 1] * inv), wh[i]);
-      p.out[c] = o;
+      p.out[(size_t)r * p.chunks_per_row + ch[j]] = o;
     }
 #pragma unroll
-    for (int q = 0; q < NV; ++q) cur[q] = nxt[q];
-    cur_res = nxt_res;
+    for (int j = 0; j < CPT; ++j) {
+#pragma unroll
+      for (int q = 0; q < NV; ++q) cur[j][q] = nxt[j][q];
+      cur_res[j] = nxt_res[j];
+    }
   }
-  cluster.sync();   // nobody leaves while a peer CTA may still read its partial
+  if (csize > 1) cluster.sync();   // nobody leaves while a peer CTA may still read its partial
 }
 
-template <int WORLD>
+template <int WORLD, int CPT = 1>
 int launch_norm(const NormParams& prm, int cluster, int row_clusters, cudaStream_t stream) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(cluster * row_clusters));
@@ -261,7 +291,7 @@ int launch_norm(const NormParams& prm, int cluster, int row_clusters, cudaStream
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return (int)cudaLaunchKernelEx(&cfg, add_rmsnorm_kernel<WORLD>, prm);
+  return (int)cudaLaunchKernelEx(&cfg, add_rmsnorm_kernel<WORLD, CPT>, prm);
 }
 
 int fill_params(NormParams* prm, const uint16_t* in, const uint16_t* residual_in,
@@ -331,8 +361,21 @@ int launch_add_rmsnorm(const uint16_t* in, const uint16_t* residual_in, const ui
                        uint16_t* out, uint16_t* residual_out, float eps, size_t rows, int hidden,
                        cudaStream_t stream) {
   NormParams prm;
-  const int cluster = fill_params(&prm, in, residual_in, weight, out, residual_out, eps, rows, hidden);
-  // up to 8 resident 256-thread CTAs per SM: bytes in flight are what this kernel lives on
+  int cluster = fill_params(&prm, in, residual_in, weight, out, residual_out, eps, rows, hidden);
+  static const size_t cpt4_min_rows = [] {
+    const char* e = getenv("B200_NORM_CPT4_MIN_ROWS");      // tuning override
+    return e ? (size_t)atol(e) : (size_t)17;
+  }();
+  if (rows >= cpt4_min_rows) {
+    // above decode batches: whole-row CTAs, four chunks per thread, (almost) no cluster
+    // barrier -- faster from 32 rows up (2.4 vs 2.8 us) and 0.91-0.97 of the copy bandwidth
+    // at prefill sizes (profiles/r1e_norm_bench.jsonl)
+    cluster = (cluster + 3) / 4;
+    size_t row_clusters = (size_t)(kMaxCtas * 4 / cluster);
+    if (row_clusters > rows) row_clusters = rows;
+    return launch_norm<0, 4>(prm, cluster, (int)row_clusters, stream);
+  }
+  // few rows (decode): one chunk per thread, a row spread over a cluster
   size_t row_clusters = (size_t)(kMaxCtas * 8 / cluster);
   if (row_clusters > rows) row_clusters = rows;
   return launch_norm<0>(prm, cluster, (int)row_clusters, stream);
