@@ -100,7 +100,7 @@ allreduce_oneshot_kernel(const ArParams p) {
       uint32_t* peer_flag = reinterpret_cast<uint32_t*>(p.region[q]) + blockIdx.x * kArMaxRanks + p.rank;
       st_release_sys(peer_flag, epoch);
       const long long t0 = clock64();
-      while (ld_acquire_sys(my_flags + q) != epoch) {
+      while ((int32_t)(ld_acquire_sys(my_flags + q) - epoch) < 0) {     // a peer may already be a call ahead
         if (clock64() - t0 > 4000000000ll) {
           printf("b200_w4a16: all-reduce barrier timeout rank %d block %d peer %d\n", p.rank,
                  blockIdx.x, q);

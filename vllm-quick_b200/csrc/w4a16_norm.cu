@@ -111,8 +111,8 @@ add_rmsnorm_kernel(const NormParams p) {
     active[j] = ch[j] < p.chunks_per_row;
   }
 
-  __shared__ float s_warp[2 * (kNormThreads / 32)];             // double buffered by row parity
-  __shared__ float s_part[2];                                  // per-CTA partial, double buffered
+  __shared__ float s_warp[2 * CPT * (kNormThreads / 32)];       // [row parity][group][warp]
+  __shared__ float s_part[2 * CPT];                            // [row parity][group]: per-CTA partials
   __shared__ uint32_t s_epoch;
 
   asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -145,7 +145,7 @@ add_rmsnorm_kernel(const NormParams p) {
             reinterpret_cast<uint32_t*>(p.region[q]) + blockIdx.x * kArMaxRanks + p.rank;
         st_release_sys(peer_flag, epoch);
         const long long t0 = clock64();
-        while (ld_acquire_sys(my_flags + q) != epoch) {
+        while ((int32_t)(ld_acquire_sys(my_flags + q) - epoch) < 0) {     // a peer may already be a call ahead
           if (clock64() - t0 > 4000000000ll) {
             printf("b200_w4a16: all-reduce+norm barrier timeout rank %d block %d peer %d\n",
                    p.rank, blockIdx.x, q);
@@ -194,10 +194,11 @@ add_rmsnorm_kernel(const NormParams p) {
   for (uint32_t r = row0; r < p.rows; r += row_step, ++it) {
     if (r + row_step < p.rows) fetch(r + row_step, nxt, nxt_res);
     uint4 xr[CPT];                          // half(x): the residual stream
-    float ssq = 0.f;
+    float ssq[CPT];
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
       xr[j] = make_uint4(0, 0, 0, 0);
+      ssq[j] = 0.f;
       if (!active[j]) continue;
       float x[8];
       uint4 xin;
@@ -231,27 +232,44 @@ add_rmsnorm_kernel(const NormParams p) {
         xr[j] = xin;
       }
 #pragma unroll
-      for (int i = 0; i < 8; ++i) ssq = fmaf(x[i], x[i], ssq);
+      for (int i = 0; i < 8; ++i) ssq[j] = fmaf(x[i], x[i], ssq[j]);
       if (p.residual_out) p.residual_out[(size_t)r * p.chunks_per_row + ch[j]] = xr[j];
     }
-    // fixed-order tree: chunks of the thread, lanes, warps, cluster ranks
+    // ONE summation order for every shape of this kernel (so the fused and the standalone
+    // variants agree bit for bit whatever CPT / cluster size they run with): the row is cut
+    // into groups of 256 chunks (group = crank * CPT + j); inside a group the 8 values of a
+    // thread, then the lane tree, then the 8 warps in order; then the groups in order.
+    float* sw = s_warp + (it & 1) * (CPT * (kNormThreads / 32));
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
-    if ((threadIdx.x & 31) == 0) s_warp[(it & 1) * (kNormThreads / 32) + (threadIdx.x >> 5)] = ssq;
+    for (int j = 0; j < CPT; ++j) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) ssq[j] += __shfl_xor_sync(0xffffffffu, ssq[j], o);
+      if ((threadIdx.x & 31) == 0) sw[j * (kNormThreads / 32) + (threadIdx.x >> 5)] = ssq[j];
+    }
     __syncthreads();
     float total = 0.f;
     if (csize == 1) {                       // the whole row lives in this CTA
 #pragma unroll
-      for (int w = 0; w < kNormThreads / 32; ++w) total += s_warp[(it & 1) * (kNormThreads / 32) + w];
-    } else {
-      if (threadIdx.x == 0) {
+      for (int j = 0; j < CPT; ++j) {
         float t = 0.f;
 #pragma unroll
-        for (int w = 0; w < kNormThreads / 32; ++w) t += s_warp[(it & 1) * (kNormThreads / 32) + w];
-        s_part[it & 1] = t;
+        for (int w = 0; w < kNormThreads / 32; ++w) t += sw[j * (kNormThreads / 32) + w];
+        total += t;
+      }
+    } else {
+      float* sp = s_part + (it & 1) * CPT;
+      if (threadIdx.x < CPT) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < kNormThreads / 32; ++w) t += sw[threadIdx.x * (kNormThreads / 32) + w];
+        sp[threadIdx.x] = t;
       }
       cluster.sync();
-      for (uint32_t j = 0; j < csize; ++j) total += *cluster.map_shared_rank(&s_part[it & 1], j);
+      for (uint32_t k = 0; k < csize; ++k) {
+        const float* rp = cluster.map_shared_rank(sp, k);
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) total += rp[j];
+      }
     }
     const float inv = rsqrtf(total * p.inv_hidden + p.eps);
 #pragma unroll
