@@ -243,6 +243,8 @@ def main():
         if not args.nccl_allreduce:
             pu.custom_all_reduce.init_custom_all_reduce(
                 max_bytes=M * hidden * 2, fused_out_features=0 if args.unfused_allreduce else hidden)
+            if args.unfused_allreduce:      # this mode means "the one-shot kernel", whatever the size policy says
+                pu.custom_all_reduce._handle.oneshot_max_bytes = 1 << 30
     method = pkg.QuickConfig(4, GROUP, True).get_linear_method()
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
 

@@ -148,6 +148,8 @@ def _rank_main(rank, world, port, q):
         pu = pkg.parallel_utils
         pu.initialize_model_parallel(world)
         pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2, fused_out_features=8192)
+        assert pu.custom_all_reduce._handle.oneshot_max_bytes in (128 << 10, 512 << 10)
+        pu.custom_all_reduce._handle.oneshot_max_bytes = 1 << 30     # exercise the kernel at every size
         g = torch.Generator(device=dev).manual_seed(100 + rank)
         for shape in [(1, 8192), (16, 8192), (256, 8192), (3, 4096)]:
             x = torch.randn(shape, device=dev, generator=g).half()

@@ -41,6 +41,12 @@ class CustomAllreduce:
         if not 2 <= self.world <= _MAX_WORLD:
             raise ValueError(f"custom all-reduce supports 2..{_MAX_WORLD} ranks, got {self.world}")
         self.max_bytes = (int(max_bytes) + 255) // 256 * 256
+        # Above this the one-shot pull (every rank reads every peer's whole message) loses to
+        # NCCL's ring / NVLS on B200 (profiles/r1e_allreduce_norm_bench_tp{2,8}.jsonl: TP = 2
+        # wins at 16 KiB and loses at 256 KiB; TP = 8 wins at 256 KiB and loses at 1 MiB) --
+        # the same split the reference makes between its one- and two-stage kernels
+        # (csrc/custom_all_reduce.cuh:520-531).  A tuning value: tests and benches may raise it.
+        self.oneshot_max_bytes = (128 << 10) if self.world <= 2 else (512 << 10)
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.fused_out_features = int(fused_out_features)
         region_bytes = L.b200_w4a16_ar_region_bytes(self.max_bytes, self.world, self.fused_out_features)
@@ -67,7 +73,8 @@ class CustomAllreduce:
     def should(self, t: torch.Tensor) -> bool:
         nbytes = t.numel() * t.element_size()
         return (t.is_cuda and t.dtype == torch.float16 and t.is_contiguous()
-                and nbytes % 16 == 0 and 0 < nbytes <= self.max_bytes and t.data_ptr() % 16 == 0)
+                and nbytes % 16 == 0 and 0 < nbytes <= min(self.max_bytes, self.oneshot_max_bytes)
+                and t.data_ptr() % 16 == 0)
 
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         out = torch.empty_like(t)
@@ -141,10 +148,11 @@ def fused_handle(M: int, N: int, G: int) -> Optional["CustomAllreduce"]:
 def norm_handle(partial: torch.Tensor) -> Optional["CustomAllreduce"]:
     """The handle if the all-reduce of this tensor can run fused with the add + RMSNorm after it."""
     hidden = partial.shape[-1]
-    # decode batches: above ~32 rows the 64-block grid of the fused kernel (one NVLink barrier
-    # flag set per block) is slower than all-reduce + norm as two kernels (scripts/norm_bench.py)
+    # decode batches: above ~32 rows (TP = 2; ~64 at TP = 8) the 64-block grid of the fused
+    # kernel (one NVLink barrier flag set per block) stops winning (scripts/norm_bench.py)
     if (_handle is not None and _handle.should(partial) and hidden % 8 == 0 and hidden <= 16384
-            and partial.numel() // hidden <= _FUSED_NORM_MAX_ROWS):
+            and partial.numel() // hidden <= (_FUSED_NORM_MAX_ROWS if _handle.world <= 2
+                                              else 2 * _FUSED_NORM_MAX_ROWS)):
         return _handle
     return None
 
