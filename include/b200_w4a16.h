@@ -250,6 +250,22 @@ int b200_w4a16_allreduce_add_rms_norm(void *const *regions, int rank, int world,
                                 int hidden, size_t max_message_bytes, int barrier,
                                 b200_stream_t stream);
 
+/* The same collective with flag-in-data packets instead of stage / fence / flag / barrier /
+ * remote read: every 16-byte chunk is pushed to each peer as two 16-byte packets
+ * {data, epoch, data, epoch} and the receiver spins on the packets themselves -- one NVLink
+ * one-way trip on the critical path.  The packet area is `4 * world * ll_message_bytes` bytes
+ * at byte `ll_offset` (a multiple of 256, behind everything b200_w4a16_ar_region_bytes covers)
+ * of every rank's region: allocate `ll_offset + 4 * world * ll_message_bytes` with
+ * b200_w4a16_ar_alloc.  rows * hidden * 2 <= ll_message_bytes.  Bit-identical results; shares
+ * the epochs with the other all-reduce entry points (calls may be mixed on one stream).
+ * `barrier` 0 = single-GPU emulation (a missing packet traps instead of being waited for). */
+int b200_w4a16_allreduce_add_rms_norm_ll(void *const *regions, int rank, int world,
+                                         const uint16_t *in, const uint16_t *residual_in,
+                                         const uint16_t *weight, uint16_t *out,
+                                         uint16_t *residual_out, float eps, size_t rows,
+                                         int hidden, size_t ll_offset, size_t ll_message_bytes,
+                                         int barrier, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

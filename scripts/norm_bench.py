@@ -77,7 +77,7 @@ def multi():
     dist.init_process_group("nccl", device_id=dev)
     pu = pkg.parallel_utils
     pu.initialize_model_parallel(world)
-    pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2)
+    pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2, ll_bytes=256 * 8192 * 2)
     pu.custom_all_reduce._handle.oneshot_max_bytes = 1 << 30     # time the kernel at every size
     for rows, hidden in [(1, 8192), (16, 8192), (64, 8192), (256, 8192)]:
         norm = pkg.RMSNorm(hidden, eps=1e-5).half().to(dev)
@@ -90,13 +90,20 @@ def multi():
         def one(i=0):
             pu.custom_all_reduce._handle.all_reduce_add_rms_norm(partial, residual, norm.weight.data, 1e-5)
 
+        def one_barrier(i=0):
+            h = pu.custom_all_reduce._handle
+            h.use_ll = False
+            h.all_reduce_add_rms_norm(partial, residual, norm.weight.data, 1e-5)
+            h.use_ll = True
+
         def nccl(i=0):
             t = partial.clone()
             dist.all_reduce(t)
             norm(t, residual)
 
         res = {}
-        for name, fn in (("two_kernels", two), ("fused", one), ("nccl_plus_norm", nccl)):
+        for name, fn in (("two_kernels", two), ("fused_barrier", one_barrier), ("fused_packets", one),
+                         ("nccl_plus_norm", nccl)):
             dist.barrier()
             med, mn = graph_time(fn, 50)
             t = torch.tensor([med], device=dev)

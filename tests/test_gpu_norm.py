@@ -176,6 +176,60 @@ def test_allreduce_norm_single_gpu_emulation(pkg, oracle, cuda_lib, world, rows,
         assert torch.equal(out, two) and torch.equal(res_out, r2), call
 
 
+@pytest.mark.parametrize("world,rows,hidden", [(2, 16, 8192), (8, 1, 8192), (4, 40, 5120), (3, 70, 768)])
+def test_allreduce_norm_packets_single_gpu_emulation(pkg, oracle, cuda_lib, world, rows, hidden):
+    """The flag-in-data variant, rank 0 of `world` on one GPU: the peers' packets
+    {data, epoch, data, epoch} are pre-placed in rank 0's packet area; what rank 0 pushes lands
+    in the "peers'" regions and is checked too.  Result must equal the barrier variant's."""
+    from gpu_util import bits
+    L = cuda_lib
+    ll_bytes = 2 * 128 * 8192
+    ll_off = HEADER + 4096
+    region_bytes = ll_off + 4 * world * ll_bytes
+    regions = [torch.zeros(region_bytes, dtype=torch.uint8, device="cuda") for _ in range(world)]
+    ptrs = (ctypes.c_void_p * world)(*[r.data_ptr() for r in regions])
+    g = torch.Generator(device="cuda").manual_seed(rows + world)
+    n = rows * hidden
+    s = torch.cuda.current_stream().cuda_stream
+    w = (torch.randn(hidden, device="cuda", generator=g) * 0.1 + 1).half()
+    for call in range(3):
+        epoch = call + 1
+        parts = [torch.randn(rows, hidden, device="cuda", generator=g).half() for _ in range(world)]
+        res = torch.randn(rows, hidden, device="cuda", generator=g).half()
+        base = ll_off + (epoch & 1) * world * 2 * ll_bytes
+        for q in range(1, world):
+            data = parts[q].view(torch.int32).reshape(-1)                       # 2 halfs per word
+            pk = torch.stack([data, torch.full_like(data, epoch)], dim=1).reshape(-1)
+            off = base + q * 2 * ll_bytes
+            regions[0][off: off + 4 * n].view(torch.int32).copy_(pk)
+        out = torch.empty_like(parts[0])
+        res_out = torch.empty_like(res)
+        st = L.b200_w4a16_allreduce_add_rms_norm_ll(ptrs, 0, world, parts[0].data_ptr(), res.data_ptr(),
+                                                    w.data_ptr(), out.data_ptr(), res_out.data_ptr(), 1e-5,
+                                                    rows, hidden, ll_off, ll_bytes, 0, s)
+        assert st == 0
+        torch.cuda.synchronize()
+        red = oracle.np_allreduce_f16([p.cpu().numpy() for p in parts])
+        two = torch.from_numpy(red.view(np.int16).copy()).view(torch.float16).cuda()
+        r2 = res.clone()
+        pkg.ops.fused_add_rms_norm(two, r2, w, 1e-5)
+        assert torch.equal(out, two) and torch.equal(res_out, r2), call
+        # rank 0's own packets arrived in every peer's area, source slot 0
+        mine = parts[0].view(torch.int32).reshape(-1)
+        want_pk = torch.stack([mine, torch.full_like(mine, epoch)], dim=1).reshape(-1)
+        for q in range(1, world):
+            got = regions[q][base: base + 4 * n].view(torch.int32)
+            assert torch.equal(got, want_pk), (call, q)
+        assert torch.all(regions[0][2048:2048 + 256].view(torch.int32) == epoch)
+    e = pkg._lib
+    assert L.b200_w4a16_allreduce_add_rms_norm_ll(ptrs, 0, world, parts[0].data_ptr(), None, w.data_ptr(),
+                                                  out.data_ptr(), None, 1e-5, rows, hidden, ll_off, hidden, 0,
+                                                  s) == e.B200_ERR_BAD_SHAPE
+    assert L.b200_w4a16_allreduce_add_rms_norm_ll(ptrs, 0, world, parts[0].data_ptr(), None, w.data_ptr(),
+                                                  out.data_ptr(), None, 1e-5, rows, hidden, ll_off + 16, ll_bytes,
+                                                  0, s) == e.B200_ERR_BAD_ARG
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
@@ -193,7 +247,7 @@ def _rank_main(rank, world, port, q):
         pkg = importlib.import_module("vllm-quick_b200")
         pu = pkg.parallel_utils
         pu.initialize_model_parallel(world)
-        pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2)
+        pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2, ll_bytes=256 * 8192 * 2)
         pu.custom_all_reduce._handle.oneshot_max_bytes = 1 << 30     # exercise the kernel at every size
         g = torch.Generator(device=dev).manual_seed(100 + rank)
         gs = torch.Generator(device=dev).manual_seed(5)                 # same on every rank
@@ -207,9 +261,12 @@ def _rank_main(rank, world, port, q):
             r_one = residual.clone()
             one, r_one = norm.forward_reduced(partial, r_one)        # dispatch (fused up to 32 rows)
             assert torch.equal(one, two) and torch.equal(r_one, r_two), (rows, hidden)
-            r_k = residual.clone()                                   # the fused kernel itself, any rows
-            k = pu.custom_all_reduce._handle.all_reduce_add_rms_norm(partial, r_k, norm.weight.data, 1e-5)
-            assert torch.equal(k, two) and torch.equal(r_k, r_two), (rows, hidden)
+            for use_ll in (True, False):                             # the fused kernels themselves, any rows
+                pu.custom_all_reduce._handle.use_ll = use_ll
+                r_k = residual.clone()
+                k = pu.custom_all_reduce._handle.all_reduce_add_rms_norm(partial, r_k, norm.weight.data, 1e-5)
+                assert torch.equal(k, two) and torch.equal(r_k, r_two), (rows, hidden, use_ll)
+            pu.custom_all_reduce._handle.use_ll = True
             ref = partial.float()
             dist.all_reduce(ref)
             assert torch.allclose(r_one.float(), ref + residual.float(), rtol=2e-3, atol=2e-2)

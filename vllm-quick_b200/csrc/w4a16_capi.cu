@@ -434,4 +434,32 @@ int b200_w4a16_allreduce_add_rms_norm(void* const* regions, int rank, int world,
   return e == 0 ? B200_OK : cuda_fail(e);
 }
 
+int b200_w4a16_allreduce_add_rms_norm_ll(void* const* regions, int rank, int world,
+                                         const uint16_t* in, const uint16_t* residual_in,
+                                         const uint16_t* weight, uint16_t* out,
+                                         uint16_t* residual_out, float eps, size_t rows, int hidden,
+                                         size_t ll_offset, size_t ll_message_bytes, int barrier,
+                                         b200_stream_t stream) {
+  if (world < 2 || world > b200::kArMaxRanks || rank < 0 || rank >= world) return B200_ERR_BAD_ARG;
+  if (hidden <= 0 || hidden % 8 != 0 || hidden > b200::norm_max_hidden() || ll_message_bytes == 0 ||
+      rows > ll_message_bytes / (2 * (size_t)hidden))
+    return B200_ERR_BAD_SHAPE;
+  if (!(eps >= 0.f) || ll_offset % 256 != 0 || ll_offset < (size_t)b200::kArHeaderBytes ||
+      ll_offset + 4 * (size_t)world * ll_message_bytes > 0xFFFFFFFFull)
+    return B200_ERR_BAD_ARG;
+  if (rows == 0) return B200_OK;
+  if (!regions || !in || !weight || !out || !aligned16(in) || !aligned16(weight) ||
+      !aligned16(out) || !aligned16(residual_in) || !aligned16(residual_out))
+    return B200_ERR_BAD_ARG;
+  for (int q = 0; q < world; ++q)
+    if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_allreduce_add_rmsnorm(regions, rank, world, in, residual_in, weight, out,
+                                             residual_out, eps, rows, hidden, 0, barrier,
+                                             reinterpret_cast<cudaStream_t>(stream), ll_offset,
+                                             ll_message_bytes);
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
 }  // extern "C"

@@ -92,7 +92,8 @@ int launch_allreduce_add_rmsnorm(void* const* regions, int rank, int world, cons
                                  const uint16_t* residual_in, const uint16_t* weight,
                                  uint16_t* out, uint16_t* residual_out, float eps, size_t rows,
                                  int hidden, size_t max_message_bytes, int barrier,
-                                 cudaStream_t stream);
+                                 cudaStream_t stream, size_t ll_offset = 0,
+                                 size_t ll_message_bytes = 0);
 
 // Routed mixture-of-experts plumbing (w4a16_moe.cu): out[i] = x[idx[i]];
 // acc[idx[i]] = half(acc[idx[i]] + half(y[i] * w[i])).  hidden % 8 == 0, idx rows distinct.

@@ -61,6 +61,9 @@ struct NormParams {
   uint32_t slot_bytes;
   int rank;
   int barrier;
+  // LL variant: flag-in-data packets pushed into the peers' regions (see add_rmsnorm_kernel)
+  uint32_t ll_off;                // byte offset of the packet area inside a region
+  uint32_t ll_slot_bytes;         // packet bytes of one source rank and parity (2 x message)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -95,7 +98,21 @@ __device__ __forceinline__ void unpack8(float (&f)[8], const uint4& v) {
 // CPT = 1 spreads a row over the most CTAs (decode: few rows, latency); CPT = 4 puts up to
 // 8192 halfs in ONE CTA, so the per-row cluster barrier (a membar + barrier pair that was 40 %
 // of the stall samples, profiles/r1e_ncu_full_add_rmsnorm.txt) shrinks to a __syncthreads.
-template <int WORLD, int CPT>
+//
+// LL ("flag in data", WORLD >= 2, CPT == 1): instead of stage -> system fence -> flag -> barrier
+// -> remote read, every 16-byte chunk is PUSHED to each peer as two 16-byte packets
+// {data0, epoch, data1, epoch} (one vector store each, no fence); the receiver spins on the
+// packets themselves until both epoch words match -- one NVLink one-way trip instead of two
+// plus a round trip.  The packet area [2 parities][WORLD sources][2 x message bytes] lives behind
+// the other slots of the region and only ever holds packets, so a stale word can never look
+// like the current epoch (epochs only grow).  Same epochs, same parity rule as the other kernels.
+__device__ __forceinline__ void st_volatile_v4(uint4* p, uint4 v) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+template <int WORLD, int CPT, bool LL = false>
 __global__ void __launch_bounds__(kNormThreads)
 add_rmsnorm_kernel(const NormParams p) {
   cg::cluster_group cluster = cg::this_cluster();
@@ -127,6 +144,23 @@ add_rmsnorm_kernel(const NormParams p) {
     __syncthreads();
     const uint32_t epoch = s_epoch;
     slot_off = kArHeaderBytes + (epoch & 1u) * p.slot_bytes;
+    if constexpr (LL) {
+      slot_off = p.ll_off + (epoch & 1u) * (uint32_t)WORLD * p.ll_slot_bytes;
+      if (active[0]) {
+        for (uint32_t r = row0; r < p.rows; r += row_step) {
+          const size_t c = (size_t)r * p.chunks_per_row + ch[0];
+          const uint4 v = p.in[c];
+          const uint4 pk0 = make_uint4(v.x, epoch, v.y, epoch), pk1 = make_uint4(v.z, epoch, v.w, epoch);
+#pragma unroll
+          for (int q = 0; q < WORLD; ++q) {
+            if (q == p.rank) continue;
+            uint4* dst = reinterpret_cast<uint4*>(p.region[q] + slot_off + (uint32_t)p.rank * p.ll_slot_bytes) + 2 * c;
+            st_volatile_v4(dst, pk0);
+            st_volatile_v4(dst + 1, pk1);
+          }
+        }
+      }
+    } else {
     // 1. stage this thread's chunk of every row of this cluster into the own slot
     if (active[0]) {
       uint4* my_slot = reinterpret_cast<uint4*>(mine + slot_off);
@@ -155,6 +189,7 @@ add_rmsnorm_kernel(const NormParams p) {
       }
       __syncthreads();
     }
+    }  // !LL
     // every block's epoch advances on every call (block 0 covers the idle ones): the slot
     // parity is then a property of the call, whatever grid the previous calls used.
     if (threadIdx.x == 0) epochs[blockIdx.x] = epoch;
@@ -178,7 +213,27 @@ add_rmsnorm_kernel(const NormParams p) {
     for (int j = 0; j < CPT; ++j) {
       if (!active[j]) continue;
       const size_t c = (size_t)r * p.chunks_per_row + ch[j];
-      if constexpr (WORLD > 0) {
+      if constexpr (WORLD > 0 && LL) {
+        const uint32_t epoch = s_epoch;
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q) {
+          if (q == p.rank) { v[j][q] = p.in[c]; continue; }
+          const uint4* src = reinterpret_cast<const uint4*>(p.region[p.rank] + slot_off + (uint32_t)q * p.ll_slot_bytes) + 2 * c;
+          uint4 a, b;
+          const long long t0 = clock64();
+          for (;;) {
+            a = ld_volatile_v4(src);
+            b = ld_volatile_v4(src + 1);
+            if (a.y == epoch && a.w == epoch && b.y == epoch && b.w == epoch) break;
+            if (!p.barrier || clock64() - t0 > 4000000000ll) {
+              printf("b200_w4a16: all-reduce+norm packet timeout rank %d block %d source %d\n", p.rank,
+                     blockIdx.x, q);
+              __trap();
+            }
+          }
+          v[j][q] = make_uint4(a.x, a.z, b.x, b.z);
+        }
+      } else if constexpr (WORLD > 0) {
 #pragma unroll
         for (int q = 0; q < WORLD; ++q)
           v[j][q] = ld_volatile_v4(reinterpret_cast<const uint4*>(p.region[q] + slot_off) + c);
@@ -295,7 +350,7 @@ add_rmsnorm_kernel(const NormParams p) {
   if (csize > 1) cluster.sync();   // nobody leaves while a peer CTA may still read its partial
 }
 
-template <int WORLD, int CPT = 1>
+template <int WORLD, int CPT = 1, bool LL = false>
 int launch_norm(const NormParams& prm, int cluster, int row_clusters, cudaStream_t stream) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(cluster * row_clusters));
@@ -309,7 +364,7 @@ int launch_norm(const NormParams& prm, int cluster, int row_clusters, cudaStream
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return (int)cudaLaunchKernelEx(&cfg, add_rmsnorm_kernel<WORLD, CPT>, prm);
+  return (int)cudaLaunchKernelEx(&cfg, add_rmsnorm_kernel<WORLD, CPT, LL>, prm);
 }
 
 int fill_params(NormParams* prm, const uint16_t* in, const uint16_t* residual_in,
@@ -326,6 +381,8 @@ int fill_params(NormParams* prm, const uint16_t* in, const uint16_t* residual_in
   prm->rows = (uint32_t)rows;
   prm->chunks_per_row = (uint32_t)(hidden / 8);
   prm->slot_bytes = 0;
+  prm->ll_off = 0;
+  prm->ll_slot_bytes = 0;
   prm->rank = 0;
   prm->barrier = 0;
   return (int)((prm->chunks_per_row + kNormThreads - 1) / kNormThreads);   // cluster size
@@ -403,7 +460,7 @@ int launch_allreduce_add_rmsnorm(void* const* regions, int rank, int world, cons
                                  const uint16_t* residual_in, const uint16_t* weight,
                                  uint16_t* out, uint16_t* residual_out, float eps, size_t rows,
                                  int hidden, size_t max_message_bytes, int barrier,
-                                 cudaStream_t stream) {
+                                 cudaStream_t stream, size_t ll_offset, size_t ll_message_bytes) {
   NormParams prm;
   const int cluster = fill_params(&prm, in, residual_in, weight, out, residual_out, eps, rows, hidden);
   for (int q = 0; q < world; ++q) prm.region[q] = static_cast<uint8_t*>(regions[q]);
@@ -412,6 +469,20 @@ int launch_allreduce_add_rmsnorm(void* const* regions, int rank, int world, cons
   prm.barrier = barrier;
   size_t row_clusters = (size_t)(kArMaxBlocks / cluster);      // one barrier flag set per block
   if (row_clusters > rows) row_clusters = rows;
+  if (ll_message_bytes > 0) {
+    prm.ll_off = (uint32_t)ll_offset;
+    prm.ll_slot_bytes = (uint32_t)(2 * ll_message_bytes);
+    switch (world) {
+      case 2: return launch_norm<2, 1, true>(prm, cluster, (int)row_clusters, stream);
+      case 3: return launch_norm<3, 1, true>(prm, cluster, (int)row_clusters, stream);
+      case 4: return launch_norm<4, 1, true>(prm, cluster, (int)row_clusters, stream);
+      case 5: return launch_norm<5, 1, true>(prm, cluster, (int)row_clusters, stream);
+      case 6: return launch_norm<6, 1, true>(prm, cluster, (int)row_clusters, stream);
+      case 7: return launch_norm<7, 1, true>(prm, cluster, (int)row_clusters, stream);
+      case 8: return launch_norm<8, 1, true>(prm, cluster, (int)row_clusters, stream);
+      default: return (int)cudaErrorInvalidValue;
+    }
+  }
   switch (world) {
     case 1: return launch_norm<1>(prm, cluster, (int)row_clusters, stream);
     case 2: return launch_norm<2>(prm, cluster, (int)row_clusters, stream);

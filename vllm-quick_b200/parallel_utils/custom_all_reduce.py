@@ -34,7 +34,7 @@ _handle: Optional["CustomAllreduce"] = None
 class CustomAllreduce:
     """One registered region per rank, mapped by every peer of the tensor-parallel group."""
 
-    def __init__(self, max_bytes: int, fused_out_features: int = 0) -> None:
+    def __init__(self, max_bytes: int, fused_out_features: int = 0, ll_bytes: int = 1 << 20) -> None:
         L = _lib.lib()
         self.rank = get_tensor_model_parallel_rank()
         self.world = get_tensor_model_parallel_world_size()
@@ -47,9 +47,14 @@ class CustomAllreduce:
         # the same split the reference makes between its one- and two-stage kernels
         # (csrc/custom_all_reduce.cuh:520-531).  A tuning value: tests and benches may raise it.
         self.oneshot_max_bytes = (128 << 10) if self.world <= 2 else (512 << 10)
+        self.use_ll = True      # all-reduce + norm: flag-in-data packets when the message fits
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.fused_out_features = int(fused_out_features)
         region_bytes = L.b200_w4a16_ar_region_bytes(self.max_bytes, self.world, self.fused_out_features)
+        # flag-in-data packet area of the all-reduce + norm kernel: [2][world][2 x ll_bytes]
+        self.ll_bytes = (int(ll_bytes) + 255) // 256 * 256
+        self.ll_off = (region_bytes + 255) // 256 * 256
+        region_bytes = self.ll_off + 4 * self.world * self.ll_bytes
         own = ctypes.c_void_p()
         _lib.check(L.b200_w4a16_ar_alloc(region_bytes, ctypes.byref(own)), "all-reduce region")
         self._own = own.value
@@ -90,6 +95,14 @@ class CustomAllreduce:
         kernel: all-reduce (linear.py:541-542) + fused_add_rms_norm (llama.py:205-222)."""
         hidden = partial.shape[-1]
         out = torch.empty_like(partial)
+        if self.use_ll and 0 < partial.numel() * 2 <= self.ll_bytes:
+            st = _lib.lib().b200_w4a16_allreduce_add_rms_norm_ll(
+                self._regions, self.rank, self.world, partial.data_ptr(), residual.data_ptr(),
+                weight.data_ptr(), out.data_ptr(), residual.data_ptr(), float(eps),
+                partial.numel() // hidden, hidden, self.ll_off, self.ll_bytes, 1,
+                torch.cuda.current_stream(partial.device).cuda_stream)
+            _lib.check(st, "all-reduce + add + rms_norm (packets)")
+            return out
         st = _lib.lib().b200_w4a16_allreduce_add_rms_norm(
             self._regions, self.rank, self.world, partial.data_ptr(), residual.data_ptr(),
             weight.data_ptr(), out.data_ptr(), residual.data_ptr(), float(eps),
@@ -127,7 +140,8 @@ class CustomAllreduce:
             self._own = None
 
 
-def init_custom_all_reduce(max_bytes: int = 8 << 20, fused_out_features: int = 0) -> None:
+def init_custom_all_reduce(max_bytes: int = 8 << 20, fused_out_features: int = 0,
+                           ll_bytes: int = 1 << 20) -> None:
     """Collective over the TP group: allocate, exchange and map the regions (default 8 MiB
     messages, the reference's limit, custom_all_reduce.py:143).  ``fused_out_features`` > 0
     also reserves the slots of the fused row-parallel GEMM + all-reduce (the model's hidden
@@ -135,7 +149,7 @@ def init_custom_all_reduce(max_bytes: int = 8 << 20, fused_out_features: int = 0
     global _handle
     if _handle is not None or get_tensor_model_parallel_world_size() == 1:
         return
-    _handle = CustomAllreduce(max_bytes, fused_out_features)
+    _handle = CustomAllreduce(max_bytes, fused_out_features, ll_bytes)
 
 
 def fused_handle(M: int, N: int, G: int) -> Optional["CustomAllreduce"]:
