@@ -258,7 +258,15 @@ int b200_w4a16_allreduce_add_rms_norm(void *const *regions, int rank, int world,
  * of every rank's region: allocate `ll_offset + 4 * world * ll_message_bytes` with
  * b200_w4a16_ar_alloc.  rows * hidden * 2 <= ll_message_bytes.  Bit-identical results; shares
  * the epochs with the other all-reduce entry points (calls may be mixed on one stream).
- * `barrier` 0 = single-GPU emulation (a missing packet traps instead of being waited for). */
+ * `barrier` 0 = single-GPU emulation (a missing packet traps instead of being waited for).
+ * (documentation of b200_w4a16_allreduce_add_rms_norm_ll, declared below) */
+/* b200_w4a16_allreduce with the same packets (same area, same arguments): out = sum over ranks
+ * of in, rank order, fp32 accumulate -- bit-identical to b200_w4a16_allreduce.
+ * n_halfs % 8 == 0, 2 * n_halfs <= ll_message_bytes. */
+int b200_w4a16_allreduce_ll(void *const *regions, int rank, int world, const uint16_t *in,
+                            uint16_t *out, size_t n_halfs, size_t ll_offset,
+                            size_t ll_message_bytes, int barrier, b200_stream_t stream);
+
 int b200_w4a16_allreduce_add_rms_norm_ll(void *const *regions, int rank, int world,
                                          const uint16_t *in, const uint16_t *residual_in,
                                          const uint16_t *weight, uint16_t *out,

@@ -53,6 +53,38 @@ def test_single_gpu_emulation_matches_rank_order_sum(pkg, cuda_lib, world, n):
         assert torch.equal(out, _expected(parts)), call
 
 
+@pytest.mark.parametrize("world,n", [(2, 16 * 8192), (8, 8192), (3, 8)])
+def test_packet_allreduce_single_gpu_emulation(pkg, cuda_lib, world, n):
+    """b200_w4a16_allreduce_ll, rank 0 of `world` on one GPU: peers' packets {data, epoch, data,
+    epoch} pre-placed; result = rank-order fp32 sum, and rank 0's packets land in the peers'."""
+    L = cuda_lib
+    ll_bytes, ll_off = 2 * 16 * 8192, HEADER
+    regions = [torch.zeros(ll_off + 4 * world * ll_bytes, dtype=torch.uint8, device="cuda") for _ in range(world)]
+    ptrs = (ctypes.c_void_p * world)(*[r.data_ptr() for r in regions])
+    g = torch.Generator(device="cuda").manual_seed(n + world)
+    s = torch.cuda.current_stream().cuda_stream
+    for epoch in (1, 2, 3):
+        parts = [torch.randn(n, device="cuda", generator=g).half() for _ in range(world)]
+        base = ll_off + (epoch & 1) * world * 2 * ll_bytes
+        for q in range(1, world):
+            data = parts[q].view(torch.int32)
+            pk = torch.stack([data, torch.full_like(data, epoch)], dim=1).reshape(-1)
+            regions[0][base + q * 2 * ll_bytes: base + q * 2 * ll_bytes + 4 * n].view(torch.int32).copy_(pk)
+        out = torch.empty_like(parts[0])
+        assert L.b200_w4a16_allreduce_ll(ptrs, 0, world, parts[0].data_ptr(), out.data_ptr(), n, ll_off,
+                                         ll_bytes, 0, s) == 0
+        torch.cuda.synchronize()
+        assert torch.equal(out, _expected(parts)), epoch
+        mine = parts[0].view(torch.int32)
+        want = torch.stack([mine, torch.full_like(mine, epoch)], dim=1).reshape(-1)
+        for q in range(1, world):
+            assert torch.equal(regions[q][base: base + 4 * n].view(torch.int32), want)
+    assert L.b200_w4a16_allreduce_ll(ptrs, 0, world, parts[0].data_ptr(), out.data_ptr(), n, ll_off, n,
+                                     0, s) == pkg._lib.B200_ERR_BAD_SHAPE
+    assert L.b200_w4a16_allreduce_ll(ptrs, 0, 1, parts[0].data_ptr(), out.data_ptr(), n, ll_off, ll_bytes,
+                                     0, s) == pkg._lib.B200_ERR_BAD_ARG
+
+
 def _to_fragment_order(Y, MT):
     """[16, N] fp16 -> the fused path's slot layout: per 128-channel tile, MT x 128 threads x
     uint4; thread ct = 32 w + 4 g + t holds tokens 8i+2t, 8i+2t+1 of channels

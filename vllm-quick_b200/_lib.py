@@ -32,7 +32,7 @@ EXPORTS = (
     "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
     "b200_w4a16_allreduce", "b200_w4a16_gemm_allreduce", "b200_w4a16_gemm_gated",
     "b200_w4a16_moe_gather", "b200_w4a16_moe_scatter_add", "b200_w4a16_silu_and_mul", "b200_w4a16_gemm_silu_mul", "b200_w4a16_add_rms_norm", "b200_w4a16_allreduce_add_rms_norm",
-    "b200_w4a16_allreduce_add_rms_norm_ll",
+    "b200_w4a16_allreduce_add_rms_norm_ll", "b200_w4a16_allreduce_ll",
 )
 
 
@@ -120,6 +120,8 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_allreduce_add_rms_norm_ll.restype = i32
     L.b200_w4a16_allreduce_add_rms_norm_ll.argtypes = [ctypes.POINTER(vp), i32, i32, vp, vp, vp, vp, vp,
                                                        f32, sz, i32, sz, sz, i32, vp]
+    L.b200_w4a16_allreduce_ll.restype = i32
+    L.b200_w4a16_allreduce_ll.argtypes = [ctypes.POINTER(vp), i32, i32, vp, vp, sz, sz, sz, i32, vp]
     _lib = L
     return L
 

@@ -42,6 +42,7 @@ struct ArParams {
   uint32_t slot_bytes;
   int rank, world;
   int barrier;                    // 0 only in the single-GPU emulation test
+  uint32_t ll_off, ll_slot_bytes; // packet variant: area offset, bytes per source rank and parity
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -138,6 +139,68 @@ allreduce_oneshot_kernel(const ArParams p) {
   }
 }
 
+// Packet ("flag in data") variant: see add_rmsnorm_kernel<WORLD, 1, true> in w4a16_norm.cu for
+// the protocol.  Every 16-byte chunk goes to each peer as two stores {data, epoch, data, epoch};
+// the receiver spins on the packets: one NVLink one-way trip, no fence, no flag, no barrier.
+template <int WORLD>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_ll_kernel(const ArParams p) {
+  uint8_t* mine = p.region[p.rank];
+  uint32_t* epochs = reinterpret_cast<uint32_t*>(mine + kArFlagBytes);
+  __shared__ uint32_t s_epoch;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (threadIdx.x == 0) s_epoch = epochs[blockIdx.x] + 1;
+  __syncthreads();
+  const uint32_t epoch = s_epoch;
+  const uint32_t base = p.ll_off + (epoch & 1u) * (uint32_t)WORLD * p.ll_slot_bytes;
+  for (uint32_t c = blockIdx.x * kArThreads + threadIdx.x; c < p.nchunks; c += gridDim.x * kArThreads) {
+    const uint4 v = p.in[c];
+    const uint4 pk0 = make_uint4(v.x, epoch, v.y, epoch), pk1 = make_uint4(v.z, epoch, v.w, epoch);
+#pragma unroll
+    for (int q = 0; q < WORLD; ++q) {
+      if (q == p.rank) continue;
+      uint4* dst = reinterpret_cast<uint4*>(p.region[q] + base + (uint32_t)p.rank * p.ll_slot_bytes) + 2 * (size_t)c;
+      asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(pk0.x), "r"(pk0.y), "r"(pk0.z), "r"(pk0.w) : "memory");
+      asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 1), "r"(pk1.x), "r"(pk1.y), "r"(pk1.z), "r"(pk1.w) : "memory");
+    }
+  }
+  if (threadIdx.x == 0) epochs[blockIdx.x] = epoch;
+  if (blockIdx.x == 0 && threadIdx.x >= gridDim.x && threadIdx.x < kArMaxBlocks) epochs[threadIdx.x] = epoch;
+  for (uint32_t c = blockIdx.x * kArThreads + threadIdx.x; c < p.nchunks; c += gridDim.x * kArThreads) {
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int q = 0; q < WORLD; ++q) {
+      if (q == p.rank) { add8(acc, p.in[c]); continue; }
+      const uint4* src = reinterpret_cast<const uint4*>(mine + base + (uint32_t)q * p.ll_slot_bytes) + 2 * (size_t)c;
+      uint4 a, b;
+      const long long t0 = clock64();
+      for (;;) {
+        a = ld_volatile_v4(src);
+        b = ld_volatile_v4(src + 1);
+        if (a.y == epoch && a.w == epoch && b.y == epoch && b.w == epoch) break;
+        if (!p.barrier || clock64() - t0 > 4000000000ll) {
+          printf("b200_w4a16: all-reduce packet timeout rank %d block %d source %d\n", p.rank, blockIdx.x, q);
+          __trap();
+        }
+      }
+      add8(acc, make_uint4(a.x, a.z, b.x, b.z));
+    }
+    uint4 o;
+    __half2* oh = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(acc[2 * i], acc[2 * i + 1]);
+    p.out[c] = o;
+  }
+}
+
+template <int WORLD>
+int launch_ar_ll(const ArParams& prm, int blocks, cudaStream_t stream) {
+  allreduce_ll_kernel<WORLD><<<blocks, kArThreads, 0, stream>>>(prm);
+  return (int)cudaGetLastError();
+}
+
 template <int WORLD>
 int launch_ar(const ArParams& prm, int blocks, cudaStream_t stream) {
   allreduce_oneshot_kernel<WORLD><<<blocks, kArThreads, 0, stream>>>(prm);
@@ -152,8 +215,11 @@ size_t ar_region_bytes(size_t max_message_bytes) {
 }
 
 int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* in, uint16_t* out,
-                     size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream) {
+                     size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream,
+                     size_t ll_offset, size_t ll_message_bytes) {
   ArParams prm;
+  prm.ll_off = (uint32_t)ll_offset;
+  prm.ll_slot_bytes = (uint32_t)(2 * ll_message_bytes);
   for (int q = 0; q < kArMaxRanks; ++q) prm.region[q] = q < world ? static_cast<uint8_t*>(regions[q]) : nullptr;
   prm.in = reinterpret_cast<const uint4*>(in);
   prm.out = reinterpret_cast<uint4*>(out);
@@ -165,6 +231,18 @@ int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* 
   int blocks = (int)((prm.nchunks + kArThreads - 1) / kArThreads);
   if (blocks < 1) blocks = 1;
   if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  if (ll_message_bytes > 0) {
+    switch (world) {
+      case 2: return launch_ar_ll<2>(prm, blocks, stream);
+      case 3: return launch_ar_ll<3>(prm, blocks, stream);
+      case 4: return launch_ar_ll<4>(prm, blocks, stream);
+      case 5: return launch_ar_ll<5>(prm, blocks, stream);
+      case 6: return launch_ar_ll<6>(prm, blocks, stream);
+      case 7: return launch_ar_ll<7>(prm, blocks, stream);
+      case 8: return launch_ar_ll<8>(prm, blocks, stream);
+      default: return (int)cudaErrorInvalidValue;
+    }
+  }
   switch (world) {
     case 1: return launch_ar<1>(prm, blocks, stream);
     case 2: return launch_ar<2>(prm, blocks, stream);

@@ -434,6 +434,25 @@ int b200_w4a16_allreduce_add_rms_norm(void* const* regions, int rank, int world,
   return e == 0 ? B200_OK : cuda_fail(e);
 }
 
+int b200_w4a16_allreduce_ll(void* const* regions, int rank, int world, const uint16_t* in,
+                            uint16_t* out, size_t n_halfs, size_t ll_offset, size_t ll_message_bytes,
+                            int barrier, b200_stream_t stream) {
+  if (world < 2 || world > b200::kArMaxRanks || rank < 0 || rank >= world) return B200_ERR_BAD_ARG;
+  if (n_halfs % 8 != 0 || ll_message_bytes == 0 || n_halfs * 2 > ll_message_bytes) return B200_ERR_BAD_SHAPE;
+  if (ll_offset % 256 != 0 || ll_offset < (size_t)b200::kArHeaderBytes ||
+      ll_offset + 4 * (size_t)world * ll_message_bytes > 0xFFFFFFFFull)
+    return B200_ERR_BAD_ARG;
+  if (n_halfs == 0) return B200_OK;
+  if (!regions || !in || !out || !aligned16(in) || !aligned16(out)) return B200_ERR_BAD_ARG;
+  for (int q = 0; q < world; ++q)
+    if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
+  const DeviceInfo& dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_allreduce(regions, rank, world, in, out, n_halfs, 0, barrier,
+                                 reinterpret_cast<cudaStream_t>(stream), ll_offset, ll_message_bytes);
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
 int b200_w4a16_allreduce_add_rms_norm_ll(void* const* regions, int rank, int world,
                                          const uint16_t* in, const uint16_t* residual_in,
                                          const uint16_t* weight, uint16_t* out,

@@ -80,7 +80,8 @@ static_assert(kArFlagBytes + kArMaxBlocks * 4 <= kArFusedCtrOff, "all-reduce hea
 static_assert(kArFusedFlagOff + 2 * kArMaxTiles * kArMaxRanks * 4 <= kArHeaderBytes, "fused flags");
 size_t ar_region_bytes(size_t max_message_bytes);
 int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* in, uint16_t* out,
-                     size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream);
+                     size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream,
+                     size_t ll_offset = 0, size_t ll_message_bytes = 0);
 
 // Residual add + RMSNorm, standalone and fused behind the one-shot all-reduce (w4a16_norm.cu).
 // hidden % 8 == 0, hidden <= norm_max_hidden(); residual_in / residual_out may be nullptr.

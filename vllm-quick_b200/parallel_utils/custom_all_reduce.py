@@ -78,11 +78,20 @@ class CustomAllreduce:
     def should(self, t: torch.Tensor) -> bool:
         nbytes = t.numel() * t.element_size()
         return (t.is_cuda and t.dtype == torch.float16 and t.is_contiguous()
-                and nbytes % 16 == 0 and 0 < nbytes <= min(self.max_bytes, self.oneshot_max_bytes)
-                and t.data_ptr() % 16 == 0)
+                and nbytes % 16 == 0 and t.data_ptr() % 16 == 0
+                and (0 < nbytes <= min(self.max_bytes, self.oneshot_max_bytes) or self._fits_ll(nbytes)))
+
+    def _fits_ll(self, nbytes: int) -> bool:
+        return self.use_ll and 0 < nbytes <= self.ll_bytes
 
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         out = torch.empty_like(t)
+        if self._fits_ll(t.numel() * 2):
+            st = _lib.lib().b200_w4a16_allreduce_ll(
+                self._regions, self.rank, self.world, t.data_ptr(), out.data_ptr(), t.numel(),
+                self.ll_off, self.ll_bytes, 1, torch.cuda.current_stream(t.device).cuda_stream)
+            _lib.check(st, "custom all-reduce (packets)")
+            return out
         st = _lib.lib().b200_w4a16_allreduce(
             self._regions, self.rank, self.world, t.data_ptr(), out.data_ptr(), t.numel(),
             self.max_bytes, 1, torch.cuda.current_stream(t.device).cuda_stream)
@@ -162,10 +171,11 @@ def fused_handle(M: int, N: int, G: int) -> Optional["CustomAllreduce"]:
 def norm_handle(partial: torch.Tensor) -> Optional["CustomAllreduce"]:
     """The handle if the all-reduce of this tensor can run fused with the add + RMSNorm after it."""
     hidden = partial.shape[-1]
-    # decode batches: above ~32 rows (TP = 2; ~64 at TP = 8) the 64-block grid of the fused
-    # kernel (one NVLink barrier flag set per block) stops winning (scripts/norm_bench.py)
+    # with packets the fused kernel wins up to ~128 rows; the barrier variant (message larger
+    # than the packet area) up to ~32 rows at TP = 2, ~64 at TP = 8 (scripts/norm_bench.py)
     if (_handle is not None and _handle.should(partial) and hidden % 8 == 0 and hidden <= 16384
-            and partial.numel() // hidden <= (_FUSED_NORM_MAX_ROWS if _handle.world <= 2
+            and partial.numel() // hidden <= (4 * _FUSED_NORM_MAX_ROWS if _handle._fits_ll(partial.numel() * 2)
+                                              else _FUSED_NORM_MAX_ROWS if _handle.world <= 2
                                               else 2 * _FUSED_NORM_MAX_ROWS)):
         return _handle
     return None
