@@ -206,6 +206,10 @@ def main():
     ap.add_argument("--model", default=None, help="llama2-7b | llama2-13b | llama2-70b")
     ap.add_argument("--layers", type=int, default=None, help="override layer count (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fused-gemm-allreduce", action="store_true",
+                    help="force the row-parallel GEMM fused with its all-reduce in one kernel (default at TP > 2)")
+    ap.add_argument("--packet-allreduce", action="store_true",
+                    help="force GEMM, then the packet all-reduce kernel (default at TP = 2)")
     ap.add_argument("--unfused-allreduce", action="store_true",
                     help="row-parallel GEMM and the peer-memory all-reduce as two kernels")
     ap.add_argument("--nccl-allreduce", action="store_true",
@@ -243,8 +247,13 @@ def main():
         if not args.nccl_allreduce:
             pu.custom_all_reduce.init_custom_all_reduce(
                 max_bytes=M * hidden * 2, fused_out_features=0 if args.unfused_allreduce else hidden)
-            if args.unfused_allreduce:      # this mode means "the one-shot kernel", whatever the size policy says
+            if args.unfused_allreduce:      # this mode means "the one-shot barrier kernel", whatever the policy says
                 pu.custom_all_reduce._handle.oneshot_max_bytes = 1 << 30
+                pu.custom_all_reduce._handle.use_ll = False
+            if args.fused_gemm_allreduce:
+                pu.custom_all_reduce._handle.prefer_fused_gemm = True
+            if args.packet_allreduce:
+                pu.custom_all_reduce._handle.prefer_fused_gemm = False
     method = pkg.QuickConfig(4, GROUP, True).get_linear_method()
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
 
@@ -363,7 +372,10 @@ def main():
             "gpu_launches": (launches_per_step + ar_launches) * args.steps,
             "allreduce": None if world == 1 else (
                 "fused into the row-parallel GEMM (b200_w4a16_gemm_allreduce)" if fused_ar else
-                "nvlink peer-memory kernel (b200_w4a16_allreduce)" if ar_launches else "nccl"),
+                ("nvlink packet kernel after the GEMM (b200_w4a16_allreduce_ll)"
+                 if pu.custom_all_reduce._handle.use_ll else
+                 "nvlink one-shot barrier kernel after the GEMM (b200_w4a16_allreduce)")
+                if ar_launches else "nccl"),
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": M * hidden * 2,
                     "d2h_bytes_per_step": M * hidden * 2, "ms_per_step": ms_e2e / args.steps},

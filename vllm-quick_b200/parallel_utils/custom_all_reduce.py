@@ -47,7 +47,13 @@ class CustomAllreduce:
         # the same split the reference makes between its one- and two-stage kernels
         # (csrc/custom_all_reduce.cuh:520-531).  A tuning value: tests and benches may raise it.
         self.oneshot_max_bytes = (128 << 10) if self.world <= 2 else (512 << 10)
-        self.use_ll = True      # all-reduce + norm: flag-in-data packets when the message fits
+        self.use_ll = True      # flag-in-data packets when the message fits the packet area
+        # Row-parallel decode GEMMs: at TP = 2 GEMM then packet all-reduce (two launches) beats
+        # the fused GEMM + all-reduce kernel, whose tile exchange still pays a system fence and a
+        # flag round trip per tile (7.37 vs 8.26 ms per Llama-2-70B decode step); at TP = 8 the
+        # fused kernel's overlap wins (5.85 vs 6.33 ms: seven peers' packets at twice the bytes).
+        # profiles/r1e_bench_tp{2,8}_*.json.  TP = 4 not measured: treated like 8.
+        self.prefer_fused_gemm = self.world > 2
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.fused_out_features = int(fused_out_features)
         region_bytes = L.b200_w4a16_ar_region_bytes(self.max_bytes, self.world, self.fused_out_features)
@@ -121,7 +127,10 @@ class CustomAllreduce:
         return out
 
     def can_fuse(self, M: int, N: int, G: int) -> bool:
-        """Fused row-parallel GEMM + all-reduce: decode batches whose output fits the slots."""
+        """Fused row-parallel GEMM + all-reduce: decode batches whose output fits the slots
+        (and, unless forced, only when the packet all-reduce cannot take the message)."""
+        if not self.prefer_fused_gemm and self._fits_ll(M * N * 2):
+            return False
         return 0 < M <= 16 and G % 128 == 0 and N <= self.fused_out_features and N <= 128 * 128
 
     def gemm_all_reduce(self, x: torch.Tensor, qweight: torch.Tensor, scales: torch.Tensor,
