@@ -250,23 +250,26 @@ int b200_w4a16_allreduce_add_rms_norm(void *const *regions, int rank, int world,
                                 int hidden, size_t max_message_bytes, int barrier,
                                 b200_stream_t stream);
 
-/* The same collective with flag-in-data packets instead of stage / fence / flag / barrier /
- * remote read: every 16-byte chunk is pushed to each peer as two 16-byte packets
- * {data, epoch, data, epoch} and the receiver spins on the packets themselves -- one NVLink
- * one-way trip on the critical path.  The packet area is `4 * world * ll_message_bytes` bytes
- * at byte `ll_offset` (a multiple of 256, behind everything b200_w4a16_ar_region_bytes covers)
- * of every rank's region: allocate `ll_offset + 4 * world * ll_message_bytes` with
- * b200_w4a16_ar_alloc.  rows * hidden * 2 <= ll_message_bytes.  Bit-identical results; shares
- * the epochs with the other all-reduce entry points (calls may be mixed on one stream).
- * `barrier` 0 = single-GPU emulation (a missing packet traps instead of being waited for).
- * (documentation of b200_w4a16_allreduce_add_rms_norm_ll, declared below) */
-/* b200_w4a16_allreduce with the same packets (same area, same arguments): out = sum over ranks
- * of in, rank order, fp32 accumulate -- bit-identical to b200_w4a16_allreduce.
- * n_halfs % 8 == 0, 2 * n_halfs <= ll_message_bytes. */
+/* ---- flag-in-data ("packet") variants of the two collectives above ---------------------------
+ * Instead of stage / system fence / flag / barrier / remote read, every 16-byte chunk is
+ * PUSHED to each peer as two 16-byte packets {data, epoch, data, epoch} and the receiver spins
+ * on the packets themselves -- one NVLink one-way trip on the critical path, no fence, no
+ * barrier.  The packet area is `4 * world * ll_message_bytes` bytes at byte `ll_offset` (a
+ * multiple of 256, behind everything b200_w4a16_ar_region_bytes covers) of every rank's
+ * region: allocate `ll_offset + 4 * world * ll_message_bytes` with b200_w4a16_ar_alloc.  The
+ * message must fit ll_message_bytes.  Results are bit-identical to the barrier variants; the
+ * epochs are shared with them (calls of all kinds may be mixed on one stream); CUDA-graph
+ * capturable.  `barrier` 0 = single-GPU emulation (a missing packet traps instead of being
+ * waited for).  world >= 2.
+ * Replaces: the same reference sites as b200_w4a16_allreduce (communication_op.py:17-41) and
+ * b200_w4a16_allreduce_add_rms_norm (linear.py:541-542 + llama.py:205-222). */
+
+/* out[n_halfs] = sum over ranks of in[n_halfs]; n_halfs % 8 == 0, 2 * n_halfs <= ll_message_bytes. */
 int b200_w4a16_allreduce_ll(void *const *regions, int rank, int world, const uint16_t *in,
                             uint16_t *out, size_t n_halfs, size_t ll_offset,
                             size_t ll_message_bytes, int barrier, b200_stream_t stream);
 
+/* all-reduce + residual add + RMSNorm; rows * hidden * 2 <= ll_message_bytes. */
 int b200_w4a16_allreduce_add_rms_norm_ll(void *const *regions, int rank, int world,
                                          const uint16_t *in, const uint16_t *residual_in,
                                          const uint16_t *weight, uint16_t *out,
