@@ -79,6 +79,7 @@ def multi():
     pu.initialize_model_parallel(world)
     pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2, ll_bytes=256 * 8192 * 2)
     pu.custom_all_reduce._handle.oneshot_max_bytes = 1 << 30     # time the kernel at every size
+    pu.custom_all_reduce._handle.ll_max_bytes = 1 << 30
     for rows, hidden in [(1, 8192), (16, 8192), (64, 8192), (256, 8192)]:
         norm = pkg.RMSNorm(hidden, eps=1e-5).half().to(dev)
         partial = torch.randn(rows, hidden, device=dev).half() * 0.01

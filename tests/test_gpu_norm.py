@@ -249,6 +249,7 @@ def _rank_main(rank, world, port, q):
         pu.initialize_model_parallel(world)
         pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2, ll_bytes=256 * 8192 * 2)
         pu.custom_all_reduce._handle.oneshot_max_bytes = 1 << 30     # exercise the kernel at every size
+        pu.custom_all_reduce._handle.ll_max_bytes = 1 << 30
         g = torch.Generator(device=dev).manual_seed(100 + rank)
         gs = torch.Generator(device=dev).manual_seed(5)                 # same on every rank
         for rows, hidden in [(1, 8192), (16, 8192), (256, 8192), (3, 4096), (16, 5120), (70, 768)]:

@@ -48,6 +48,10 @@ class CustomAllreduce:
         # (csrc/custom_all_reduce.cuh:520-531).  A tuning value: tests and benches may raise it.
         self.oneshot_max_bytes = (128 << 10) if self.world <= 2 else (512 << 10)
         self.use_ll = True      # flag-in-data packets when the message fits the packet area
+        # packets double the NVLink bytes and every rank receives world - 1 copies: measured to
+        # win up to 1 MiB at TP = 2 (r1e_allreduce_norm_bench_tp2.jsonl); not yet measured per
+        # size at TP = 8, so stay at the size the one-shot kernel was already trusted with there
+        self.ll_max_bytes = (1 << 20) if self.world <= 2 else (512 << 10)
         # Row-parallel decode GEMMs: at TP = 2 GEMM then packet all-reduce (two launches) beats
         # the fused GEMM + all-reduce kernel, whose tile exchange still pays a system fence and a
         # flag round trip per tile (7.37 vs 8.26 ms per Llama-2-70B decode step); at TP = 8 the
@@ -88,7 +92,7 @@ class CustomAllreduce:
                 and (0 < nbytes <= min(self.max_bytes, self.oneshot_max_bytes) or self._fits_ll(nbytes)))
 
     def _fits_ll(self, nbytes: int) -> bool:
-        return self.use_ll and 0 < nbytes <= self.ll_bytes
+        return self.use_ll and 0 < nbytes <= min(self.ll_bytes, self.ll_max_bytes)
 
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         out = torch.empty_like(t)
