@@ -38,7 +38,7 @@ typedef enum {
   B200_ERR_BAD_SHAPE = 1,  /* shape precondition violated (reference: std::invalid_argument,
                               csrc/quantization/awq/gemm_kernels.cu:412-419) */
   B200_ERR_BAD_ARG = 2,    /* null / misaligned pointer, unknown layout */
-  B200_ERR_WORKSPACE = 3,  /* workspace missing or smaller than b200_w4a16_workspace_bytes */
+  B200_ERR_WORKSPACE = 3,  /* workspace missing, misaligned or smaller than b200_w4a16_workspace_bytes */
   B200_ERR_CUDA = 4,       /* a CUDA runtime / driver call failed (see b200_w4a16_last_cuda_error) */
   B200_ERR_NO_DEVICE = 5   /* no sm_100 device: the library has no fallback path */
 } b200_status_t;
@@ -59,13 +59,20 @@ int b200_w4a16_last_cuda_error(void);
  * (== K*N/8 when N % 128 == 0; N % 128 == 64 pads the last tile column). */
 size_t b200_w4a16_repacked_words(int K, int N);
 
-/* Bytes of zero-initialised scratch b200_w4a16_gemm needs for this problem.  The caller
- * zero-fills it ONCE; every launch leaves it zeroed again.  One workspace may be shared by
- * all GEMMs issued on one stream (size it for the largest).  `layout` B200_LAYOUT_AWQ adds
+/* Bytes of scratch b200_w4a16_gemm needs for this problem.  The caller initialises it ONCE
+ * with b200_w4a16_workspace_init (outside any CUDA-graph capture); every launch leaves it in
+ * that state again.  One workspace may be shared by all GEMMs issued on one stream (size it
+ * for the largest), and by every CUDA graph captured on it.  `layout` B200_LAYOUT_AWQ adds
  * room for an on-the-fly repack.
  * Replaces: the internal `torch::empty({split_k, M, N})` scratch of awq_gemm
  * (csrc/quantization/awq/gemm_kernels.cu:401). */
 size_t b200_w4a16_workspace_bytes(int M, int K, int N, int layout);
+
+/* Puts a workspace into its idle state: split-K partial tiles cross CTAs as self-flagging fp32
+ * words, an unwritten slot reads 0xFFFFFFFF in every word (asynchronous fill on `stream`).
+ * A workspace that was never initialised makes the first split GEMM take garbage for
+ * partial sums -- hence a call of its own instead of a "zero it yourself" rule. */
+int b200_w4a16_workspace_init(void *workspace, size_t workspace_bytes, b200_stream_t stream);
 
 /* y[M,N] = x[M,K] . dequant(qweight, scales, qzeros), fp16 in / fp32 accumulate / fp16 out.
  * Replaces: awq_gemm(in_feats, kernel, scaling_factors, zeros, split_k_iters)
@@ -122,11 +129,13 @@ int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int *tok_
 
 /* Which kernel variant b200_w4a16_gemm launches for this problem: B200_VARIANT_DECODE
  * (M <= 16 and G % 128 == 0: warp-level mma.sync with the dequantized registers as the A
- * fragment, bandwidth bound) or B200_VARIANT_TCGEN05 (tcgen05 MMA with TMEM operands and
- * accumulators).  Negative: -b200_status_t.  The reference picks between its GEMM kernel and
- * dequantize + cuBLAS on `num_tokens >= 256`
+ * fragment, bandwidth bound), B200_VARIANT_TCDECODE (17 <= M <= 64, G % 128 == 0: tcgen05 MMA
+ * on unscaled (q - z) operands in TMEM, group scale applied to per-tile accumulators by the
+ * epilogue, bandwidth bound) or B200_VARIANT_TCGEN05 (tcgen05 MMA with TMEM operands and
+ * accumulators, compute bound).  Negative: -b200_status_t.  The reference picks between its
+ * GEMM kernel and dequantize + cuBLAS on `num_tokens >= 256`
  * (vllm/model_executor/layers/quantization/awq.py:154). */
-enum { B200_VARIANT_TCGEN05 = 0, B200_VARIANT_DECODE = 1 };
+enum { B200_VARIANT_TCGEN05 = 0, B200_VARIANT_DECODE = 1, B200_VARIANT_TCDECODE = 2 };
 int b200_w4a16_gemm_variant(int M, int K, int N, int G);
 
 /* ---- NVLink peer-memory all-reduce for the row-parallel linears --------------------------
@@ -140,8 +149,9 @@ int b200_w4a16_gemm_variant(int M, int K, int N, int G);
  * to every call.  Larger messages go through NCCL in the Python layer. */
 
 /* Bytes of one rank's region: all-reduce messages up to max_message_bytes, plus (when
- * fused_out_features > 0) the slots of the fused row-parallel GEMM + all-reduce for outputs of
- * up to fused_out_features channels x 16 tokens from `world` ranks.  0 on bad arguments. */
+ * fused_out_features > 0) the packet slots of the fused row-parallel GEMM + all-reduce for
+ * outputs of up to fused_out_features channels x 16 tokens from `world` ranks (two parities x
+ * world x 64 bytes per channel).  0 on bad arguments. */
 size_t b200_w4a16_ar_region_bytes(size_t max_message_bytes, int world, int fused_out_features);
 /* cudaMalloc + zero-fill a region on the current device / free it. */
 int b200_w4a16_ar_alloc(size_t bytes, void **dev_ptr);
@@ -165,10 +175,11 @@ int b200_w4a16_allreduce(void *const *regions, int rank, int world, const uint16
 /* Row-parallel GEMM fused with its all-reduce, decode batches (M <= 16, G % 128 == 0):
  *   y[M,N] = sum over ranks of  x_rank[M,K_rank] . dequant(qweight_rank, ...)      (fp16 out)
  * ONE kernel per rank: a channel tile that finishes its K reduction is rounded to fp16 and
- * pushed over NVLink into every rank's region (peer stores), its arrival is flagged per tile,
- * and each rank sums the arrived copies in rank order with fp32 accumulation -- so the transfer
- * of early tiles overlaps the weight stream of later ones, and the result is bit-identical on
- * every rank and to b200_w4a16_gemm followed by b200_w4a16_allreduce.
+ * pushed over NVLink into every rank's region as 16-byte packets {data, epoch, data, epoch}
+ * (peer stores; no fence, no flag: the receiver polls the packets themselves), and each rank
+ * sums the arrived copies in rank order with fp32 accumulation -- so the transfer of early
+ * tiles overlaps the weight stream of later ones, and the result is bit-identical on every
+ * rank and to b200_w4a16_gemm followed by b200_w4a16_allreduce.
  * Replaces: RowParallelLinear.forward's apply_weights + tensor_model_parallel_all_reduce pair
  * (vllm/model_executor/layers/linear.py:538-542).  qweight is in the B200 layout.  `regions`,
  * `max_message_bytes`, `fused_out_features` as given to b200_w4a16_ar_region_bytes when the

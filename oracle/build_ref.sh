@@ -1,7 +1,9 @@
 #!/bin/bash
-# Compiles the reference's AWQ kernels, unmodified and from where they lie under
-# /root/reference, for sm_100a into oracle/_ref/ref_awq.so (git-ignored, travels with gpurun).
-# No reference source is copied into this repository.  ~4 minutes of nvcc.
+# Compiles the reference's AWQ kernels (csrc/quantization/awq/gemm_kernels.cu) and the two
+# kernels on either side of the quantized linears (csrc/layernorm_kernels.cu,
+# csrc/activation_kernels.cu), unmodified and from where they lie under /root/reference, for
+# sm_100a into oracle/_ref/ref_awq.so (git-ignored, travels with gpurun).
+# No reference source is copied into this repository.  ~6 minutes of nvcc.
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${REFERENCE_ROOT:-/root/reference}"
@@ -20,9 +22,14 @@ PYEOF
 )"
 INC="${TORCH_INC//,/ }"
 COMMON="-O2 -std=c++17 -DTORCH_EXTENSION_NAME=ref_awq -DTORCH_API_INCLUDE_EXTENSION_H -D_GLIBCXX_USE_CXX11_ABI=1 $INC -I$PY_INC -I$REF/csrc"
-nvcc -gencode arch=compute_100a,code=sm_100a $COMMON -Xcompiler -fPIC -c "$SRC" -o "$OUT/gemm_kernels.o"
+for f in "$SRC" "$REF/csrc/layernorm_kernels.cu" "$REF/csrc/activation_kernels.cu"; do
+  nvcc -gencode arch=compute_100a,code=sm_100a $COMMON -Xcompiler -fPIC -c "$f" \
+       -o "$OUT/$(basename "${f%.cu}").o" &
+done
+wait
+for f in gemm_kernels layernorm_kernels activation_kernels; do [ -f "$OUT/$f.o" ] || exit 4; done
 g++ $COMMON -fPIC -c "$HERE/ref_stub.cpp" -o "$OUT/ref_stub.o"
-g++ -shared -o "$OUT/ref_awq$EXT_SUFFIX" "$OUT/gemm_kernels.o" "$OUT/ref_stub.o" \
+g++ -shared -o "$OUT/ref_awq$EXT_SUFFIX" "$OUT/gemm_kernels.o" "$OUT/layernorm_kernels.o" "$OUT/activation_kernels.o" "$OUT/ref_stub.o" \
     -L"$TORCH_LIB" -ltorch -ltorch_cpu -ltorch_python -lc10 -lc10_cuda -ltorch_cuda \
     -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,"$TORCH_LIB"
 rm -f "$OUT"/*.o

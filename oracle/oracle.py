@@ -235,6 +235,23 @@ def make_inputs(M: int, K: int, N: int, G: int = 128, seed: int = 0, signed_scal
 # vectors; the two restatements are checked against each other and against the reference's
 # tolerance ("parity unpinned" beyond that).
 
+def make_norm_inputs(tokens: int, hidden: int, seed: int, scale=None):
+    """Seeded (x, residual, weight) for the RMSNorm parity cases; recipe of the reference's own
+    test (tests/kernels/test_layernorm.py:35-38: weight ~ N(1, 0.1), x scaled by 1/(2 hidden))."""
+    rng = np.random.default_rng(seed)
+    scale = 1.0 / (2 * hidden) if scale is None else scale
+    x = (rng.standard_normal((tokens, hidden)) * scale).astype(np.float16)
+    r = (rng.standard_normal((tokens, hidden)) * scale).astype(np.float16)
+    w = rng.normal(1.0, 0.1, hidden).astype(np.float16)
+    return x, r, w
+
+
+def make_act_inputs(tokens: int, d: int, seed: int, scale: float = 1.0) -> np.ndarray:
+    """Seeded [tokens, 2 d] input of SiLU-and-multiply (tests/kernels/test_activation.py:33)."""
+    rng = np.random.default_rng(seed)
+    return (rng.standard_normal((tokens, 2 * d)) * scale).astype(np.float16)
+
+
 def np_rms_norm_forward(x: np.ndarray, weight: np.ndarray, eps: float, residual=None):
     """RMSNorm._forward (layernorm.py:26-44) for fp16 arrays."""
     x32 = x.astype(np.float32)

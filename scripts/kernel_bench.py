@@ -30,7 +30,12 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--once", action="store_true", help="single eager launch per shape (for ncu)")
     ap.add_argument("--min-mb", type=int, default=512)
+    ap.add_argument("--kernel", default=None, choices=["decode", "tcdecode", "tcgen05"],
+                    help="pin the kernel variant (loads the tuning build: make -C vllm-quick_b200/csrc tune)")
     args = ap.parse_args()
+    if args.kernel:
+        os.environ["B200_W4A16_KERNEL"] = args.kernel
+        pkg._lib.use_library("libb200_w4a16_tune.so")
     dev = torch.device("cuda", 0)
     g = torch.Generator(device=dev).manual_seed(0)
     peak = 6541.5
@@ -79,7 +84,8 @@ def main():
             plan = pkg._lib.gemm_plan(M, K, N)
             print(json.dumps({"M": M, "K": K, "N": N, "us": round(us, 3), "GBps": round(gbs, 1),
                               "hbm_frac": round(gbs / peak, 4), "TFLOPs": round(tf, 2),
-                              "grid": plan["grid"], "tok": plan["tok_tile"], "sets": nsets}))
+                              "grid": plan["grid"], "tok": plan["tok_tile"], "sets": nsets,
+                              "kernel": args.kernel or plan["variant"]}))
             del sets, graph
 
 

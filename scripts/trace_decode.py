@@ -13,8 +13,8 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-os.environ["B200_W4A16_TRACE"] = "1"
 pkg = importlib.import_module("vllm-quick_b200")
+pkg._lib.use_library("libb200_w4a16_trace.so")      # make -C vllm-quick_b200/csrc trace
 
 NAMES = ["entry", "w_filled", "prod_dep", "cons_dep", "tile0", "seg0_done", "seg0_out", "exit",
          "lastseg_done"]
@@ -26,7 +26,10 @@ def main():
     ap.add_argument("--k", type=int, default=4096)
     ap.add_argument("--n", type=int, default=4096)
     ap.add_argument("--launches", type=int, default=6)
+    ap.add_argument("--kernel", default=None, choices=["decode", "tcdecode", "tcgen05"])
     args = ap.parse_args()
+    if args.kernel:
+        os.environ["B200_W4A16_KERNEL"] = args.kernel      # honoured by tuning / trace builds only
     M, K, N, G = args.m, args.k, args.n, 128
     dev = torch.device("cuda", 0)
     g = torch.Generator(device=dev).manual_seed(0)

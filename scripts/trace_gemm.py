@@ -1,7 +1,6 @@
 #!/usr/bin/env python
-"""Pipeline timeline of one GEMM launch (needs `make -C vllm-quick_b200/csrc trace` and
-B200_W4A16_TRACE=1).  Prints, for a few CTAs, per-tile clock offsets of every pipeline role.
-Usage: B200_W4A16_TRACE=1 python scripts/trace_gemm.py --m 16 --k 4096 --n 22016"""
+"""Pipeline timeline of one GEMM launch (needs `make -C vllm-quick_b200/csrc trace`).  Prints, for a few CTAs, per-tile clock offsets of every pipeline role.
+Usage: python scripts/trace_gemm.py --m 16 --k 4096 --n 22016"""
 import argparse
 import ctypes
 import importlib
@@ -13,8 +12,8 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-os.environ["B200_W4A16_TRACE"] = "1"
 pkg = importlib.import_module("vllm-quick_b200")
+pkg._lib.use_library("libb200_w4a16_trace.so")      # make -C vllm-quick_b200/csrc trace
 
 
 def main():
@@ -24,7 +23,10 @@ def main():
     ap.add_argument("--n", type=int, default=22016)
     ap.add_argument("--ctas", default="0,73,147")
     ap.add_argument("--warm", type=int, default=4)
+    ap.add_argument("--kernel", default=None, choices=["decode", "tcdecode", "tcgen05"])
     args = ap.parse_args()
+    if args.kernel:
+        os.environ["B200_W4A16_KERNEL"] = args.kernel      # honoured by tuning / trace builds only
     M, K, N, G = args.m, args.k, args.n, 128
     dev = torch.device("cuda", 0)
     g = torch.Generator(device=dev).manual_seed(0)

@@ -29,6 +29,13 @@ SMALL = [  # (M, K, N, G, seed)
     (16, 512, 256, 256, 4), (5, 1024, 256, 128, 5),
 ]
 FULL = [(16, 4096, 4096, 128, 0), (1, 4096, 12288, 128, 1), (64, 11008, 4096, 128, 2)]
+# RMSNorm / fused_add_rms_norm (csrc/layernorm_kernels.cu) and SiLU-and-multiply
+# (csrc/activation_kernels.cu): (tokens, hidden | d, seed, input scale; None = the reference
+# test's 1 / (2 hidden)).  Small cases whole, large ones as SHA-256 + strided sample.
+NORM = [(1, 4096, 0, None), (7, 768, 1, None), (16, 8192, 2, 1.0), (83, 5120, 3, 1.0),
+        (16, 4096, 4, 4.0), (256, 8192, 5, 1.0)]
+NORM_EPS = 1e-6
+ACT = [(1, 11008, 0, 1.0), (7, 512, 1, 1.0), (16, 14336, 2, 3.0), (83, 13824, 3, 1.0)]
 
 
 def load_ref():
@@ -49,6 +56,15 @@ def dev(a):
 
 def bits(t):
     return t.contiguous().cpu().view(torch.int16).numpy().view(np.uint16)
+
+
+def put(dst, key, a):
+    """Small outputs whole; large ones as SHA-256 of the bytes + a strided sample."""
+    if a.size <= 65536:
+        dst[key] = a
+    else:
+        dst[key + "_sha256"] = np.frombuffer(hashlib.sha256(a.tobytes()).digest(), dtype=np.uint8)
+        dst[key + "_sample"] = a[::3, ::37].copy()
 
 
 def main():
@@ -75,6 +91,24 @@ def main():
         full[f"case{i}_W_sample"] = W[::97, ::89].copy()
         full[f"case{i}_Y_sample"] = Y[:, ::61].copy()
     np.savez_compressed(os.path.join(out_dir, "ref_full.npz"), **full)
+    aux = {}
+    for i, (tokens, hidden, seed, scale) in enumerate(NORM):
+        x, r, w = oracle.make_norm_inputs(tokens, hidden, seed, scale)
+        out = torch.empty_like(dev(x))
+        ref.rms_norm(out, dev(x), dev(w), NORM_EPS)
+        xi, ri = dev(x), dev(r)
+        ref.fused_add_rms_norm(xi, ri, dev(w), NORM_EPS)      # in place: xi = normed, ri = x + r
+        aux[f"norm{i}_shape"] = np.array([tokens, hidden, seed, -1 if scale is None else int(scale)])
+        put(aux, f"norm{i}_out", bits(out))
+        put(aux, f"norm{i}_fused_out", bits(xi))
+        put(aux, f"norm{i}_fused_residual", bits(ri))
+    for i, (tokens, d, seed, scale) in enumerate(ACT):
+        a = oracle.make_act_inputs(tokens, d, seed, scale)
+        out = torch.empty((tokens, d), dtype=torch.float16, device="cuda")
+        ref.silu_and_mul(out, dev(a))
+        aux[f"act{i}_shape"] = np.array([tokens, d, seed, int(scale)])
+        put(aux, f"act{i}_out", bits(out))
+    np.savez_compressed(os.path.join(out_dir, "ref_norm_act.npz"), **aux)
     torch.cuda.synchronize()
     print("golden vectors written to", out_dir, [f for f in os.listdir(out_dir)])
 

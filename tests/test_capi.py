@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol(pkg, cuda_lib):
 
 
 def test_version_and_strerror(cuda_lib):
-    assert cuda_lib.b200_w4a16_version() == 103
+    assert cuda_lib.b200_w4a16_version() == 200
     assert cuda_lib.b200_w4a16_strerror(0) == b"ok"
     assert b"shape" in cuda_lib.b200_w4a16_strerror(1)
     assert b"no sm_100" in cuda_lib.b200_w4a16_strerror(5)
@@ -119,5 +119,5 @@ def test_gemm_plan(pkg, M, K, N, tok, grid):
     assert plan["grid"] == grid
     assert plan["smem_bytes"] <= 227 * 1024
     ws = pkg._lib.lib().b200_w4a16_workspace_bytes(M, K, N, 1)
-    assert 4096 <= ws <= 4096 + 148 * 2 * 128 * 128 * 4
+    assert 256 <= ws <= 148 * 2 * 128 * 128 * 4
     assert pkg._lib.lib().b200_w4a16_workspace_bytes(M, K, N, 0) >= ws + K * N // 2

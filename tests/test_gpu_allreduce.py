@@ -36,7 +36,7 @@ def test_single_gpu_emulation_matches_rank_order_sum(pkg, cuda_lib, world, n):
     max_bytes = 2 * 16 * 8192
     slot = (max_bytes + 255) // 256 * 256
     assert L.b200_w4a16_ar_region_bytes(max_bytes, world, 0) == HEADER + 2 * slot
-    assert L.b200_w4a16_ar_region_bytes(max_bytes, world, 8192) == HEADER + 2 * slot + 2 * world * 8192 * 32
+    assert L.b200_w4a16_ar_region_bytes(max_bytes, world, 8192) == HEADER + 2 * slot + 2 * world * 8192 * 64
     regions = [torch.zeros(HEADER + 2 * slot, dtype=torch.uint8, device="cuda") for _ in range(world)]
     ptrs = (ctypes.c_void_p * world)(*[r.data_ptr() for r in regions])
     g = torch.Generator(device="cuda").manual_seed(n + world)
@@ -85,12 +85,13 @@ def test_packet_allreduce_single_gpu_emulation(pkg, cuda_lib, world, n):
                                      0, s) == pkg._lib.B200_ERR_BAD_ARG
 
 
-def _to_fragment_order(Y, MT):
-    """[16, N] fp16 -> the fused path's slot layout: per 128-channel tile, MT x 128 threads x
-    uint4; thread ct = 32 w + 4 g + t holds tokens 8i+2t, 8i+2t+1 of channels
-    32 w + 16 b + 8 r + g (word 2 b + r), see push_tile in csrc/w4a16_decode.cu."""
+def _to_packets(Y, MT, epoch):
+    """[16, N] fp16 -> the fused path's packet slot of one source rank: per 128-channel tile,
+    2 MT x 128 packets {half2, epoch, half2, epoch}; packet e = (b MT + i) 128 + ct of thread
+    ct = 32 w + 4 g + t holds tokens 8i+2t, 8i+2t+1 of channels 32 w + 16 b + g and + 8
+    (push_packet in csrc/w4a16_decode.cu)."""
     N = Y.shape[1]
-    out = np.zeros((N // 128, MT, 128, 4, 2), dtype=np.float16)
+    data = np.zeros((N // 128, 2 * MT, 128, 2, 2), dtype=np.float16)
     for w in range(4):
         for g in range(8):
             for t in range(4):
@@ -99,15 +100,21 @@ def _to_fragment_order(Y, MT):
                     for b in range(2):
                         for r in range(2):
                             ch = 32 * w + 16 * b + 8 * r + g
-                            out[:, i, ct, 2 * b + r, 0] = Y[8 * i + 2 * t, ch::128]
-                            out[:, i, ct, 2 * b + r, 1] = Y[8 * i + 2 * t + 1, ch::128]
-    return out
+                            data[:, b * MT + i, ct, r, 0] = Y[8 * i + 2 * t, ch::128]
+                            data[:, b * MT + i, ct, r, 1] = Y[8 * i + 2 * t + 1, ch::128]
+    words = data.view(np.uint32).reshape(N // 128, 2 * MT, 128, 2)
+    pk = np.empty((N // 128, 2 * MT, 128, 4), dtype=np.uint32)
+    pk[..., 0] = words[..., 0]
+    pk[..., 2] = words[..., 1]
+    pk[..., 1] = epoch
+    pk[..., 3] = epoch
+    return pk
 
 
-@pytest.mark.parametrize("M,K,N", [(16, 1024, 512), (5, 512, 256), (16, 4096, 4096)])
+@pytest.mark.parametrize("M,K,N", [(16, 1024, 512), (5, 512, 256), (16, 4096, 4096), (16, 1024, 8192), (1, 3584, 8192)])
 def test_fused_gemm_allreduce_single_gpu_emulation(pkg, oracle, cuda_lib, M, K, N):
-    """Rank 0 of a world of two, both regions on cuda:0: rank 1's fp16 tiles and arrival flags
-    are pre-placed, so the kernel never waits on another launch.  Result must equal
+    """Rank 0 of a world of two, both regions on cuda:0: rank 1's packets are pre-placed, so the
+    kernel never waits on another launch.  Result must equal
     fp16(float(fp16(y0)) + float(y1)) with y0 the unfused GEMM of the same inputs."""
     from gpu_util import to_dev
     L = cuda_lib
@@ -121,32 +128,33 @@ def test_fused_gemm_allreduce_single_gpu_emulation(pkg, oracle, cuda_lib, M, K, 
     y0 = pkg.ops.quick_gemm(dx, r, ds, dqz, 8)
     MT = 1 if M <= 8 else 2
     data_off = HEADER + 2 * ((max_bytes + 255) // 256 * 256)
-    slot = fused_n * 32
-    ws = torch.zeros(L.b200_w4a16_workspace_bytes(M, K, N, 1), dtype=torch.uint8, device="cuda")
+    slot = fused_n * 64
+    ws = torch.empty(L.b200_w4a16_workspace_bytes(M, K, N, 1), dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    assert L.b200_w4a16_workspace_init(ws.data_ptr(), ws.numel(), stream) == 0
     rng = np.random.default_rng(M)
     for epoch in (1, 2, 3):
         Y1 = np.zeros((16, N), dtype=np.float16)
         Y1[:M] = rng.standard_normal((M, N)).astype(np.float16)
         par = epoch & 1
-        frag = torch.from_numpy(_to_fragment_order(Y1, MT).view(np.uint8).reshape(-1)).cuda()
+        pk = torch.from_numpy(_to_packets(Y1, MT, epoch).view(np.uint8).reshape(-1)).cuda()
         off = data_off + par * world * slot + 1 * slot
-        regions[0][off: off + frag.numel()] = frag
-        flags = regions[0][4096: 4096 + 2 * 128 * 8 * 4].view(torch.int32).view(2, 128, 8)
-        flags[par, : N // 128, 1] = epoch
+        regions[0][off: off + pk.numel()] = pk
         y = torch.empty((M, N), dtype=torch.float16, device="cuda")
         st = L.b200_w4a16_gemm_allreduce(dx.data_ptr(), r.data_ptr(), ds.data_ptr(), dqz.data_ptr(),
                                          y.data_ptr(), M, K, N, G, 0, ws.data_ptr(), ws.numel(), ptrs,
-                                         0, world, max_bytes, fused_n,
-                                         torch.cuda.current_stream().cuda_stream)
+                                         0, world, max_bytes, fused_n, stream)
         assert st == 0
         torch.cuda.synchronize()
         want = (y0.float() + torch.from_numpy(Y1[:M].astype(np.float32)).cuda()).half()
         assert torch.equal(y, want), epoch
-        # the tile copies it pushed to the "peer" are its own fp16 GEMM output
-        peer = regions[1][data_off + par * world * slot: data_off + par * world * slot + (N // 128) * MT * 2048]
-        mine = _to_fragment_order(np.pad(y0.cpu().numpy(), ((0, 16 - M), (0, 0))), MT).view(np.uint8).reshape(-1)
-        assert np.array_equal(peer.cpu().numpy(), mine)
+        # the packets it pushed to the "peer" (and to itself) carry its own fp16 GEMM output
+        mine = _to_packets(np.pad(y0.cpu().numpy(), ((0, 16 - M), (0, 0))), MT, epoch).view(np.uint8).reshape(-1)
+        for q in range(world):
+            got = regions[q][data_off + par * world * slot: data_off + par * world * slot + mine.size]
+            assert np.array_equal(got.cpu().numpy(), mine), (epoch, q)
         assert int(regions[0][3072:3076].view(torch.int32).item()) == epoch     # call closed
+        assert bool((ws == 0xFF).all())                                         # scratch handed back idle
 
 
 def test_allreduce_rejects_bad_arguments(pkg, cuda_lib):

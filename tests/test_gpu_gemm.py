@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from gpu_util import gemm_err, to_dev
+from gpu_util import gemm_check, gemm_err, sampled_case, to_dev
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-2
@@ -71,6 +71,34 @@ def test_gemm_is_deterministic_and_workspace_self_cleans(pkg, oracle, cuda_lib):
     torch.cuda.synchronize()
     for y in ys[1:]:
         assert torch.equal(ys[0], y)
+    # every launch hands the split-K scratch back in its idle state (all words 0xFFFFFFFF)
+    for ws in pkg.ops._workspaces.values():      # (beyond the slots: scratch of the AWQ-layout entry point)
+        assert bool((ws[:148 * 2 * 128 * 128 * 4] == 0xFF).all())
+
+
+@pytest.mark.parametrize("M", [16, 48, 200])
+def test_two_graphs_on_the_default_capture_stream_replay_in_any_order(pkg, oracle, cuda_lib, M):
+    """The reference captures its graphs with torch.cuda.graph(graph, pool=...) and no stream
+    (worker/model_runner.py:781): all captures share the scratch created eagerly at load time,
+    so a graph other than the first captured one may be the first to replay."""
+    x, qw, s, qz = oracle.make_inputs(M, 4096, 4096, 128, seed=M)
+    dx, ds, dqz = to_dev(x), to_dev(s), to_dev(qz)
+    r = pkg.ops.quick_repack(to_dev(qw))
+    pkg.ops.ensure_workspace(dx.device)
+    eager = pkg.ops.quick_gemm(dx, r, ds, dqz, 8)
+    torch.cuda.synchronize()
+    graphs, outs = [], []
+    for _ in range(2):
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            outs.append(pkg.ops.quick_gemm(dx, r, ds, dqz, 8))
+        graphs.append(gr)
+    graphs[1].replay()
+    torch.cuda.synchronize()
+    assert torch.equal(outs[1], eager)
+    graphs[0].replay(); graphs[1].replay(); graphs[0].replay()
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], eager) and torch.equal(outs[1], eager)
 
 
 def test_gemm_exactness_on_integer_inputs(pkg, oracle, cuda_lib):
@@ -153,7 +181,7 @@ def test_cuda_graph_capture(pkg, oracle, cuda_lib):
     r = pkg.ops.quick_repack(to_dev(qw))
     st = torch.cuda.Stream()
     with torch.cuda.stream(st):
-        eager = pkg.ops.quick_gemm(dx, r, ds, dqz, 8)   # allocates the workspace for this stream
+        eager = pkg.ops.quick_gemm(dx, r, ds, dqz, 8)
         st.synchronize()
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph, stream=st):
@@ -163,3 +191,55 @@ def test_cuda_graph_capture(pkg, oracle, cuda_lib):
         st.synchronize()
     assert torch.equal(out, eager)
     assert torch.isfinite(out2).all()
+
+
+# ---- the exact shapes the driver-run benchmarks use (stream-K segment boundaries depend on
+# (channel tiles, K blocks, 148): every new shape is a new split pattern)
+LLAMA70B_TP = {  # per-rank (K, N) of qkv / o / gate_up / down, vLLM sharding (linear.py:312-552)
+    1: [(8192, 10240), (8192, 8192), (8192, 57344), (28672, 8192)],
+    2: [(8192, 5120), (4096, 8192), (8192, 28672), (14336, 8192)],
+    4: [(8192, 2560), (2048, 8192), (8192, 14336), (7168, 8192)],
+    8: [(8192, 1280), (1024, 8192), (8192, 7168), (3584, 8192)],
+}
+
+
+@pytest.mark.parametrize("tp", [1, 2, 4, 8])
+@pytest.mark.parametrize("layer", [0, 1, 2, 3])
+@pytest.mark.parametrize("M", [1, 16, 40])
+def test_gemm_llama70b_tp_shards(pkg, oracle, cuda_lib, tp, layer, M):
+    K, N = LLAMA70B_TP[tp][layer]
+    x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, 128, seed=tp * 100 + layer * 10 + M)
+    y = pkg.ops.quick_gemm(x, pkg.ops.quick_repack(qw), s, qz, 8)
+    gemm_check(y[:, cols], Yf, TOL, (tp, layer, M))
+
+
+@pytest.mark.parametrize("K,N", [(5120, 15360), (5120, 5120), (5120, 27648), (13824, 5120)])
+@pytest.mark.parametrize("M", [1024, 8192])
+def test_gemm_llama13b_prefill_shapes(pkg, oracle, cuda_lib, M, K, N):
+    # BASELINE configs[2]: every token row, a sample of output channels, against the oracle
+    x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, 128, seed=M + N, n_words=8)
+    y = pkg.ops.quick_gemm(x, pkg.ops.quick_repack(qw), s, qz, 8)
+    gemm_check(y[:, cols], Yf, TOL, (M, K, N))
+
+
+@pytest.mark.parametrize("K,N", [(4096, 14336), (14336, 4096), (4096, 28672), (4096, 768), (512, 4096)])
+@pytest.mark.parametrize("M", [3, 16, 64, 333])
+def test_gemm_mixtral_shapes(pkg, oracle, cuda_lib, M, K, N):
+    # BASELINE configs[4]: expert w1 / w3 (and their merge), w2, attention shards at TP = 8
+    x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, 128, seed=M + K + N, n_words=16)
+    y = pkg.ops.quick_gemm(x, pkg.ops.quick_repack(qw), s, qz, 8)
+    gemm_check(y[:, cols], Yf, TOL, (M, K, N))
+
+
+@pytest.mark.parametrize("M", [17, 24, 32, 33, 48, 64])
+@pytest.mark.parametrize("K,N", [(4096, 4096), (4096, 22016), (11008, 4096), (1024, 8192), (256, 128), (4096, 192)])
+def test_gemm_tcgen05_decode_mode(pkg, oracle, cuda_lib, M, K, N):
+    """17..64 tokens with G % 128 == 0: the tcgen05 kernel in decode mode (unscaled operands in
+    TMEM, group scale applied to per-tile accumulators by the epilogue warps)."""
+    assert cuda_lib.b200_w4a16_gemm_variant(M, K, N, 128) == 2
+    x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, 128, seed=M * 7 + N, n_words=min(16, N // 8))
+    y = pkg.ops.quick_gemm(x, pkg.ops.quick_repack(qw), s, qz, 8)
+    gemm_check(y[:, cols], Yf, TOL, (M, K, N))
+    assert torch.equal(y, pkg.ops.quick_gemm(x, pkg.ops.quick_repack(qw), s, qz, 8))   # deterministic
+    xg = torch.zeros_like(x)
+    assert not bool(pkg.ops.quick_gemm(xg, pkg.ops.quick_repack(qw), s, qz, 8).any())   # y(0) == 0

@@ -11,12 +11,22 @@ import subprocess
 from typing import Optional
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-# B200_W4A16_TRACE=1 selects the instrumented build (`make -C csrc trace`), a tuning aid only.
-_TRACE = os.environ.get("B200_W4A16_TRACE") == "1"
-# B200_W4A16_LIB=<file name under lib/> selects a tuning build (`make -C csrc diag DIAG=n`).
-LIB_PATH = os.path.join(_PKG, "lib", os.environ.get("B200_W4A16_LIB") or
-                        ("libb200_w4a16_trace.so" if _TRACE else "libb200_w4a16.so"))
+# The product library.  Tuning harnesses under scripts/ that want an instrumented build
+# (`make -C csrc tune | trace | diag`) call use_library() before the first op; nothing here
+# reads the environment.
+LIB_PATH = os.path.join(_PKG, "lib", "libb200_w4a16.so")
 CSRC = os.path.join(_PKG, "csrc")
+
+
+_lib: Optional[ctypes.CDLL] = None
+
+
+def use_library(file_name: str) -> None:
+    """Tuning aid (scripts/ only): load lib/<file_name> instead of the product library."""
+    global LIB_PATH
+    if _lib is not None:
+        raise B200LibraryError("use_library() must be called before the library is loaded")
+    LIB_PATH = os.path.join(_PKG, "lib", file_name)
 
 B200_OK, B200_ERR_BAD_SHAPE, B200_ERR_BAD_ARG, B200_ERR_WORKSPACE, B200_ERR_CUDA, \
     B200_ERR_NO_DEVICE = range(6)
@@ -32,7 +42,7 @@ EXPORTS = (
     "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
     "b200_w4a16_allreduce", "b200_w4a16_gemm_allreduce", "b200_w4a16_gemm_gated",
     "b200_w4a16_moe_gather", "b200_w4a16_moe_scatter_add", "b200_w4a16_silu_and_mul", "b200_w4a16_gemm_silu_mul", "b200_w4a16_add_rms_norm", "b200_w4a16_allreduce_add_rms_norm",
-    "b200_w4a16_allreduce_add_rms_norm_ll", "b200_w4a16_allreduce_ll",
+    "b200_w4a16_allreduce_add_rms_norm_ll", "b200_w4a16_allreduce_ll", "b200_w4a16_workspace_init",
 )
 
 
@@ -50,9 +60,6 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if res.returncode != 0:
         raise B200LibraryError("building libb200_w4a16.so failed (see output above)")
     return LIB_PATH
-
-
-_lib: Optional[ctypes.CDLL] = None
 
 
 def lib() -> ctypes.CDLL:
@@ -74,6 +81,8 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_repacked_words.argtypes = [i32, i32]
     L.b200_w4a16_workspace_bytes.restype = sz
     L.b200_w4a16_workspace_bytes.argtypes = [i32, i32, i32, i32]
+    L.b200_w4a16_workspace_init.restype = i32
+    L.b200_w4a16_workspace_init.argtypes = [vp, sz, vp]
     L.b200_w4a16_gemm.restype = i32
     L.b200_w4a16_gemm.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, sz, vp]
     L.b200_w4a16_gemm_gated.restype = i32
@@ -146,4 +155,5 @@ def gemm_plan(M: int, K: int, N: int, G: int = 128, split_k_hint: int = 0) -> di
                                      ctypes.byref(smem)), "gemm_plan")
     variant = lib().b200_w4a16_gemm_variant(M, K, N, G)
     return {"tok_tile": tok.value, "split_k": split.value, "grid": grid.value,
-            "smem_bytes": smem.value, "variant": "decode" if variant == 1 else "tcgen05"}
+            "smem_bytes": smem.value,
+            "variant": {0: "tcgen05", 1: "decode", 2: "tcdecode"}.get(variant, str(variant))}

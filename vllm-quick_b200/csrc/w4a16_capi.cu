@@ -13,35 +13,45 @@ namespace {
 
 thread_local int g_last_cuda_error = 0;
 
-constexpr size_t kCounterBytes = 4096;  // arrival counters live at the front of the workspace
-
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Workspace layout: [0, kMaxPartialBytes) self-flagging partial-tile slots (whatever the plan,
+// a launch uses a prefix of it and hands it back all-0xFF) | from kMaxPartialBytes on: scratch
+// for the on-the-fly interleave of checkpoint-layout weights.  The scratch must never overlap
+// ANY plan's slots: leftovers of a repack would read as arrived partial sums.
+constexpr size_t kMaxPartialBytes = (size_t)b200::kMaxCtas * 2 * 128 * b200::kTileN * sizeof(float);
 
 struct DeviceInfo {
   int status;    // b200_status_t of the probe
   int sm_count;
 };
 
-const DeviceInfo& device_info() {
-  static DeviceInfo info = [] {
-    DeviceInfo d{B200_ERR_NO_DEVICE, b200::kMaxCtas};
-    int dev = 0, major = 0, sms = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return d; }
-    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
-      cudaGetLastError();
-      return d;
-    }
-    if (major != 10) return d;
+// Probe of the CURRENT device (a process may drive several): compute capability and the SM
+// count the planner may rely on -- the stream-K kernels need every CTA of the grid resident,
+// so on a device that exposes fewer SMs (MIG slice, MPS share) the grid shrinks with it.
+DeviceInfo device_info() {
+  static DeviceInfo cache[b200::kMaxDevices];
+  static bool known[b200::kMaxDevices] = {};
+  DeviceInfo d{B200_ERR_NO_DEVICE, b200::kMaxCtas};
+  int dev = 0, major = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return d; }
+  if (dev >= 0 && dev < b200::kMaxDevices && known[dev]) return cache[dev];
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess ||
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+    cudaGetLastError();
+    return d;
+  }
+  if (major == 10) {
     d.status = B200_OK;
     d.sm_count = sms < b200::kMaxCtas ? sms : b200::kMaxCtas;
-    return d;
-  }();
-  return info;
+  }
+  if (dev >= 0 && dev < b200::kMaxDevices) { cache[dev] = d; known[dev] = true; }
+  return d;
 }
 
 int sm_count_or_default() {
-  // workspace sizing must work before a device is touched: assume one full B200.
+  // workspace sizing and plan queries must work before a device is touched: one full B200
+  // (an upper bound for the scratch; launches plan with the probed count).
   return b200::kMaxCtas;
 }
 
@@ -59,31 +69,36 @@ bool gemm_shape_ok(int M, int K, int N, int G) {
   return true;
 }
 
-// one rank's fp16 copy of a fused GEMM output: 16 tokens x N, N rounded up to whole tiles
+// one rank's fused GEMM output as 16-byte packets {data, epoch, data, epoch}: 16 tokens x N fp16
+// = 32 B of data per channel, 64 B of packets; N rounded up to whole tiles
 size_t fused_slot_bytes(int out_features) {
-  return (size_t)((out_features + b200::kTileN - 1) / b200::kTileN) * b200::kTileN * 32;
+  return (size_t)((out_features + b200::kTileN - 1) / b200::kTileN) * b200::kTileN * 64;
 }
 
 bool use_pdl() {
+#ifdef B200_TUNING   // `make tune` only: the product library reads no environment variables
   static const bool on = [] {
     const char* e = getenv("B200_W4A16_NO_PDL");
     return !(e && e[0] == '1');
   }();
   return on;
+#else
+  return true;
+#endif
 }
 
 }  // namespace
 
 extern "C" {
 
-int b200_w4a16_version(void) { return 103; }
+int b200_w4a16_version(void) { return 200; }
 
 const char* b200_w4a16_strerror(int status) {
   switch (status) {
     case B200_OK: return "ok";
     case B200_ERR_BAD_SHAPE: return "shape precondition violated";
     case B200_ERR_BAD_ARG: return "null or misaligned pointer, or unknown layout";
-    case B200_ERR_WORKSPACE: return "workspace missing or too small";
+    case B200_ERR_WORKSPACE: return "workspace missing, too small or misaligned (initialise it with b200_w4a16_workspace_init)";
     case B200_ERR_CUDA: return "CUDA call failed";
     case B200_ERR_NO_DEVICE: return "no sm_100 device (this library has no fallback path)";
     default: return "unknown status";
@@ -104,12 +119,21 @@ size_t b200_w4a16_repacked_words(int K, int N) {
 }
 
 size_t b200_w4a16_workspace_bytes(int M, int K, int N, int layout) {
-  if (M <= 0 || K <= 0 || N <= 0) return kCounterBytes;
+  if (M <= 0 || K <= 0 || N <= 0) return 256;
   b200::GemmPlan plan;
   b200::make_gemm_plan(M, K, N, 128, 0, sm_count_or_default(), &plan);
-  size_t bytes = kCounterBytes + align_up(plan.ws_partial_bytes, 256);
-  if (layout == B200_LAYOUT_AWQ) bytes += align_up(b200_w4a16_repacked_words(K, N) * 4, 256);
-  return bytes;
+  size_t bytes = align_up(plan.ws_partial_bytes, 256);
+  if (layout == B200_LAYOUT_AWQ) bytes = kMaxPartialBytes + align_up(b200_w4a16_repacked_words(K, N) * 4, 256);
+  return bytes < 256 ? 256 : bytes;
+}
+
+int b200_w4a16_workspace_init(void* workspace, size_t workspace_bytes, b200_stream_t stream) {
+  if (!workspace || workspace_bytes == 0 || !aligned16(workspace)) return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  // every word of an unwritten partial-tile slot reads as kPartEmpty (w4a16_common.cuh)
+  cudaError_t e = cudaMemsetAsync(workspace, 0xFF, workspace_bytes, reinterpret_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? B200_OK : cuda_fail((int)e);
 }
 
 int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int* tok_tile,
@@ -130,7 +154,8 @@ int b200_w4a16_gemm_variant(int M, int K, int N, int G) {
   b200::GemmPlan plan;
   if (b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, 0, sm_count_or_default(), &plan))
     return -B200_ERR_BAD_SHAPE;
-  return plan.kind == b200::kKindDecode ? B200_VARIANT_DECODE : B200_VARIANT_TCGEN05;
+  return plan.kind == b200::kKindDecode ? B200_VARIANT_DECODE
+         : plan.kind == b200::kKindTcDecode ? B200_VARIANT_TCDECODE : B200_VARIANT_TCGEN05;
 }
 
 int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
@@ -169,7 +194,7 @@ int b200_w4a16_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int 
   if (d <= 0 || d % 8 != 0 || (paired != 0 && paired != 1)) return B200_ERR_BAD_SHAPE;
   if (rows == 0) return B200_OK;
   if (!in || !out || !aligned16(in) || !aligned16(out)) return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_silu_and_mul(in, out, rows, d, paired, reinterpret_cast<cudaStream_t>(stream));
   return e == 0 ? B200_OK : cuda_fail(e);
@@ -187,39 +212,37 @@ static int gemm_impl(const uint16_t* x, const int32_t* qweight, const uint16_t* 
   if (!aligned16(x) || !aligned16(qweight) || !aligned16(scales) || !aligned16(qzeros) ||
       !aligned16(y))
     return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
 
   b200::GemmPlan plan;
-  if (b200::make_gemm_plan(M, K, N, G, split_k_hint, sm_count_or_default(), &plan))
+  if (b200::make_gemm_plan(M, K, N, G, split_k_hint, dev.sm_count, &plan))
     return B200_ERR_BAD_SHAPE;
   const size_t part_bytes = align_up(plan.ws_partial_bytes, 256);
-  size_t need = kCounterBytes + part_bytes;
-  if (layout == B200_LAYOUT_AWQ) need += align_up(b200_w4a16_repacked_words(K, N) * 4, 256);
-  if (!workspace || workspace_bytes < need || !aligned16(workspace)) return B200_ERR_WORKSPACE;
-  if (plan.ws_counter_bytes > kCounterBytes) return B200_ERR_WORKSPACE;
+  size_t need = part_bytes;
+  if (layout == B200_LAYOUT_AWQ) need = kMaxPartialBytes + align_up(b200_w4a16_repacked_words(K, N) * 4, 256);
+  if (part_bytes > kMaxPartialBytes || !workspace || workspace_bytes < need || !aligned16(workspace))
+    return B200_ERR_WORKSPACE;
   if (act && plan.kind != b200::kKindDecode) return B200_ERR_BAD_SHAPE;
 
   uint8_t* ws = static_cast<uint8_t*>(workspace);
-  int* counters = reinterpret_cast<int*>(ws);
-  void* partials = ws + kCounterBytes;
+  void* partials = ws;
   const int32_t* qw = qweight;
   bool pdl = use_pdl();
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (layout == B200_LAYOUT_AWQ) {
     // Checkpoint-layout weights: interleave into scratch first.  The weight prefetch of the
     // GEMM must then wait for the repack, so programmatic launch is off for this call.
-    int32_t* scratch = reinterpret_cast<int32_t*>(ws + kCounterBytes + part_bytes);
+    int32_t* scratch = reinterpret_cast<int32_t*>(ws + kMaxPartialBytes);
     int e = b200::launch_repack(qweight, scratch, K, N, B200_REPACK_AWQ_TO_B200, s);
     if (e != 0) return cuda_fail(e);
     qw = scratch;
     pdl = false;
   }
   int e = plan.kind == b200::kKindDecode
-              ? b200::launch_decode(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters,
-                                    pdl, s, nullptr, gate, act)
-              : b200::launch_gemm(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, counters,
-                                  pdl, s);
+              ? b200::launch_decode(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, pdl, s,
+                                    nullptr, gate, act)
+              : b200::launch_gemm(x, qw, scales, qzeros, y, M, K, N, G, plan, partials, pdl, s);
   if (e != 0) return cuda_fail(e);
   return B200_OK;
 }
@@ -239,7 +262,7 @@ int b200_w4a16_dequant(const int32_t* qweight, const uint16_t* scales, const int
   if (!aligned16(qweight) || !aligned16(scales) || !aligned16(W) ||
       (reinterpret_cast<uintptr_t>(qzeros) & 3u))
     return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_dequant(qweight, scales, qzeros, W, K, N, G, layout,
                                reinterpret_cast<cudaStream_t>(stream));
@@ -255,7 +278,7 @@ int b200_w4a16_repack(const int32_t* src, int32_t* dst, int K, int N, int direct
   if (!src || !dst || src == dst || (reinterpret_cast<uintptr_t>(src) & 3u) ||
       (reinterpret_cast<uintptr_t>(dst) & 3u))
     return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_repack(src, dst, K, N, direction, reinterpret_cast<cudaStream_t>(stream));
   return e == 0 ? B200_OK : cuda_fail(e);
@@ -283,34 +306,30 @@ int b200_w4a16_gemm_allreduce(const uint16_t* x, const int32_t* qweight, const u
     return B200_ERR_BAD_ARG;
   for (int q = 0; q < world; ++q)
     if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   b200::GemmPlan plan;
-  if (b200::make_gemm_plan(M, K, N, G, split_k_hint, sm_count_or_default(), &plan)) return B200_ERR_BAD_SHAPE;
-  if (plan.kind != b200::kKindDecode) return B200_ERR_BAD_SHAPE;   // pinned to the tcgen05 variant
+  if (b200::make_gemm_plan(M, K, N, G, split_k_hint, dev.sm_count, &plan)) return B200_ERR_BAD_SHAPE;
+  if (plan.kind != b200::kKindDecode) return B200_ERR_BAD_SHAPE;   // pinned to another variant (tuning builds)
   const size_t part_bytes = align_up(plan.ws_partial_bytes, 256);
-  if (!workspace || workspace_bytes < kCounterBytes + part_bytes || !aligned16(workspace))
-    return B200_ERR_WORKSPACE;
-  if (plan.ws_counter_bytes > kCounterBytes) return B200_ERR_WORKSPACE;
+  if (!workspace || workspace_bytes < part_bytes || !aligned16(workspace)) return B200_ERR_WORKSPACE;
   b200::FusedArParams ar;
   for (int q = 0; q < b200::kArMaxRanks; ++q)
     ar.region[q] = q < world ? static_cast<uint8_t*>(regions[q]) : nullptr;
   ar.rank = rank;
   ar.world = world;
   ar.ctr_off = b200::kArFusedCtrOff;
-  ar.flag_off = b200::kArFusedFlagOff;
   ar.data_off = (uint32_t)b200::ar_region_bytes(max_message_bytes);
   ar.slot_bytes = (uint32_t)fused_slot_bytes(fused_out_features);
   uint8_t* ws = static_cast<uint8_t*>(workspace);
-  int e = b200::launch_decode(x, qweight, scales, qzeros, y, M, K, N, G, plan, ws + kCounterBytes,
-                              reinterpret_cast<int*>(ws), use_pdl(),
+  int e = b200::launch_decode(x, qweight, scales, qzeros, y, M, K, N, G, plan, ws, use_pdl(),
                               reinterpret_cast<cudaStream_t>(stream), &ar);
   return e == 0 ? B200_OK : cuda_fail(e);
 }
 
 int b200_w4a16_ar_alloc(size_t bytes, void** dev_ptr) {
   if (!dev_ptr || bytes == 0) return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   cudaError_t e = cudaMalloc(dev_ptr, bytes);
   if (e != cudaSuccess) return cuda_fail((int)e);
@@ -360,7 +379,7 @@ int b200_w4a16_allreduce(void* const* regions, int rank, int world, const uint16
   if (!regions || !in || !out || !aligned16(in) || !aligned16(out)) return B200_ERR_BAD_ARG;
   for (int q = 0; q < world; ++q)
     if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_allreduce(regions, rank, world, in, out, n_halfs, max_message_bytes,
                                  barrier, reinterpret_cast<cudaStream_t>(stream));
@@ -373,7 +392,7 @@ int b200_w4a16_moe_gather(const uint16_t* x, const int32_t* idx, uint16_t* out, 
   if (rows == 0) return B200_OK;
   if (!x || !idx || !out || !aligned16(x) || !aligned16(out) || (reinterpret_cast<uintptr_t>(idx) & 3u))
     return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_moe_gather(x, idx, out, rows, hidden, reinterpret_cast<cudaStream_t>(stream));
   return e == 0 ? B200_OK : cuda_fail(e);
@@ -386,7 +405,7 @@ int b200_w4a16_moe_scatter_add(const uint16_t* y, const int32_t* idx, const floa
   if (!y || !idx || !w || !acc || !aligned16(y) || !aligned16(acc) ||
       (reinterpret_cast<uintptr_t>(idx) & 3u) || (reinterpret_cast<uintptr_t>(w) & 3u))
     return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_moe_scatter_add(y, idx, w, acc, rows, hidden, reinterpret_cast<cudaStream_t>(stream));
   return e == 0 ? B200_OK : cuda_fail(e);
@@ -403,7 +422,7 @@ int b200_w4a16_add_rms_norm(const uint16_t* in, const uint16_t* residual_in, con
   if (!in || !weight || !out || !aligned16(in) || !aligned16(weight) || !aligned16(out) ||
       !aligned16(residual_in) || !aligned16(residual_out))
     return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_add_rmsnorm(in, residual_in, weight, out, residual_out, eps, rows, hidden,
                                    reinterpret_cast<cudaStream_t>(stream));
@@ -426,7 +445,7 @@ int b200_w4a16_allreduce_add_rms_norm(void* const* regions, int rank, int world,
     return B200_ERR_BAD_ARG;
   for (int q = 0; q < world; ++q)
     if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_allreduce_add_rmsnorm(regions, rank, world, in, residual_in, weight, out,
                                              residual_out, eps, rows, hidden, max_message_bytes,
@@ -446,7 +465,7 @@ int b200_w4a16_allreduce_ll(void* const* regions, int rank, int world, const uin
   if (!regions || !in || !out || !aligned16(in) || !aligned16(out)) return B200_ERR_BAD_ARG;
   for (int q = 0; q < world; ++q)
     if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_allreduce(regions, rank, world, in, out, n_halfs, 0, barrier,
                                  reinterpret_cast<cudaStream_t>(stream), ll_offset, ll_message_bytes);
@@ -472,7 +491,7 @@ int b200_w4a16_allreduce_add_rms_norm_ll(void* const* regions, int rank, int wor
     return B200_ERR_BAD_ARG;
   for (int q = 0; q < world; ++q)
     if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
-  const DeviceInfo& dev = device_info();
+  const DeviceInfo dev = device_info();
   if (dev.status != B200_OK) return dev.status;
   int e = b200::launch_allreduce_add_rmsnorm(regions, rank, world, in, residual_in, weight, out,
                                              residual_out, eps, rows, hidden, 0, barrier,

@@ -103,6 +103,18 @@ __device__ __forceinline__ void dequant_word_zs1(uint32_t w, uint32_t zlo, uint3
   o3 = hfma2_u32(a3, s2, 0u);  // rows (6,7)
 }
 
+// One packed word -> (q - z) for its eight K rows as four half2 (exact; NO scale): the decode
+// variants apply the group scale to the fp32 accumulator instead (9 instead of 13 operations).
+__device__ __forceinline__ void unpack_sub_zero(uint32_t w, uint32_t zlo, uint32_t zhi,
+                                                uint32_t& o0, uint32_t& o1, uint32_t& o2,
+                                                uint32_t& o3) {
+  const uint32_t t = w >> 8;
+  o0 = hsub2_u32(lop3_and_or(w, 0x000f000fu, 0x64006400u), zlo);               // rows (0,1)
+  o1 = hfma2_u32(lop3_and_or(w, 0x00f000f0u, 0x64006400u), 0x2c002c00u, zhi);  // rows (2,3)
+  o2 = hsub2_u32(lop3_and_or(t, 0x000f000fu, 0x64006400u), zlo);               // rows (4,5)
+  o3 = hfma2_u32(lop3_and_or(t, 0x00f000f0u, 0x64006400u), 0x2c002c00u, zhi);  // rows (6,7)
+}
+
 // Zero point of channel c (0..127 inside a tile) from a row of 16 packed zero words.
 __device__ __forceinline__ uint32_t zero_of_channel(const uint32_t* zrow, int c) {
   return (zrow[c >> 3] >> (4 * awq_nibble(c & 7))) & 0xFu;
@@ -142,10 +154,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   return ok != 0;
 }
 
-// Bounded wait: a pipeline bug must surface as a trapped launch, never as a hung GPU.
+// Bounded waits.  Inside one GPU a pipeline bug must surface as a trapped launch, never as a
+// hung device: B200_WATCHDOG_CYCLES (~2 s) bounds every wait on this GPU's own CTAs.  Waits on
+// ANOTHER rank are different: seconds of skew are ordinary in serving (uneven checkpoint
+// load, a GC pause, a debugger), the reference's kernels and NCCL simply wait -- so every
+// cross-rank spin shares B200_PEER_WATCHDOG_CYCLES, ~10 minutes by default (0 = wait forever),
+// and traps only as a last resort against a dead peer.
 #ifndef B200_WATCHDOG_CYCLES
 #define B200_WATCHDOG_CYCLES (4000000000ll)  // ~2 s at 1.9 GHz
 #endif
+#ifndef B200_PEER_WATCHDOG_CYCLES
+#define B200_PEER_WATCHDOG_CYCLES (1200000000000ll)  // ~10 min at 1.9 GHz
+#endif
+__device__ __forceinline__ bool peer_wait_expired(long long t0) {
+  return B200_PEER_WATCHDOG_CYCLES > 0 && clock64() - t0 > B200_PEER_WATCHDOG_CYCLES;
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
@@ -348,6 +371,67 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* addr) {
   int v;
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
   return v;
+}
+
+// 16-byte accesses for data another CTA (or another GPU) writes while we poll it.
+//  * `volatile` = strong, system scope (SASS LDG/STG.E.128.STRONG.SYS): always performed at
+//    the coherence point; what the NVLink packets and every RE-poll use.  Strong loads of one
+//    thread complete one after the other, though -- a chain of L2 round trips as long as the
+//    number of contributors (measured: profiles/r2c_trace_decode_4096.log, 2.2 us).
+//  * `weak_na` = weak, L1 no-allocate (LDG.E.NA.128): tuning builds only (flag 2).  It was
+//    tried for the first look at a slot and REJECTED: it neither shortened the fix-up nor stayed
+//    correct (stale words made back-to-back launches differ, profiles/r2e notes in DESIGN.md).
+__device__ __forceinline__ uint4 ld_volatile_u4(const void* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_volatile_u4(void* p, uint4 v) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_weak_na_u4(const void* p) {
+  uint4 v;
+  asm volatile("ld.weak.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+// First look at a polled slot: strong like every other poll (flag 2 of a tuning build: weak).
+constexpr int kFlagNoEvictFirst = 1, kFlagWeakFirstPoll = 2;
+__device__ __forceinline__ uint4 ld_first_poll_u4(const void* p, int flags) {
+  return (flags & kFlagWeakFirstPoll) ? ld_weak_na_u4(p) : ld_volatile_u4(p);
+}
+
+// Stream-K partial tiles travel through L2 as SELF-FLAGGING fp32 words: a slot that has not been
+// written holds kPartEmpty (an fp32 NaN bit pattern no arithmetic produces: hardware NaNs are
+// 0x7fffffff) in every word; the contributor stores its sums (a real value can never alias the
+// marker: part_word clamps), the owner polls the words themselves and puts the marker back.
+// One L2 hop, no fence, no counter, no flag -- and the workspace is left as it was found.
+constexpr uint32_t kPartEmpty = 0xFFFFFFFFu;
+__device__ __forceinline__ uint32_t part_word(float v) { return min(__float_as_uint(v), 0xFFFFFFFEu); }
+__device__ __forceinline__ uint4 part_pack(float a, float b, float c, float d) {
+  return make_uint4(part_word(a), part_word(b), part_word(c), part_word(d));
+}
+__device__ __forceinline__ bool part_ready(const uint4& v) {
+  return v.x != kPartEmpty && v.y != kPartEmpty && v.z != kPartEmpty && v.w != kPartEmpty;
+}
+// Wait for one 16-byte group of a contributor's partial tile, take it, restore the marker.
+__device__ __forceinline__ float4 part_take(uint4* slot, uint4 first) {
+  uint4 v = first;
+  if (!part_ready(v)) {
+    const long long t0 = clock64();
+    do {
+      v = ld_volatile_u4(slot);
+      if (clock64() - t0 > B200_WATCHDOG_CYCLES) {
+        printf("b200_w4a16: stream-K partial timeout block %d thread %d\n", blockIdx.x, threadIdx.x);
+        __trap();
+      }
+    } while (!part_ready(v));
+  }
+  st_volatile_u4(slot, make_uint4(kPartEmpty, kPartEmpty, kPartEmpty, kPartEmpty));
+  return make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z),
+                     __uint_as_float(v.w));
 }
 
 // silu(gate) * up on two GEMM outputs, exactly as the unfused pair computes it: the GEMM rounds

@@ -13,6 +13,8 @@
 //
 //  * same B200 weight layout, same stream-K decomposition and deterministic fix-up as the
 //    tcgen05 kernel: contiguous 8 KiB tiles arrive by 1-D bulk async copy on an mbarrier ring.
+//    Partial tiles cross CTAs as self-flagging fp32 words through L2 (kPartEmpty, one hop: no
+//    fence, no counter) and are summed in CTA order by all consumer threads of the owner.
 //  * a consumer warp owns 32 output channels of the 128-channel tile and all 128 K rows.
 //    Lane (g,t) reads word t of channel g (one 4-byte, bank-conflict-free load), expands it
 //    with the exact lop3 / sub / fma sequence into (q - z) as four half2 -- which already are
@@ -22,8 +24,10 @@
 //  * the group scale is applied to the fp32 group accumulator (one FFMA per accumulator per
 //    128 rows) instead of to every weight: (q - z) stays exact, the GEMM result differs from
 //    fp16-rounded-W arithmetic by < 2^-11 relative per term (tolerance 1e-2, test_gpu_gemm).
-//  * two CTAs per SM (296 CTAs): the next kernel's CTAs slot in under programmatic dependent
-//    launch and prefetch their weights while this kernel's tail drains.
+//  * one persistent CTA per SM; under programmatic dependent launch the next kernel's CTAs
+//    prefetch their whole weight ring while this kernel's tail (fix-up, exchange) drains.
+//  * row-parallel fusion (ar.world > 1): finished fp16 tiles go to every rank as 16-byte
+//    packets {data, epoch, data, epoch} -- the receiver polls the packets themselves.
 #include "w4a16_common.cuh"
 #include "w4a16_internal.h"
 #include "w4a16_streamk.cuh"
@@ -54,12 +58,7 @@ constexpr int kConsumerThreads = kDecGroups * kGroupThreads;
 // wait + three bulk copies per 8 KiB tile) must never queue behind dequant arithmetic.
 constexpr int kFirstConsumerWarp = 0;
 constexpr int kWProducerWarp = kDecGroups * kGroupWarps;      // first of kDecGroups producer warps
-// One helper warp takes the two L2 round trips of the stream-K protocol off the consumers:
-// the release fence + counter add that publishes a partial tile, and the acquire spin of the
-// tile's owner.  (On a consumer thread each stalls its warp -- and with it the group's next
-// tile -- for ~0.8 us; profiles/r1d_decode_diag.md.)
-constexpr int kHelperWarp = kWProducerWarp + kDecGroups;
-constexpr int kDecThreads = (kHelperWarp + 1) * 32;
+constexpr int kDecThreads = (kWProducerWarp + kDecGroups) * 32;
 
 template <int MT>
 struct DCfg {
@@ -92,8 +91,7 @@ struct DecodeParams {
   const uint16_t* scales;
   const uint32_t* qz;
   uint16_t* y;
-  float* partials;
-  int* counters;
+  uint4* partials;   // [CTA][2 slots][2 MT x 128] self-flagging fp32 quads (kPartEmpty = unwritten)
   int M, K, N;
   int KB, NT;
   int T, P;
@@ -140,20 +138,6 @@ __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 
-__device__ __forceinline__ void st_release_sys_u32(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ uint4 ld_volatile_u4(const uint4* p) {
-  uint4 v;
-  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-  return v;
-}
 __device__ __forceinline__ uint32_t pack_half2(float a, float b) {
   const __half2 h = __floats2half2_rn(a, b);
   return *reinterpret_cast<const uint32_t*>(&h);
@@ -169,16 +153,6 @@ __device__ __forceinline__ void mma_16816(float (&d)[4], uint32_t a0, uint32_t a
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-// One packed word -> (q - z) for its eight K rows as four half2 (exact; no scale).
-__device__ __forceinline__ void unpack_sub_zero(uint32_t w, uint32_t zlo, uint32_t zhi,
-                                                uint32_t& o0, uint32_t& o1, uint32_t& o2,
-                                                uint32_t& o3) {
-  const uint32_t t = w >> 8;
-  o0 = hsub2_u32(lop3_and_or(w, 0x000f000fu, 0x64006400u), zlo);               // rows (0,1)
-  o1 = hfma2_u32(lop3_and_or(w, 0x00f000f0u, 0x64006400u), 0x2c002c00u, zhi);  // rows (2,3)
-  o2 = hsub2_u32(lop3_and_or(t, 0x000f000fu, 0x64006400u), zlo);               // rows (4,5)
-  o3 = hfma2_u32(lop3_and_or(t, 0x00f000f0u, 0x64006400u), 0x2c002c00u, zhi);  // rows (6,7)
-}
 
 template <int MT>
 __global__ void __launch_bounds__(kDecThreads, 1)
@@ -208,7 +182,7 @@ w4a16_decode_kernel(const DecodeParams p) {
   }
   __syncthreads();
 
-  if (warp >= kWProducerWarp && warp < kHelperWarp) {
+  if (warp >= kWProducerWarp) {
     // ---------------- producers: kDecGroups warps, warp w feeds the tiles of walk indices
     // = w mod kDecGroups, i.e. exactly the stages consumer group w drains.  Lane 0 streams the
     // weights, scales and zeros (bulk copies); all 32 lanes stage x[:, K block] into fragment
@@ -319,44 +293,6 @@ w4a16_decode_kernel(const DecodeParams p) {
       issue_x(c);
       advance(c);
     }
-  } else if (warp == kHelperWarp) {
-    // ---------------- helper: publishes group 0's partial tiles and waits for the contributors
-    asm volatile("griddepcontrol.wait;" ::: "memory");        // the counters belong to earlier work until now
-    if (p.gate && *reinterpret_cast<const volatile int*>(p.gate) == 0) return;   // expert without tokens
-    const bool fused = p.ar.world > 1;
-    int own_nt = -1, own_last = 0;
-    bool own_local = false;
-    for (int idx = 0; idx < walk.nseg; ++idx) {
-      int t0, n;
-      walk.seg(idx, t0, n);
-      if (n == p.KB) continue;
-      const int nt = t0 / p.KB;
-      const int owner = owner_of(nt * p.KB, p.P, p.T);
-      if (owner == (int)blockIdx.x) {
-        own_nt = nt;
-        own_last = owner_of(nt * p.KB + p.KB - 1, p.P, p.T);
-        own_local = !fused && idx == walk.nseg - 1;
-        if (own_local) continue;                              // handed over in shared memory
-      }
-      // group 0 has issued the stores of this partial tile (barrier 5 / 6: slot 0 / 1)
-      if (idx == 0) named_bar_sync(5, kGroupThreads + 32); else named_bar_sync(6, kGroupThreads + 32);
-      if (lane == 0) red_add_release_gpu(p.counters + owner, 1);
-    }
-    if (!fused && own_nt >= 0) {
-      if (lane == 0) {
-        const int need = own_last - (int)blockIdx.x + (own_local ? 0 : 1);
-        const long long t0 = clock64();
-        while (ld_acquire_gpu(p.counters + blockIdx.x) < need) {
-          if (clock64() - t0 > B200_WATCHDOG_CYCLES) {
-            printf("b200_w4a16: stream-K fix-up timeout block %d\n", blockIdx.x);
-            __trap();
-          }
-        }
-        p.counters[blockIdx.x] = 0;                           // leave the workspace zeroed
-      }
-      __syncwarp();
-      named_bar_sync(4, kConsumerThreads + 32);               // release the consumers' fix-up
-    }
   } else {
     // ---------------- consumer groups: tile i of the walk goes to group i % kDecGroups; inside a
     // group, warp w owns channels 32 w .. 32 w + 31 of the tile
@@ -419,36 +355,30 @@ w4a16_decode_kernel(const DecodeParams p) {
     // ---- row-parallel fusion: a finished tile goes to every rank's region instead of y
     const bool fused = p.ar.world > 1;
     uint32_t epoch = 0, ar_slot = 0;
-    if (fused && grp == 0) {
+    if (fused) {
       // previous fused launch has fully completed (griddepcontrol.wait above): its bump is visible
       epoch = *reinterpret_cast<volatile uint32_t*>(p.ar.region[p.ar.rank] + p.ar.ctr_off) + 1;
       ar_slot = p.ar.data_off + (epoch & 1u) * (uint32_t)p.ar.world * p.ar.slot_bytes;
     }
-    // tile nt of source rank r, slot layout [nt][2 MT quarters][128 threads] x 8 bytes... kept
-    // thread-private: thread ct owns MT uint4 (tokens 8i+2t, +1 of four channels) per tile
-    auto push_tile = [&](int nt, const float (&v)[2][MT][4]) {
-      uint4 frag[MT];
-#pragma unroll
-      for (int i = 0; i < MT; ++i)
-        frag[i] = make_uint4(pack_half2(v[0][i][0], v[0][i][1]), pack_half2(v[0][i][2], v[0][i][3]),
-                             pack_half2(v[1][i][0], v[1][i][1]), pack_half2(v[1][i][2], v[1][i][3]));
+    // A finished tile travels as 16-byte packets {data, epoch, data, epoch}: packet e of tile nt
+    // (e = (b MT + i) 128 + thread-in-group: one accumulator fragment = tokens 8i+2t, +1 of
+    // channels n, n + 8) lands at [parity][source rank][nt][e] of EVERY rank's region, the own
+    // one included.  No fence, no flag: the receiver polls the packets (epochs only grow, so a
+    // stale packet never matches).
+    auto push_packet = [&](int nt, int e, float v0, float v1, float v2, float v3) {
+      const uint4 pk = make_uint4(pack_half2(v0, v1), epoch, pack_half2(v2, v3), epoch);
       const uint32_t off = ar_slot + (uint32_t)p.ar.rank * p.ar.slot_bytes +
-                           ((uint32_t)nt * MT * kGroupThreads + ct) * 16u;
+                           ((uint32_t)nt * (2 * MT * kGroupThreads) + (uint32_t)e) * 16u;
 #pragma unroll
-      for (int q = 0; q < kArMaxRanks; ++q) {
-        if (q < p.ar.world) {
-          uint4* dst = reinterpret_cast<uint4*>(p.ar.region[q] + off);
+      for (int q = 0; q < kArMaxRanks; ++q)
+        if (q < p.ar.world) st_volatile_u4(p.ar.region[q] + off, pk);
+    };
+    auto push_tile = [&](int nt, const float (&v)[2][MT][4]) {
 #pragma unroll
-          for (int i = 0; i < MT; ++i) dst[i * kGroupThreads] = frag[i];
-        }
-      }
-      __threadfence_system();
-      named_bar_sync(1, kGroupThreads);                       // the whole tile is on its way
-      if (ct < p.ar.world) {
-        uint32_t* flag = reinterpret_cast<uint32_t*>(p.ar.region[ct] + p.ar.flag_off) +
-                         (((epoch & 1u) * kArMaxTiles + nt) * kArMaxRanks + p.ar.rank);
-        st_release_sys_u32(flag, epoch);
-      }
+      for (int b = 0; b < 2; ++b)
+#pragma unroll
+        for (int i = 0; i < MT; ++i)
+          push_packet(nt, (b * MT + i) * kGroupThreads + ct, v[b][i][0], v[b][i][1], v[b][i][2], v[b][i][3]);
     };
     auto emit_tile = [&](int nt, const float (&v)[2][MT][4]) {
       if (fused) push_tile(nt, v); else write_y(nt, v);
@@ -625,175 +555,112 @@ w4a16_decode_kernel(const DecodeParams p) {
                 make_float4(tot[b][i][0], tot[b][i][1], tot[b][i][2], tot[b][i][3]);
       } else {
         const int slot = idx == 0 ? 0 : 1;
-        float4* part = reinterpret_cast<float4*>(p.partials) +
-                       ((size_t)blockIdx.x * 2 + slot) * (C::kPartFloats / 4) + ct;
+        uint4* part = p.partials + ((size_t)blockIdx.x * 2 + slot) * (2 * MT * kGroupThreads) + ct;
 #pragma unroll
         for (int b = 0; b < 2; ++b)
 #pragma unroll
           for (int i = 0; i < MT; ++i)
-            __stcg(part + (b * MT + i) * kGroupThreads,
-                   make_float4(tot[b][i][0], tot[b][i][1], tot[b][i][2], tot[b][i][3]));
-        // every partial store is issued: the helper warp fences and publishes, we carry on
-        if (slot == 0) asm volatile("bar.arrive 5, %0;" ::"n"(kGroupThreads + 32) : "memory");
-        else asm volatile("bar.arrive 6, %0;" ::"n"(kGroupThreads + 32) : "memory");
+            st_volatile_u4(part + (b * MT + i) * kGroupThreads,
+                           part_pack(tot[b][i][0], tot[b][i][1], tot[b][i][2], tot[b][i][3]));
       }
       if (ct == 0 && idx == 0) TD(6);
     }
 
-    // ---- deferred fix-up (group 0 of the owning CTA, after all of its tiles): the other
-    // contributors handled this tile FIRST in their walk, so their partials are long there.
-    // Fixed CTA order -> bit-identical results run to run.  Every CTA of the grid is resident
-    // (grid <= SM count, one CTA per SM), so the wait cannot deadlock.
-    if (!fused && own_nt >= 0) {
-      // Non-fused: ALL consumer threads take part, one float4 of the partial tile each, every
-      // contributor's load in flight at once (one L2 round trip instead of one per pair of
-      // contributors on group 0 alone: this tail is on every launch's critical path).
-      const int tid = threadIdx.x - kFirstConsumerWarp * 32;  // 0 .. kConsumerThreads - 1
-      // the helper warp has seen every contributor's counter add (acquire); the barrier also
-      // orders group 0's shared-memory hand-over
-      named_bar_sync(4, kConsumerThreads + 32);
-      constexpr int kEntries = 2 * MT * kGroupThreads;        // float4 per partial tile
-      const float4* pbase = reinterpret_cast<const float4*>(p.partials);
+    // ---- tail: every consumer thread takes part (groups 1.. have nothing else left to do)
+    constexpr int kEntries = 2 * MT * kGroupThreads;          // 16-byte quads per tile
+    const int tid = threadIdx.x - kFirstConsumerWarp * 32;    // 0 .. kConsumerThreads - 1
+    // quad e = (b MT + i) 128 + thread-in-group of tile nt: the accumulator fragment of write_y
+    auto store_entry = [&](int nt, int e, const float (&v)[4]) {
+      const int q = e / kGroupThreads, et = e % kGroupThreads;
+      const int eb = q / MT, ei = q % MT;
+      const int m0 = 8 * ei + 2 * (et & 3);
+      if (p.act) {
+        const int NO = p.N >> 1;
+        const int no = ((nt * kTileN + (et >> 5) * 32 + 16 * eb) >> 1) + ((et & 31) >> 2);
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+          if (m0 + k < p.M && no < NO) p.y[(size_t)(m0 + k) * NO + no] = silu_mul_f16(v[k], v[k + 2]);
+        return;
+      }
+      const int n0 = nt * kTileN + (et >> 5) * 32 + ((et & 31) >> 2) + 16 * eb;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int m = m0 + (k & 1), nn = n0 + (k >> 1) * 8;
+        if (m < p.M && nn < p.N) p.y[(size_t)m * p.N + nn] = __half_as_ushort(__float2half_rn(v[k]));
+      }
+    };
+
+    // ---- deferred stream-K fix-up (the CTA owning the first K block of a split tile): the other
+    // contributors handled this tile FIRST in their walk.  Their quads are polled where they
+    // land (self-flagging words, w4a16_common.cuh), every contributor's load in flight at once,
+    // summed in CTA order -> bit-identical run to run; the slots are handed back empty.  Every
+    // CTA of the grid is resident (grid <= SM count, one CTA per SM): the wait cannot deadlock.
+    if (own_nt >= 0) {
+      named_bar_sync(4, kConsumerThreads);                    // group 0's hand-over is in place
       for (int e = tid; e < kEntries; e += kConsumerThreads) {
-        float4 sum = own_local ? xchg[e] : __ldcg(pbase + ((size_t)blockIdx.x * 2 + own_slot) * kEntries + e);
+        float4 sum;
+        if (own_local) {
+          sum = xchg[e];
+        } else {
+          uint4* sl = p.partials + ((size_t)blockIdx.x * 2 + own_slot) * kEntries + e;
+          sum = part_take(sl, ld_first_poll_u4(sl, p.flags));
+        }
         constexpr int kBatch = 8;
         for (int pc = blockIdx.x + 1; pc <= own_last; pc += kBatch) {
-          float4 f[kBatch];
+          uint4 f[kBatch];
 #pragma unroll
           for (int u = 0; u < kBatch; ++u)
-            if (pc + u <= own_last) f[u] = __ldcg(pbase + ((size_t)(pc + u) * 2) * kEntries + e);
+            if (pc + u <= own_last) f[u] = ld_first_poll_u4(p.partials + ((size_t)(pc + u) * 2) * kEntries + e, p.flags);
 #pragma unroll
           for (int u = 0; u < kBatch; ++u)                    // CTA order: deterministic
-            if (pc + u <= own_last) { sum.x += f[u].x; sum.y += f[u].y; sum.z += f[u].z; sum.w += f[u].w; }
-        }
-        // entry e = (b * MT + i) * 128 + thread-in-group: the fragment layout of write_y
-        const int q = e / kGroupThreads, et = e % kGroupThreads;
-        const int eb = q / MT, ei = q % MT;
-        const int n0 = own_nt * kTileN + (et >> 5) * 32 + ((et & 31) >> 2) + 16 * eb;
-        const int m0 = 8 * ei + 2 * (et & 3);
-        const float v[4] = {sum.x, sum.y, sum.z, sum.w};
-        if (p.act) {
-          const int NO = p.N >> 1;
-          const int no = ((own_nt * kTileN + (et >> 5) * 32 + 16 * eb) >> 1) + ((et & 31) >> 2);
-#pragma unroll
-          for (int k = 0; k < 2; ++k)
-            if (m0 + k < p.M && no < NO) p.y[(size_t)(m0 + k) * NO + no] = silu_mul_f16(v[k], v[k + 2]);
-          continue;
-        }
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int m = m0 + (k & 1), nn = n0 + (k >> 1) * 8;
-          if (m < p.M && nn < p.N) p.y[(size_t)m * p.N + nn] = __half_as_ushort(__float2half_rn(v[k]));
-        }
-      }
-    }
-    if (fused && grp == 0 && own_nt >= 0) {
-      if (ct == 0) {
-        const int need = own_last - (int)blockIdx.x + 1;
-        const long long t0 = clock64();
-        while (ld_acquire_gpu(p.counters + blockIdx.x) < need) {
-          if (clock64() - t0 > B200_WATCHDOG_CYCLES) {
-            printf("b200_w4a16: stream-K fix-up timeout block %d\n", blockIdx.x);
-            __trap();
-          }
-        }
-        p.counters[blockIdx.x] = 0;                           // leave the workspace zeroed
-      }
-      named_bar_sync(1, kGroupThreads);
-      float tot[2][MT][4];
-#pragma unroll
-      for (int b = 0; b < 2; ++b)
-#pragma unroll
-        for (int i = 0; i < MT; ++i)
-#pragma unroll
-          for (int e = 0; e < 4; ++e) tot[b][i][e] = 0.f;
-      const float4* src = reinterpret_cast<const float4*>(p.partials) +
-                          ((size_t)blockIdx.x * 2 + own_slot) * (C::kPartFloats / 4) + ct;
-      const float4* nxt = reinterpret_cast<const float4*>(p.partials) +
-                          ((size_t)(blockIdx.x + 1) * 2) * (C::kPartFloats / 4) + ct;
-      float4 f[2][2 * MT];
-#pragma unroll
-      for (int q = 0; q < 2 * MT; ++q) f[0][q] = __ldcg(src + q * kGroupThreads);
-      // two contributors in flight: the loads of pc + 1 overlap the adds of pc
-#pragma unroll 1
-      for (int pc = blockIdx.x; pc <= own_last; pc += 2, nxt += 4 * (C::kPartFloats / 4)) {
-        if (pc + 1 <= own_last) {
-#pragma unroll
-          for (int q = 0; q < 2 * MT; ++q) f[1][q] = __ldcg(nxt + q * kGroupThreads);
-        }
-#pragma unroll
-        for (int b = 0; b < 2; ++b)
-#pragma unroll
-          for (int i = 0; i < MT; ++i) {
-            tot[b][i][0] += f[0][b * MT + i].x; tot[b][i][1] += f[0][b * MT + i].y;
-            tot[b][i][2] += f[0][b * MT + i].z; tot[b][i][3] += f[0][b * MT + i].w;
-          }
-        if (pc + 2 <= own_last) {
-#pragma unroll
-          for (int q = 0; q < 2 * MT; ++q)
-            f[0][q] = __ldcg(nxt + 2 * (C::kPartFloats / 4) + q * kGroupThreads);
-        }
-        if (pc + 1 <= own_last) {
-#pragma unroll
-          for (int b = 0; b < 2; ++b)
-#pragma unroll
-            for (int i = 0; i < MT; ++i) {
-              tot[b][i][0] += f[1][b * MT + i].x; tot[b][i][1] += f[1][b * MT + i].y;
-              tot[b][i][2] += f[1][b * MT + i].z; tot[b][i][3] += f[1][b * MT + i].w;
+            if (pc + u <= own_last) {
+              const float4 g4 = part_take(p.partials + ((size_t)(pc + u) * 2) * kEntries + e, f[u]);
+              sum.x += g4.x; sum.y += g4.y; sum.z += g4.z; sum.w += g4.w;
             }
         }
+        const float v[4] = {sum.x, sum.y, sum.z, sum.w};
+        if (fused) push_packet(own_nt, e, v[0], v[1], v[2], v[3]);
+        else store_entry(own_nt, e, v);
       }
-      emit_tile(own_nt, tot);
     }
 
-    // ---- fused all-reduce: CTA b reduces channel tiles b, b + P, ... once every rank's copy
-    // has landed in OUR region (local reads), rank order, fp32 accumulate -> bit-identical on
-    // every rank and identical to GEMM-then-all-reduce of fp16 outputs.
-    if (fused && grp == 0) {
+    // ---- fused all-reduce: CTA b reduces channel tiles b, b + P, ... as every rank's packets
+    // land in OUR region (local polls), rank order, fp32 accumulate -> bit-identical on every
+    // rank and identical to GEMM-then-all-reduce of fp16 outputs.
+    if (fused) {
       uint8_t* mine = p.ar.region[p.ar.rank];
       for (int nt = blockIdx.x; nt < p.NT; nt += gridDim.x) {
-        if (ct < p.ar.world) {
-          const uint32_t* flag = reinterpret_cast<const uint32_t*>(mine + p.ar.flag_off) +
-                                 (((epoch & 1u) * kArMaxTiles + nt) * kArMaxRanks + ct);
-          const long long t0 = clock64();
-          while (ld_acquire_sys_u32(flag) != epoch) {
-            if (clock64() - t0 > B200_WATCHDOG_CYCLES) {
-              printf("b200_w4a16: fused all-reduce timeout rank %d tile %d peer %d\n", p.ar.rank, nt, ct);
-              __trap();
-            }
-          }
-        }
-        named_bar_sync(1, kGroupThreads);
-        float sum[2][MT][4];
+        for (int e = tid; e < kEntries; e += kConsumerThreads) {
+          const uint8_t* src = mine + ar_slot + ((uint32_t)nt * kEntries + (uint32_t)e) * 16u;
+          uint4 f[kArMaxRanks];
 #pragma unroll
-        for (int b = 0; b < 2; ++b)
+          for (int q = 0; q < kArMaxRanks; ++q)
+            if (q < p.ar.world) f[q] = ld_first_poll_u4(src + (size_t)q * p.ar.slot_bytes, p.flags);
+          float v[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int i = 0; i < MT; ++i)
-#pragma unroll
-            for (int e = 0; e < 4; ++e) sum[b][i][e] = 0.f;
-        const uint32_t off = ar_slot + ((uint32_t)nt * MT * kGroupThreads + ct) * 16u;
-#pragma unroll
-        for (int q = 0; q < kArMaxRanks; ++q) {
-          if (q < p.ar.world) {
-            const uint4* src = reinterpret_cast<const uint4*>(mine + off + (uint32_t)q * p.ar.slot_bytes);
-#pragma unroll
-            for (int i = 0; i < MT; ++i) {
-              const uint4 f = ld_volatile_u4(src + i * kGroupThreads);
-              const uint32_t w[4] = {f.x, f.y, f.z, f.w};
-#pragma unroll
-              for (int h = 0; h < 4; ++h) {
-                const float2 g2 = __half22float2(*reinterpret_cast<const __half2*>(&w[h]));
-                sum[h >> 1][i][(h & 1) * 2] += g2.x;
-                sum[h >> 1][i][(h & 1) * 2 + 1] += g2.y;
+          for (int q = 0; q < kArMaxRanks; ++q) {
+            if (q < p.ar.world) {
+              if (f[q].y != epoch || f[q].w != epoch) {
+                const long long t0 = clock64();
+                do {
+                  f[q] = ld_volatile_u4(src + (size_t)q * p.ar.slot_bytes);
+                  if (peer_wait_expired(t0)) {
+                    printf("b200_w4a16: fused all-reduce timeout rank %d tile %d source %d\n", p.ar.rank, nt, q);
+                    __trap();
+                  }
+                } while (f[q].y != epoch || f[q].w != epoch);
               }
+              const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&f[q].x));
+              const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&f[q].z));
+              v[0] += lo.x; v[1] += lo.y; v[2] += hi.x; v[3] += hi.y;
             }
           }
+          store_entry(nt, e, v);
         }
-        write_y(nt, sum);
       }
       // the last CTA to get here closes the call: bump the epoch for the next fused launch
-      named_bar_sync(1, kGroupThreads);
-      if (ct == 0) {
+      named_bar_sync(1, kConsumerThreads);
+      if (tid == 0) {
         uint32_t* ctr = reinterpret_cast<uint32_t*>(mine + p.ar.ctr_off);
         __threadfence();
         if (atomicAdd(ctr + 1, 1u) == gridDim.x - 1) {
@@ -809,13 +676,16 @@ w4a16_decode_kernel(const DecodeParams p) {
 
 template <int MT>
 int launch_decode_impl(const DecodeParams& prm, bool pdl, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  // the opt-in is per device: a process may drive several GPUs
+  static bool attr_set[kMaxDevices] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= kMaxDevices || !attr_set[dev]) {
     cudaError_t e = cudaFuncSetAttribute(w4a16_decode_kernel<MT>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          DCfg<MT>::kSmemBytes);
     if (e != cudaSuccess) return (int)e;
-    attr_set = true;
+    if (dev >= 0 && dev < kMaxDevices) attr_set[dev] = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(prm.P);
@@ -831,11 +701,15 @@ int launch_decode_impl(const DecodeParams& prm, bool pdl, cudaStream_t stream) {
 }
 
 int decode_flags() {
+#ifdef B200_TUNING   // `make tune` only: the product library reads no environment variables
   static const int f = [] {
     const char* e = getenv("B200_W4A16_FLAGS");
     return e ? atoi(e) : 0;
   }();
   return f;
+#else
+  return 0;
+#endif
 }
 
 }  // namespace
@@ -847,13 +721,12 @@ void fill_decode_plan(int M, GemmPlan* plan) {
   plan->smem_bytes = mt == 1 ? DCfg<1>::kSmemBytes : DCfg<2>::kSmemBytes;
   plan->ws_partial_bytes = (size_t)plan->ctas * 2 * (mt == 1 ? DCfg<1>::kPartFloats : DCfg<2>::kPartFloats) *
                            sizeof(float);
-  plan->ws_counter_bytes = (size_t)plan->ctas * sizeof(int);
 }
 
 int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                   const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
-                  const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
-                  cudaStream_t stream, const FusedArParams* ar, const int* gate, int act) {
+                  const GemmPlan& plan, void* ws_partials, bool pdl, cudaStream_t stream,
+                  const FusedArParams* ar, const int* gate, int act) {
   DecodeParams prm;
   prm.act = act;
   prm.qw = reinterpret_cast<const uint32_t*>(qw_b200);
@@ -861,8 +734,7 @@ int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* sca
   prm.scales = scales;
   prm.qz = reinterpret_cast<const uint32_t*>(qzeros);
   prm.y = y;
-  prm.partials = reinterpret_cast<float*>(ws_partials);
-  prm.counters = ws_counters;
+  prm.partials = reinterpret_cast<uint4*>(ws_partials);
   prm.M = M; prm.K = K; prm.N = N;
   prm.KB = plan.k_blocks; prm.NT = plan.n_tiles;
   prm.T = plan.n_tiles * plan.k_blocks;

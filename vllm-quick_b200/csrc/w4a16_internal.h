@@ -14,13 +14,15 @@ constexpr int kTileK = 128;        // input rows per weight tile       (8 x UMMA
 constexpr int kTileWords = 2048;   // int32 words per packed tile (8 KiB)
 constexpr int kMaxCtas = 148;      // one CTA per SM on B200
 constexpr int kDecodeCtasPerSm = 1;    // decode kernel residency (w4a16_decode.cu)
-constexpr int kDecodeMaxTokens = 16;   // M above this goes to the tcgen05 kernel
+constexpr int kDecodeMaxTokens = 16;   // mma.sync decode kernel (w4a16_decode.cu) up to here
+constexpr int kTcDecodeMaxTokens = 64; // tcgen05 kernel in decode mode (scale in the epilogue) up to here
+constexpr int kMaxDevices = 64;        // per-device launch state (shared-memory opt-in)
 
-enum GemmKind { kKindTcgen05 = 0, kKindDecode = 1 };
+enum GemmKind { kKindTcgen05 = 0, kKindDecode = 1, kKindTcDecode = 2 };
 
 // How a GEMM is cut into CTAs (stream-K over the (channel tile, token tile, K block) space).
 struct GemmPlan {
-  int kind;          // GemmKind: tcgen05 stream-K kernel or the mma.sync decode kernel
+  int kind;          // GemmKind: tcgen05 kernel (prefill / decode mode) or the mma.sync decode kernel
   int tok_tile;      // tokens per MMA tile (tcgen05 N): 16 / 32 / 64 / 128
   int n_tiles;       // ceil(N / 128)
   int m_tiles;       // ceil(M / tok_tile)
@@ -29,8 +31,7 @@ struct GemmPlan {
   int stages;        // smem pipeline depth
   int smem_bytes;    // dynamic shared memory per CTA
   int max_split;     // most CTAs contributing to one output tile
-  size_t ws_partial_bytes;  // fp32 partial-tile scratch
-  size_t ws_counter_bytes;  // per-output-tile arrival counters (must be zero on entry)
+  size_t ws_partial_bytes;  // fp32 partial-tile scratch (self-flagging words: all 0xFF on entry and exit)
 };
 
 int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, GemmPlan* plan);
@@ -38,8 +39,7 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
 // y[M,N] = x[M,K] . dequant(W) with W in the B200 layout.  Returns cudaError_t.
 int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                 const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
-                const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
-                cudaStream_t stream);
+                const GemmPlan& plan, void* ws_partials, bool pdl, cudaStream_t stream);
 
 // Row-parallel fusion of the decode kernel with the all-reduce (w4a16_decode.cu): where in the
 // ranks' peer-mapped regions the fused path keeps its epoch counter, per-tile flags and slots.
@@ -49,18 +49,16 @@ struct FusedArParams {
   uint8_t* region[kArMaxRanks];        // index = rank; own region at [rank]
   int rank, world;                     // world <= 1: not fused
   uint32_t ctr_off;                    // two u32: epoch of the last fused call, CTA done counter
-  uint32_t flag_off;                   // flags[2 parities][kArMaxTiles][kArMaxRanks] u32
-  uint32_t data_off;                   // slots [2 parities][world][slot_bytes]
-  uint32_t slot_bytes;                 // one rank's fp16 copy of the output, 16 tokens: N * 32
+  uint32_t data_off;                   // packet slots [2 parities][world source ranks][slot_bytes]
+  uint32_t slot_bytes;                 // one rank's output as {data, epoch, data, epoch} packets: 64 B / channel
 };
 
 // Decode variant (M <= 16, G % 128 == 0): same layout, workspace protocol and semantics.
 void fill_decode_plan(int M, GemmPlan* plan);
 int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                   const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
-                  const GemmPlan& plan, void* ws_partials, int* ws_counters, bool pdl,
-                  cudaStream_t stream, const FusedArParams* ar = nullptr,
-                  const int* gate = nullptr, int act = 0);
+                  const GemmPlan& plan, void* ws_partials, bool pdl, cudaStream_t stream,
+                  const FusedArParams* ar = nullptr, const int* gate = nullptr, int act = 0);
 
 // silu(x[:, :d]) * x[:, d:] (paired == 0: the reference's [gate | up] halves) or, paired == 1,
 // the channel-paired order the fused gate_up GEMM uses (every 16 channels = 8 gate + 8 up).
@@ -69,15 +67,13 @@ int launch_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int d, i
 
 // NVLink peer-memory all-reduce (w4a16_allreduce.cu).  Region = header + two data slots.
 // Region layout: [0, 2 KiB) flags[block][rank] | [2 KiB, +256) per-block epochs |
-// [3 KiB, +8) fused epoch + done counter | [4 KiB, 12 KiB) fused flags | [16 KiB ...) two
-// all-reduce slots, then (fused_bytes > 0) 2 x world fused slots.
+// [3 KiB, +8) fused epoch + done counter | [16 KiB ...) two all-reduce slots, then
+// (fused_bytes > 0) 2 x world fused packet slots.
 constexpr int kArMaxBlocks = 64;
 constexpr int kArFlagBytes = kArMaxBlocks * kArMaxRanks * 4;   // flags[block][rank]
 constexpr int kArFusedCtrOff = 3072;
-constexpr int kArFusedFlagOff = 4096;
 constexpr int kArHeaderBytes = 16384;
 static_assert(kArFlagBytes + kArMaxBlocks * 4 <= kArFusedCtrOff, "all-reduce header layout");
-static_assert(kArFusedFlagOff + 2 * kArMaxTiles * kArMaxRanks * 4 <= kArHeaderBytes, "fused flags");
 size_t ar_region_bytes(size_t max_message_bytes);
 int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* in, uint16_t* out,
                      size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream,

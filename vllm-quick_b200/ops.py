@@ -21,23 +21,65 @@ from . import _lib
 from ._lib import LAYOUT_AWQ, LAYOUT_B200
 
 PACK_FACTOR = 8
-# counters (4 KiB) + fp32 partial tiles of one full wave (148 CTAs x 2 x 128 x 128 x 4 B)
-_BASE_WORKSPACE_BYTES = 4096 + 148 * 2 * 128 * 128 * 4
+# fp32 partial tiles of one full wave (148 CTAs x 2 slots x 128 x 128 x 4 B): covers every plan
+_BASE_WORKSPACE_BYTES = 148 * 2 * 128 * 128 * 4
 
+# Split-K scratch (include/b200_w4a16.h: b200_w4a16_workspace_init).  Eager launches use one
+# workspace per (device, stream) -- GEMMs on different streams may overlap.  Launches recorded
+# into a CUDA graph use ONE workspace per device that is created and initialised eagerly,
+# before any capture: the reference's CUDAGraphRunner captures ~35 graphs on torch's own
+# capture stream (worker/model_runner.py:781), and scratch first created inside capture #1
+# would be initialised by a node of that graph only -- replaying any other graph first would
+# read uninitialised partial slots.  Captured graphs of one device therefore share scratch and
+# must not be replayed concurrently with each other (the reference replays one at a time).
 _workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+_capture_workspaces: Dict[int, torch.Tensor] = {}
 
 
 def _stream_ptr(device: torch.device) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
 
+def _device_index(device: torch.device) -> int:
+    return device.index if device.index is not None else torch.cuda.current_device()
+
+
+def _new_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    ws = torch.empty(max(nbytes, _BASE_WORKSPACE_BYTES), dtype=torch.uint8, device=device)
+    with torch.cuda.device(device):
+        _lib.check(_lib.lib().b200_w4a16_workspace_init(ws.data_ptr(), ws.numel(), _stream_ptr(device)),
+                   "workspace init")
+    return ws
+
+
+def ensure_workspace(device: torch.device, nbytes: int = 0) -> None:
+    """Create (eagerly, never inside a capture) the scratch that CUDA-graph captures on
+    ``device`` will use.  Called by the linear methods when weights are created / loaded;
+    call it yourself with a larger ``nbytes`` before capturing ``awq_gemm`` on checkpoint-layout
+    weights (their on-the-fly interleave needs room for the whole matrix)."""
+    device = torch.device(device)
+    idx = _device_index(device)
+    ws = _capture_workspaces.get(idx)
+    if ws is not None and ws.numel() >= nbytes:
+        return
+    if torch.cuda.is_current_stream_capturing():
+        raise RuntimeError("b200 w4a16: the split-K workspace must exist before CUDA-graph capture "
+                           "starts -- call ops.ensure_workspace(device[, nbytes]) first")
+    _capture_workspaces[idx] = _new_workspace(device, nbytes)
+    torch.cuda.current_stream(device).synchronize()      # graphs may replay on any stream
+
+
 def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    """Zero-initialised scratch, one per (device, stream); the kernels leave it zeroed."""
-    key = (device.index if device.index is not None else torch.cuda.current_device(),
-           _stream_ptr(device))
+    idx = _device_index(device)
+    if torch.cuda.is_current_stream_capturing():
+        ensure_workspace(device, nbytes)                  # raises if it would have to allocate
+        return _capture_workspaces[idx]
+    if idx not in _capture_workspaces:
+        ensure_workspace(device)
+    key = (idx, _stream_ptr(device))
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
-        ws = torch.zeros(max(nbytes, _BASE_WORKSPACE_BYTES), dtype=torch.uint8, device=device)
+        ws = _new_workspace(device, nbytes)
         _workspaces[key] = ws
     return ws
 

@@ -108,6 +108,8 @@ class AWQLinearMethod(LinearMethodBase):
         if weights.get("qweight_layout", LAYOUT_CHECKPOINT) == LAYOUT_CHECKPOINT:
             qweight.data = ops.quick_repack(qweight.data.contiguous())
             weights["qweight_layout"] = LAYOUT_INTERLEAVED
+            # load time, never inside a capture: the scratch later CUDA-graph captures will use
+            ops.ensure_workspace(qweight.device)
         return qweight
 
     def pair_gate_up(self, weights: Dict[str, Any]) -> None:
