@@ -46,7 +46,7 @@ namespace {
 // TOP warp ids, one per sub-partition; the epilogue sits above the dequant warps.
 constexpr int kFirstDequantWarp = 0;
 constexpr int kGroups = 4;                              // dequant warpgroups, tiles round-robin
-constexpr int kDequantThreads = kGroups * 128;          // warps 0..15 (warp % 4 == lane quarter)
+// dequant warps 0..15 (warp % 4 == lane quarter)
 constexpr int kFirstEpiWarp = 16;                       // warps 16..19 (warp % 4 == lane quarter)
 constexpr int kEpiThreads = 128;
 constexpr int kAllocWarp = 20;
@@ -502,14 +502,14 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           }
           const float sc = __half2float(__ushort_as_half(sring[(itg % C::kSRing) * kTileN + c]));
           const uint32_t dbase = tmem + lane_base + C::kDCol + (itg % C::kAccSlots) * C::kDStride;
+          uint32_t v[MTOK / 16][16];
 #pragma unroll
-          for (int cc = 0; cc < MTOK; cc += 16) {
-            uint32_t v[16];
-            tmem_ld_x16(dbase + cc, v);
-            tc_wait_ld();
+          for (int cc = 0; cc < MTOK / 16; ++cc) tmem_ld_x16(dbase + cc * 16, v[cc]);
+          tc_wait_ld();
 #pragma unroll
-            for (int e = 0; e < 16; ++e) tot[cc + e] = fmaf(sc, __uint_as_float(v[e]), tot[cc + e]);
-          }
+          for (int cc = 0; cc < MTOK / 16; ++cc)
+#pragma unroll
+            for (int e = 0; e < 16; ++e) tot[cc * 16 + e] = fmaf(sc, __uint_as_float(v[cc][e]), tot[cc * 16 + e]);
           if ((itg + 1) % C::kCommit == 0 || itg == n_total - 1) {
             tc_fence_before();
             mbar_arrive(bar_dempty + 8 * ((itg / C::kCommit) % C::kAccGroups));

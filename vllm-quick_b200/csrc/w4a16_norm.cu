@@ -180,7 +180,7 @@ add_rmsnorm_kernel(const NormParams p) {
         st_release_sys(peer_flag, epoch);
         const long long t0 = clock64();
         while ((int32_t)(ld_acquire_sys(my_flags + q) - epoch) < 0) {     // a peer may already be a call ahead
-          if (clock64() - t0 > 4000000000ll) {
+          if (peer_wait_expired(t0)) {
             printf("b200_w4a16: all-reduce+norm barrier timeout rank %d block %d peer %d\n",
                    p.rank, blockIdx.x, q);
             __trap();
@@ -225,7 +225,7 @@ add_rmsnorm_kernel(const NormParams p) {
             a = ld_volatile_v4(src);
             b = ld_volatile_v4(src + 1);
             if (a.y == epoch && a.w == epoch && b.y == epoch && b.w == epoch) break;
-            if (!p.barrier || clock64() - t0 > 4000000000ll) {
+            if (!p.barrier || peer_wait_expired(t0)) {
               printf("b200_w4a16: all-reduce+norm packet timeout rank %d block %d source %d\n", p.rank,
                      blockIdx.x, q);
               __trap();

@@ -112,8 +112,15 @@ class CustomAllreduce:
                                 weight: torch.Tensor, eps: float) -> torch.Tensor:
         """``residual += all_reduce(partial)`` (in place) and the RMSNorm of it (returned), one
         kernel: all-reduce (linear.py:541-542) + fused_add_rms_norm (llama.py:205-222)."""
-        hidden = partial.shape[-1]
+        from .. import ops
+        _, rows, hidden = ops._norm_args(partial, weight, residual)    # fp16, contiguous, same shape
+        if hidden % 8 or not 0 < hidden <= 16384:
+            raise ValueError("fused all-reduce + RMSNorm needs hidden % 8 == 0 and hidden <= 16384")
+        if partial.numel() * 2 > self.max_bytes:
+            raise ValueError("message larger than the registered peer buffer")
         out = torch.empty_like(partial)
+        if rows == 0:
+            return out
         if self.use_ll and 0 < partial.numel() * 2 <= self.ll_bytes:
             st = _lib.lib().b200_w4a16_allreduce_add_rms_norm_ll(
                 self._regions, self.rank, self.world, partial.data_ptr(), residual.data_ptr(),
