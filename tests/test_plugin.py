@@ -58,3 +58,51 @@ def test_set_weight_attrs_refuses_overwrite(pkg):
     with pytest.raises(AssertionError):
         pkg.set_weight_attrs(t, {"input_dim": 1})
     pkg.set_weight_attrs(t, None)
+
+
+# ---- load-time selection of the method (reference config.py:151-182, weight_utils.py:86-122)
+
+def test_resolve_quantization(pkg):
+    r = pkg.resolve_quantization
+    assert r(None) is None
+    assert r("AWQ") == "awq"
+    assert r(None, {"quant_method": "AWQ"}) == "awq"
+    assert r("awq", {"quant_method": "awq"}) == "awq"
+    assert r("quick", {"quant_method": "awq"}) == "quick"       # QUICK consumes AWQ checkpoints
+    with pytest.raises(ValueError, match="does not match"):
+        r("awq", {"quant_method": "gptq"})
+    with pytest.raises(ValueError, match="Unknown quantization method"):
+        r("squeezellm")
+
+
+def test_get_quant_config_from_files(pkg, tmp_path):
+    import json
+    with pytest.raises(ValueError, match="Cannot find the config file"):
+        pkg.get_quant_config("awq", str(tmp_path))
+    (tmp_path / "config.json").write_text("{}")
+    (tmp_path / "quant_config.json").write_text(json.dumps({"w_bit": 4, "q_group_size": 64, "zero_point": True}))
+    cfg = pkg.get_quant_config("awq", str(tmp_path))
+    assert isinstance(cfg, pkg.AWQConfig) and cfg.group_size == 64
+    (tmp_path / "quantize_config.json").write_text(json.dumps({"bits": 4, "group_size": 128, "zero_point": True}))
+    with pytest.raises(ValueError, match="multiple config files"):
+        pkg.get_quant_config("awq", str(tmp_path))
+    # the HF quantization_config wins over files
+    cfg = pkg.get_quant_config("quick", str(tmp_path), {"bits": 4, "group_size": 128, "zero_point": True,
+                                                        "version": "quick", "quant_method": "awq"})
+    assert isinstance(cfg, pkg.QuickConfig) and cfg.pre_interleaved
+
+
+def test_get_linear_method(pkg, tmp_path):
+    import json
+    assert pkg.get_linear_method(None) is None
+    hf = {"quant_method": "awq", "bits": 4, "group_size": 128, "zero_point": True}
+    m = pkg.get_linear_method(None, hf_quant_config=hf, capability=100)
+    assert type(m) is pkg.AWQLinearMethod
+    m = pkg.get_linear_method("quick", hf_quant_config=hf, capability=100)
+    assert type(m) is pkg.QuickLinearMethod
+    with pytest.raises(ValueError, match="not supported for the current GPU"):
+        pkg.get_linear_method("awq", hf_quant_config=hf, capability=70)
+    with pytest.raises(ValueError, match="is not supported for quantization method"):
+        pkg.get_linear_method("awq", hf_quant_config=hf, dtype=torch.bfloat16, capability=100)
+    (tmp_path / "quantize_config.json").write_text(json.dumps({"bits": 4, "group_size": 128, "zero_point": True}))
+    assert isinstance(pkg.get_linear_method("awq", str(tmp_path), capability=100), pkg.LinearMethodBase)

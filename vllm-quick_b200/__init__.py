@@ -15,5 +15,7 @@ from .activation import LlamaMLP, SiluAndMul  # noqa: F401
 from .mixtral_moe import MixtralMLP, MixtralMoE  # noqa: F401
 from .quantization import (AWQConfig, AWQLinearMethod, QuantizationConfig, QuickConfig,  # noqa: F401
                            QuickLinearMethod, get_quantization_config)
+from . import weight_utils  # noqa: F401
+from .weight_utils import get_linear_method, get_quant_config, resolve_quantization  # noqa: F401
 
 __version__ = "0.1.0"
