@@ -236,7 +236,7 @@ def kernel_name(pkg, M, K, N):
     plan = pkg._lib.gemm_plan(M, K, N)
     if plan["variant"] == "decode":
         return f"w4a16_decode_kernel<{plan['tok_tile'] // 8}>"
-    return f"w4a16_gemm_kernel<{plan['tok_tile']}, {'true' if plan['variant'] == 'tcdecode' else 'false'}>"
+    return f"w4a16_gemm_kernel<{plan['tok_tile']}, {plan['unit_tiles']}>"
 
 
 def rand_awq(torch, dev, g, K, N):

@@ -129,14 +129,17 @@ int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int *tok_
 
 /* Which kernel variant b200_w4a16_gemm launches for this problem: B200_VARIANT_DECODE
  * (M <= 16 and G % 128 == 0: warp-level mma.sync with the dequantized registers as the A
- * fragment, bandwidth bound), B200_VARIANT_TCDECODE (17 <= M <= 64, G % 128 == 0: tcgen05 MMA
- * on unscaled (q - z) operands in TMEM, group scale applied to per-tile accumulators by the
- * epilogue, bandwidth bound) or B200_VARIANT_TCGEN05 (tcgen05 MMA with TMEM operands and
- * accumulators, compute bound).  Negative: -b200_status_t.  The reference picks between its
- * GEMM kernel and dequantize + cuBLAS on `num_tokens >= 256`
+ * fragment, bandwidth bound) or B200_VARIANT_TCGEN05 (tcgen05 MMA with TMEM operands and
+ * accumulators; compute bound from a few hundred tokens up).  Negative: -b200_status_t.  The
+ * reference picks between its GEMM kernel and dequantize + cuBLAS on `num_tokens >= 256`
  * (vllm/model_executor/layers/quantization/awq.py:154). */
-enum { B200_VARIANT_TCGEN05 = 0, B200_VARIANT_DECODE = 1, B200_VARIANT_TCDECODE = 2 };
+enum { B200_VARIANT_TCGEN05 = 0, B200_VARIANT_DECODE = 1 };
 int b200_w4a16_gemm_variant(int M, int K, int N, int G);
+
+/* Introspection: channel tiles per work unit of the tcgen05 kernel for this problem -- 2 when
+ * one activation tile feeds two adjacent 128-channel weight tiles (large problems), else 1
+ * (always 1 for B200_VARIANT_DECODE).  Negative: -b200_status_t. */
+int b200_w4a16_gemm_unit_tiles(int M, int K, int N, int G);
 
 /* ---- NVLink peer-memory all-reduce for the row-parallel linears --------------------------
  * Replaces: tensor_model_parallel_all_reduce after RowParallelLinear's GEMM
@@ -229,6 +232,16 @@ int b200_w4a16_gemm_silu_mul(const uint16_t *x, const int32_t *qweight, const ui
                              const int32_t *qzeros, uint16_t *y, int M, int K, int N, int G,
                              int split_k_hint, void *workspace, size_t workspace_bytes,
                              b200_stream_t stream);
+
+/* The same behind a routed-expert gate (see b200_w4a16_gemm_gated): `gate` points at an int32
+ * on the device; 0 = no token of the batch chose this expert -- nothing is streamed and
+ * y[M, N/2] is zero-filled.  NULL = no gate.  Used for the merged w1 / w3 projection of a
+ * Mixtral expert (vllm/model_executor/models/mixtral_quant.py:87-93). */
+int b200_w4a16_gemm_silu_mul_gated(const uint16_t *x, const int32_t *qweight,
+                                   const uint16_t *scales, const int32_t *qzeros, uint16_t *y,
+                                   int M, int K, int N, int G, int split_k_hint,
+                                   const int32_t *gate, void *workspace, size_t workspace_bytes,
+                                   b200_stream_t stream);
 
 /* ---- residual add + RMSNorm around the row-parallel linears ---------------
  * out[rows, hidden] = half(float(half(x)) * rsqrt(mean(x^2) + eps)) * weight,

@@ -30,7 +30,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--once", action="store_true", help="single eager launch per shape (for ncu)")
     ap.add_argument("--min-mb", type=int, default=512)
-    ap.add_argument("--kernel", default=None, choices=["decode", "tcdecode", "tcgen05"],
+    ap.add_argument("--kernel", default=None, choices=["decode", "tcgen05"],
                     help="pin the kernel variant (loads the tuning build: make -C vllm-quick_b200/csrc tune)")
     args = ap.parse_args()
     if args.kernel:

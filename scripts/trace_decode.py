@@ -26,7 +26,7 @@ def main():
     ap.add_argument("--k", type=int, default=4096)
     ap.add_argument("--n", type=int, default=4096)
     ap.add_argument("--launches", type=int, default=6)
-    ap.add_argument("--kernel", default=None, choices=["decode", "tcdecode", "tcgen05"])
+    ap.add_argument("--kernel", default=None, choices=["decode", "tcgen05"])
     args = ap.parse_args()
     if args.kernel:
         os.environ["B200_W4A16_KERNEL"] = args.kernel      # honoured by tuning / trace builds only

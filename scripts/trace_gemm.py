@@ -23,7 +23,7 @@ def main():
     ap.add_argument("--n", type=int, default=22016)
     ap.add_argument("--ctas", default="0,73,147")
     ap.add_argument("--warm", type=int, default=4)
-    ap.add_argument("--kernel", default=None, choices=["decode", "tcdecode", "tcgen05"])
+    ap.add_argument("--kernel", default=None, choices=["decode", "tcgen05"])
     args = ap.parse_args()
     if args.kernel:
         os.environ["B200_W4A16_KERNEL"] = args.kernel      # honoured by tuning / trace builds only

@@ -34,7 +34,7 @@ def gemm_check(y: torch.Tensor, Yf: np.ndarray, tol: float = 1e-2, what=""):
     return rel, abs_small
 
 
-def sampled_case(oracle, M, K, N, G, seed, n_words=32):
+def sampled_case(oracle, M, K, N, G, seed, n_words=32, edge_words=0):
     """A full-size GEMM problem generated on the GPU (SURVEY.md 8d recipe) plus the fp32 oracle
     result for a random sample of 8 * n_words output channels: only the sampled packed
     columns travel to the host, so any BASELINE shape is checked in well under a second."""
@@ -43,7 +43,12 @@ def sampled_case(oracle, M, K, N, G, seed, n_words=32):
     qz = torch.randint(-2**31, 2**31 - 1, (K // G, N // 8), dtype=torch.int32, device="cuda", generator=g)
     s = (torch.rand((K // G, N), device="cuda", generator=g) * 0.019 + 0.001).half()
     x = torch.randn((M, K), device="cuda", generator=g).half()
-    words = torch.randperm(N // 8, device="cuda", generator=g)[:n_words].sort().values
+    words = torch.randperm(N // 8, device="cuda", generator=g)[:n_words]
+    if edge_words:      # always include the first and the last packed columns (tile-edge cases)
+        edge = torch.cat([torch.arange(edge_words, device="cuda"),
+                          torch.arange(N // 8 - edge_words, N // 8, device="cuda")])
+        words = torch.unique(torch.cat([words, edge]))
+    words = words.sort().values
     cols = (words[:, None] * 8 + torch.arange(8, device="cuda")[None, :]).reshape(-1)
     W = oracle.dequantize(qw[:, words].contiguous().cpu().numpy(),
                           s[:, cols].contiguous().cpu().view(torch.int16).numpy().view(np.float16),

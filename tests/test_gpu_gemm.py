@@ -73,7 +73,7 @@ def test_gemm_is_deterministic_and_workspace_self_cleans(pkg, oracle, cuda_lib):
         assert torch.equal(ys[0], y)
     # every launch hands the split-K scratch back in its idle state (all words 0xFFFFFFFF)
     for ws in pkg.ops._workspaces.values():      # (beyond the slots: scratch of the AWQ-layout entry point)
-        assert bool((ws[:148 * 2 * 128 * 128 * 4] == 0xFF).all())
+        assert bool((ws[:148 * 2 * 2 * 128 * 128 * 4] == 0xFF).all())
 
 
 @pytest.mark.parametrize("M", [16, 48, 200])
@@ -233,13 +233,33 @@ def test_gemm_mixtral_shapes(pkg, oracle, cuda_lib, M, K, N):
 
 @pytest.mark.parametrize("M", [17, 24, 32, 33, 48, 64])
 @pytest.mark.parametrize("K,N", [(4096, 4096), (4096, 22016), (11008, 4096), (1024, 8192), (256, 128), (4096, 192)])
-def test_gemm_tcgen05_decode_mode(pkg, oracle, cuda_lib, M, K, N):
-    """17..64 tokens with G % 128 == 0: the tcgen05 kernel in decode mode (unscaled operands in
-    TMEM, group scale applied to per-tile accumulators by the epilogue warps)."""
-    assert cuda_lib.b200_w4a16_gemm_variant(M, K, N, 128) == 2
+def test_gemm_mid_batches(pkg, oracle, cuda_lib, M, K, N):
+    """17..64 tokens: the tcgen05 kernel with 32- / 64-token tiles (single channel tiles on the
+    small shapes, channel-tile pairs on 4096 -> 22016)."""
+    assert cuda_lib.b200_w4a16_gemm_variant(M, K, N, 128) == 0
     x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, 128, seed=M * 7 + N, n_words=min(16, N // 8))
     y = pkg.ops.quick_gemm(x, pkg.ops.quick_repack(qw), s, qz, 8)
     gemm_check(y[:, cols], Yf, TOL, (M, K, N))
     assert torch.equal(y, pkg.ops.quick_gemm(x, pkg.ops.quick_repack(qw), s, qz, 8))   # deterministic
     xg = torch.zeros_like(x)
     assert not bool(pkg.ops.quick_gemm(xg, pkg.ops.quick_repack(qw), s, qz, 8).any())   # y(0) == 0
+
+
+@pytest.mark.parametrize("M,K,N,G", [
+    (40, 16384, 19 * 128, 128),       # odd channel-tile count with pairs: the phantom tile is dropped
+    (300, 5120, 37 * 128, 128),
+    (130, 16384, 11 * 128 + 64, 128), # ragged last tile
+    (520, 2048, 4096, 64),            # G < 128: two (scale, zero) rows per weight tile
+    (96, 16384, 2560, 32),            # G = 32: four rows per tile
+])
+def test_gemm_channel_tile_pairs(pkg, oracle, cuda_lib, M, K, N, G):
+    """Work units of two channel tiles (one activation tile feeds both) on shapes where the
+    pairing has an edge -- odd tile counts, ragged N, G < 128: every token row, a sample of
+    channels that always includes the first and the last ones."""
+    assert cuda_lib.b200_w4a16_gemm_unit_tiles(M, K, N, G) == 2
+    x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, G, seed=M + N, n_words=12, edge_words=4)
+    r = pkg.ops.quick_repack(qw)
+    y = pkg.ops.quick_gemm(x, r, s, qz, 8)
+    gemm_check(y[:, cols], Yf, TOL, (M, K, N, G))
+    assert torch.isfinite(y).all()
+    assert torch.equal(y, pkg.ops.quick_gemm(x, r, s, qz, 8))   # deterministic

@@ -37,11 +37,11 @@ REPACK_AWQ_TO_B200, REPACK_B200_TO_AWQ = 0, 1
 EXPORTS = (
     "b200_w4a16_version", "b200_w4a16_strerror", "b200_w4a16_last_cuda_error",
     "b200_w4a16_repacked_words", "b200_w4a16_workspace_bytes", "b200_w4a16_gemm",
-    "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan", "b200_w4a16_gemm_variant",
+    "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan", "b200_w4a16_gemm_variant", "b200_w4a16_gemm_unit_tiles",
     "b200_w4a16_ar_region_bytes", "b200_w4a16_ar_alloc", "b200_w4a16_ar_free",
     "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
     "b200_w4a16_allreduce", "b200_w4a16_gemm_allreduce", "b200_w4a16_gemm_gated",
-    "b200_w4a16_moe_gather", "b200_w4a16_moe_scatter_add", "b200_w4a16_silu_and_mul", "b200_w4a16_gemm_silu_mul", "b200_w4a16_add_rms_norm", "b200_w4a16_allreduce_add_rms_norm",
+    "b200_w4a16_moe_gather", "b200_w4a16_moe_scatter_add", "b200_w4a16_silu_and_mul", "b200_w4a16_gemm_silu_mul", "b200_w4a16_gemm_silu_mul_gated", "b200_w4a16_add_rms_norm", "b200_w4a16_allreduce_add_rms_norm",
     "b200_w4a16_allreduce_add_rms_norm_ll", "b200_w4a16_allreduce_ll", "b200_w4a16_workspace_init",
 )
 
@@ -112,6 +112,8 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_allreduce.argtypes = [ctypes.POINTER(vp), i32, i32, vp, vp, sz, sz, i32, vp]
     L.b200_w4a16_gemm_variant.restype = i32
     L.b200_w4a16_gemm_variant.argtypes = [i32, i32, i32, i32]
+    L.b200_w4a16_gemm_unit_tiles.restype = i32
+    L.b200_w4a16_gemm_unit_tiles.argtypes = [i32, i32, i32, i32]
     f32 = ctypes.c_float
     L.b200_w4a16_moe_gather.restype = i32
     L.b200_w4a16_moe_gather.argtypes = [vp, vp, vp, sz, i32, vp]
@@ -121,6 +123,8 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_silu_and_mul.argtypes = [vp, vp, sz, i32, i32, vp]
     L.b200_w4a16_gemm_silu_mul.restype = i32
     L.b200_w4a16_gemm_silu_mul.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, sz, vp]
+    L.b200_w4a16_gemm_silu_mul_gated.restype = i32
+    L.b200_w4a16_gemm_silu_mul_gated.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, sz, vp]
     L.b200_w4a16_add_rms_norm.restype = i32
     L.b200_w4a16_add_rms_norm.argtypes = [vp, vp, vp, vp, vp, f32, sz, i32, vp]
     L.b200_w4a16_allreduce_add_rms_norm.restype = i32
@@ -156,4 +160,5 @@ def gemm_plan(M: int, K: int, N: int, G: int = 128, split_k_hint: int = 0) -> di
     variant = lib().b200_w4a16_gemm_variant(M, K, N, G)
     return {"tok_tile": tok.value, "split_k": split.value, "grid": grid.value,
             "smem_bytes": smem.value,
-            "variant": {0: "tcgen05", 1: "decode", 2: "tcdecode"}.get(variant, str(variant))}
+            "variant": {0: "tcgen05", 1: "decode"}.get(variant, str(variant)),
+            "unit_tiles": lib().b200_w4a16_gemm_unit_tiles(M, K, N, G)}

@@ -19,7 +19,7 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 // a launch uses a prefix of it and hands it back all-0xFF) | from kMaxPartialBytes on: scratch
 // for the on-the-fly interleave of checkpoint-layout weights.  The scratch must never overlap
 // ANY plan's slots: leftovers of a repack would read as arrived partial sums.
-constexpr size_t kMaxPartialBytes = (size_t)b200::kMaxCtas * 2 * 128 * b200::kTileN * sizeof(float);
+constexpr size_t kMaxPartialBytes = (size_t)b200::kMaxCtas * 2 * 2 * 128 * b200::kTileN * sizeof(float);
 
 struct DeviceInfo {
   int status;    // b200_status_t of the probe
@@ -154,8 +154,15 @@ int b200_w4a16_gemm_variant(int M, int K, int N, int G) {
   b200::GemmPlan plan;
   if (b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, 0, sm_count_or_default(), &plan))
     return -B200_ERR_BAD_SHAPE;
-  return plan.kind == b200::kKindDecode ? B200_VARIANT_DECODE
-         : plan.kind == b200::kKindTcDecode ? B200_VARIANT_TCDECODE : B200_VARIANT_TCGEN05;
+  return plan.kind == b200::kKindDecode ? B200_VARIANT_DECODE : B200_VARIANT_TCGEN05;
+}
+
+int b200_w4a16_gemm_unit_tiles(int M, int K, int N, int G) {
+  if (!gemm_shape_ok(M, K, N, G)) return -B200_ERR_BAD_SHAPE;
+  b200::GemmPlan plan;
+  if (b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, 0, sm_count_or_default(), &plan))
+    return -B200_ERR_BAD_SHAPE;
+  return plan.pair;
 }
 
 int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
@@ -183,10 +190,19 @@ int b200_w4a16_gemm_silu_mul(const uint16_t* x, const int32_t* qweight, const ui
                              const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
                              int split_k_hint, void* workspace, size_t workspace_bytes,
                              b200_stream_t stream) {
+  return b200_w4a16_gemm_silu_mul_gated(x, qweight, scales, qzeros, y, M, K, N, G, split_k_hint,
+                                        nullptr, workspace, workspace_bytes, stream);
+}
+
+int b200_w4a16_gemm_silu_mul_gated(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
+                                   const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
+                                   int split_k_hint, const int32_t* gate, void* workspace,
+                                   size_t workspace_bytes, b200_stream_t stream) {
   if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
+  // y is [M, N / 2] written with 16-byte stores when the gate is closed: N / 2 % 8 == 0
   if (M > b200::kDecodeMaxTokens || G % b200::kTileK != 0 || N % 16 != 0) return B200_ERR_BAD_SHAPE;
   return gemm_impl(x, qweight, scales, qzeros, y, M, K, N, G, B200_LAYOUT_B200, split_k_hint,
-                   nullptr, 1, workspace, workspace_bytes, stream);
+                   gate, 1, workspace, workspace_bytes, stream);
 }
 
 int b200_w4a16_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int d, int paired,

@@ -309,10 +309,11 @@ w4a16_decode_kernel(const DecodeParams p) {
       // expert without tokens: y = 0 (the caller scales it by a zero routing weight), CTA b
       // clears channel tiles b, b + P, ...: 16-byte stores, 16 per token row and tile
       const int tid = threadIdx.x - kFirstConsumerWarp * 32;
-      for (int nt = blockIdx.x; nt < p.NT; nt += gridDim.x)
+      const int NO = p.act ? p.N >> 1 : p.N;                  // fused activation: y is [M, N / 2]
+      for (int nt = blockIdx.x; nt * kTileN < NO; nt += gridDim.x)
         for (int v = tid; v < p.M * 16; v += kConsumerThreads) {
           const int m = v >> 4, n0 = nt * kTileN + (v & 15) * 8;
-          if (n0 < p.N) *reinterpret_cast<uint4*>(p.y + (size_t)m * p.N + n0) = make_uint4(0u, 0u, 0u, 0u);
+          if (n0 < NO) *reinterpret_cast<uint4*>(p.y + (size_t)m * NO + n0) = make_uint4(0u, 0u, 0u, 0u);
         }
       return;
     }
@@ -595,32 +596,67 @@ w4a16_decode_kernel(const DecodeParams p) {
     // land (self-flagging words, w4a16_common.cuh), every contributor's load in flight at once,
     // summed in CTA order -> bit-identical run to run; the slots are handed back empty.  Every
     // CTA of the grid is resident (grid <= SM count, one CTA per SM): the wait cannot deadlock.
+    // Every poll of a thread -- its own slot and up to kBatch contributors, for BOTH of its
+    // entries -- is issued before the first one is looked at: one L2 round trip in all.  (The
+    // first version looked at the own slot, then at a batch, entry by entry: four dependent
+    // round trips, 2.6 us between the last tile and the exit of every owner CTA --
+    // profiles/r2j_trace_decode_m16_4096x4096.txt.)
     if (own_nt >= 0) {
       named_bar_sync(4, kConsumerThreads);                    // group 0's hand-over is in place
-      for (int e = tid; e < kEntries; e += kConsumerThreads) {
-        float4 sum;
-        if (own_local) {
-          sum = xchg[e];
-        } else {
-          uint4* sl = p.partials + ((size_t)blockIdx.x * 2 + own_slot) * kEntries + e;
-          sum = part_take(sl, ld_first_poll_u4(sl, p.flags));
+      constexpr int kPer = (kEntries + kConsumerThreads - 1) / kConsumerThreads;   // entries per thread
+      constexpr int kBatch = 8;
+      const int nother = own_last - (int)blockIdx.x;          // contributors after this CTA
+      uint4* const mine = p.partials + ((size_t)blockIdx.x * 2 + own_slot) * kEntries;
+      uint4* const others = p.partials + ((size_t)(blockIdx.x + 1) * 2) * kEntries;   // their slot 0
+      uint4 own[kPer], f[kPer][kBatch];
+#pragma unroll
+      for (int i = 0; i < kPer; ++i) {
+        const int e = tid + i * kConsumerThreads;
+        if (e < kEntries && !own_local) own[i] = ld_first_poll_u4(mine + e, p.flags);
+      }
+#pragma unroll
+      for (int i = 0; i < kPer; ++i)
+#pragma unroll
+        for (int u = 0; u < kBatch; ++u) {
+          const int e = tid + i * kConsumerThreads;
+          if (e < kEntries && u < nother) f[i][u] = ld_first_poll_u4(others + (size_t)u * 2 * kEntries + e, p.flags);
         }
-        constexpr int kBatch = 8;
-        for (int pc = blockIdx.x + 1; pc <= own_last; pc += kBatch) {
-          uint4 f[kBatch];
+      float4 sum[kPer];
 #pragma unroll
-          for (int u = 0; u < kBatch; ++u)
-            if (pc + u <= own_last) f[u] = ld_first_poll_u4(p.partials + ((size_t)(pc + u) * 2) * kEntries + e, p.flags);
+      for (int i = 0; i < kPer; ++i) {
+        const int e = tid + i * kConsumerThreads;
+        if (e < kEntries) sum[i] = own_local ? xchg[e] : part_take(mine + e, own[i]);
+      }
+      for (int base = 0; base < nother; base += kBatch) {
+        if (base > 0) {                                       // more than kBatch contributors: next batch
 #pragma unroll
-          for (int u = 0; u < kBatch; ++u)                    // CTA order: deterministic
-            if (pc + u <= own_last) {
-              const float4 g4 = part_take(p.partials + ((size_t)(pc + u) * 2) * kEntries + e, f[u]);
-              sum.x += g4.x; sum.y += g4.y; sum.z += g4.z; sum.w += g4.w;
+          for (int i = 0; i < kPer; ++i)
+#pragma unroll
+            for (int u = 0; u < kBatch; ++u) {
+              const int e = tid + i * kConsumerThreads;
+              if (e < kEntries && base + u < nother)
+                f[i][u] = ld_first_poll_u4(others + (size_t)(base + u) * 2 * kEntries + e, p.flags);
             }
         }
-        const float v[4] = {sum.x, sum.y, sum.z, sum.w};
-        if (fused) push_packet(own_nt, e, v[0], v[1], v[2], v[3]);
-        else store_entry(own_nt, e, v);
+#pragma unroll
+        for (int i = 0; i < kPer; ++i)
+#pragma unroll
+          for (int u = 0; u < kBatch; ++u) {                  // CTA order: deterministic
+            const int e = tid + i * kConsumerThreads;
+            if (e < kEntries && base + u < nother) {
+              const float4 g4 = part_take(others + (size_t)(base + u) * 2 * kEntries + e, f[i][u]);
+              sum[i].x += g4.x; sum[i].y += g4.y; sum[i].z += g4.z; sum[i].w += g4.w;
+            }
+          }
+      }
+#pragma unroll
+      for (int i = 0; i < kPer; ++i) {
+        const int e = tid + i * kConsumerThreads;
+        if (e < kEntries) {
+          const float v[4] = {sum[i].x, sum[i].y, sum[i].z, sum[i].w};
+          if (fused) push_packet(own_nt, e, v[0], v[1], v[2], v[3]);
+          else store_entry(own_nt, e, v);
+        }
       }
     }
 

@@ -1,34 +1,46 @@
-// w4a16_gemm.cu -- the W4A16 group-quantized GEMM for sm_100a.
+// w4a16_gemm.cu -- the tcgen05 W4A16 group-quantized GEMM for sm_100a (batches above 16 tokens).
 //
 //   y[M,N] (fp16) = x[M,K] (fp16) . dequant(qweight, scales, qzeros)[K,N]     fp32 accumulate
 //
 // Replaces the reference's gemm_forward_4bit_cuda_m16nXk32 + Tensor.sum(0)
 // (csrc/quantization/awq/gemm_kernels.cu:30-272, :389-446) and its dequantize + cuBLAS branch
-// (vllm/model_executor/layers/quantization/awq.py:154-159).  Design (DESIGN.md section 4):
+// (vllm/model_executor/layers/quantization/awq.py:154-159).  Design (DESIGN.md section 4.2):
 //
 //  * swap-AB: the tcgen05 "M" dimension (128 TMEM lanes) is OUTPUT CHANNELS, the tcgen05 "N"
-//    dimension is TOKENS (16..128), so a decode batch of 1..16 tokens still fills the MMA.
-//  * weights arrive as contiguous 8 KiB tiles (128 channels x 128 rows, B200 layout) by 1-D
-//    bulk async copy; activations by 2-D TMA with the 128-byte swizzle tcgen05 expects.
-//  * four dequant warpgroups take tiles round-robin.  A thread reads one 16-byte word group
-//    (bank-conflict free), expands it in registers with the reference's exact lop3 / sub / fma
-//    sequence, and writes the fp16 pairs straight into TENSOR MEMORY with tcgen05.st:
+//    dimension is TOKENS (MTOK = 16..128).
+//  * TWO independent rings in shared memory.  Weights: contiguous 8 KiB tiles (128 channels x
+//    128 rows, B200 layout) + their scale / zero rows by 1-D bulk copy, 8-16 stages deep (HBM
+//    latency), recycled as soon as the dequant warps have READ them.  Activations: [MTOK x 128]
+//    fp16 tiles by 2-D TMA with the 128-byte swizzle tcgen05 expects, 4-8 stages (L2 latency),
+//    recycled when the MMAs that read them have completed.  (One shared ring of 5 x 41 KiB
+//    stages starved the tensor pipe at 128 tokens: 852 cycles per tile where the MMAs need 512,
+//    profiles/r2j_trace_prefill_m2048_5120x15360.txt.)
+//  * PAIR = 2 (large problems): a CTA works on TWO adjacent channel tiles per activation tile --
+//    256 channels x MTOK tokens per K block -- so an activation tile is fetched from L2 once
+//    per two weight tiles: 24 instead of 40 KiB of L2 -> SM traffic per 128 x 128 x 128 MMA
+//    block at MTOK = 128 (the old kernel moved 10 TB/s out of L2 at 1.0 PFLOP/s).
+//  * four dequant warpgroups take weight tiles round-robin.  A thread reads one 16-byte word
+//    group (bank-conflict free), expands it in registers with the reference's exact lop3 / sub /
+//    fma sequence, and writes the fp16 pairs straight into TENSOR MEMORY with tcgen05.st:
 //    thread = TMEM lane = channel, so the registers already are the MMA A-operand -- no
 //    shared-memory round trip for the dequantized tile (the reference's :168 store +
 //    :198-203 ldmatrix).  A ring of 4-6 operand buffers decouples them from the MMA.
-//  * one thread issues tcgen05.mma (A from TMEM, B from shared memory); two fp32 accumulator
-//    buffers in TMEM let a dedicated epilogue warpgroup drain tile i while tile i+1 runs.
-//  * stream-K: the (channel tile, token tile, K block) space is cut into equal contiguous
-//    ranges, one per SM.  A CTA does its two partial output tiles FIRST, so the cross-CTA
-//    reduction (fp32 partials through L2, fixed CTA order, done by whichever CTA arrives
-//    last -- no second kernel, deterministic) overlaps the rest of the weight stream.
-//  * decode mode (DEC, batches of 17..64 tokens, G % 128 == 0): bandwidth bound.  The dequant
-//    warps write the UNSCALED (q - z) (9 instead of 13 operations per packed word), every
-//    128-row tile gets its own fp32 accumulator in a TMEM ring, and the epilogue warpgroup
-//    applies the group scale while it drains them (one FFMA per accumulator element and tile)
-//    into registers -- the tensor pipe costs the dequant warps no issue slot at all.
-//  * programmatic dependent launch: the weight pipeline is filled BEFORE griddepcontrol.wait
+//  * one thread issues tcgen05.mma (A from TMEM, B from shared memory); fp32 accumulators in
+//    TMEM, drained by a dedicated epilogue warpgroup while the next output tile's MMAs run.
+//  * stream-K: the (channel-tile group, token tile, K block) space is cut into equal contiguous
+//    ranges, one per SM.  A CTA does its two partial output tiles FIRST and publishes them as
+//    self-flagging fp32 words; after its main loop the CTA that owns a split tile's first K
+//    block sums the contributors in CTA order with ALL its dequant + epilogue threads, every
+//    poll of a thread in flight at once (no second kernel, deterministic).
+//  * programmatic dependent launch: the weight ring is filled BEFORE griddepcontrol.wait
 //    (weights never depend on the previous kernel), so launch ramp overlaps the previous op.
+//
+// A decode-mode variant of this kernel (unscaled (q - z) operands, group scale applied to
+// per-tile accumulators by the epilogue) was built and measured in round 2 and REMOVED: at
+// <= 64 tokens a tcgen05.mma of K = 16 costs the tensor pipe 41-56 cycles whatever N is, eight
+// of them per 8 KiB tile are level with the HBM tile period, and the per-tile accumulator drain
+// made it slower than this kernel at 24..64 tokens and no faster than the mma.sync decode
+// kernel at <= 16 (profiles/r2j_decode_variants.md).
 #include "w4a16_common.cuh"
 #include "w4a16_internal.h"
 #include "w4a16_streamk.cuh"
@@ -41,15 +53,14 @@ namespace {
 
 // Warp roles.  The issue arbiter of a sub-partition favours the highest warp id
 // (B300_MICROARCH.md, multi-warp arbiter), so the single-thread roles whose latency paces the
-// whole pipeline -- above all the MMA issuer, measured at ~700 cycles per tile when it sat at
-// warp 1 underneath sixteen busy dequant warps (profiles/r2c_trace_tcdec_57344.log) -- take the
-// TOP warp ids, one per sub-partition; the epilogue sits above the dequant warps.
-constexpr int kFirstDequantWarp = 0;
-constexpr int kGroups = 4;                              // dequant warpgroups, tiles round-robin
-// dequant warps 0..15 (warp % 4 == lane quarter)
+// whole pipeline -- above all the MMA issuer -- take the TOP warp ids, one per sub-partition;
+// the epilogue sits above the dequant warps.
+constexpr int kGroups = 4;                              // dequant warpgroups, weight tiles round-robin
+constexpr int kDequantThreads = kGroups * 128;          // warps 0..15 (warp % 4 == TMEM lane quarter)
 constexpr int kFirstEpiWarp = 16;                       // warps 16..19 (warp % 4 == lane quarter)
 constexpr int kEpiThreads = 128;
-constexpr int kAllocWarp = 20;
+constexpr int kFixThreads = kDequantThreads + kEpiThreads;   // everyone who takes part in the fix-up
+constexpr int kAllocWarp = 20;                          // TMEM allocation + second weight producer
 constexpr int kXProducerWarp = 21;
 constexpr int kProducerWarp = 22;
 constexpr int kMmaWarp = 23;
@@ -58,44 +69,45 @@ constexpr int kScaleRowsMax = 4;                        // G = 32 -> four (scale
 constexpr int kTmemACols = 64;                          // one dequantized tile: 128 fp16 per lane
 constexpr int kTmemCols = 512;
 constexpr int kMaxSmem = 227 * 1024;
+constexpr int kCommit = 2;                              // weight tiles per tcgen05.commit
 
-template <int MTOK, bool DEC>
+template <int V>
+struct IntC { static constexpr int value = V; };
+
+template <int MTOK, int PAIR>
 struct Cfg {
-  // dequantized-operand ring in TMEM
-  static constexpr int kABufs = DEC ? (MTOK <= 32 ? 6 : 4) : (MTOK <= 64 ? 6 : 4);
+  // accumulators: PAIR per buffer set; two sets (drain overlaps the next tile's MMAs) unless
+  // 2 x 128 columns per set leave no room (MTOK = 128, PAIR = 2: one set, drained half by half)
+  static constexpr int kAccBufs = (MTOK * PAIR > 128) ? 1 : 2;
+  static constexpr int kAccCols = kAccBufs * PAIR * MTOK;
+  // dequantized-operand ring in TMEM: what the accumulators leave, at most 6, even
+  static constexpr int kABufsFit = (kTmemCols - kAccCols) / kTmemACols;
+  static constexpr int kABufs = kABufsFit >= 6 ? 6 : 4;
   static constexpr int kDCol = kABufs * kTmemACols;    // accumulators start here
-  // prefill: two accumulator buffers, one per output tile in flight.  DEC: a ring of per-tile
-  // accumulators (MTOK columns each), handed to the epilogue kCommit tiles at a time.
-  static constexpr int kDStride = DEC ? MTOK : (MTOK <= 64 ? 64 : 128);
-  static constexpr int kAccSlots = DEC ? ((kTmemCols - kDCol) / MTOK > 8 ? 8 : (kTmemCols - kDCol) / MTOK) : 2;
+  // activation ring
   static constexpr int kXBytes = MTOK * 256;           // two swizzle atoms of [MTOK x 64] fp16
-  static constexpr int kWOff = kXBytes;
-  static constexpr int kSOff = kWOff + kTileWords * 4;
-  static constexpr int kRows = DEC ? 1 : kScaleRowsMax; // (scale, zero) rows per tile
-  static constexpr int kZOff = kSOff + kRows * 256;
-  static constexpr int kStageBytes = ((kZOff + kRows * 64 + 1023) / 1024) * 1024;
+  static constexpr int kXStages = MTOK >= 128 ? 4 : MTOK == 64 ? 6 : 8;
+  // weight ring: [8 KiB tile | 4 x 256 B scale rows | 4 x 64 B zero rows]
+  static constexpr int kSOff = kTileWords * 4;
+  static constexpr int kZOff = kSOff + kScaleRowsMax * 256;
+  static constexpr int kWStageBytes = kZOff + kScaleRowsMax * 64;            // 9472
+  static constexpr int kWStages = MTOK >= 128 ? 8 : MTOK == 64 ? 12 : 16;
   static constexpr int kBarBytes = 1024;
-  // DEC: the scale row of tile it, kept until the epilogue has scaled the tile's accumulator
-  // (the stage itself is recycled as soon as the tile's MMAs are done).  16 slots >= operand
-  // ring + accumulator ring, so a slot is never rewritten before it has been read.
-  static constexpr int kSRing = 16;
-  static constexpr int kSRingBytes = DEC ? kSRing * 256 : 0;
-  static constexpr int kStagesFit = (kMaxSmem - kBarBytes - kSRingBytes - 1024) / kStageBytes;
-  static constexpr int kStages = kStagesFit > 16 ? 16 : kStagesFit;
-  static constexpr int kSmemBytes = kBarBytes + kSRingBytes + kStages * kStageBytes + 1024;  // + align slack
-  // A tcgen05.commit costs the tensor pipe ~110 cycles (scripts/probes/mma_probe.cu), so MMA
-  // completion is signalled once per kCommit tiles on a ring of kDoneBars barriers; the
-  // producer (stage reuse), the dequant groups (operand-buffer reuse) and, in DEC mode, the
-  // epilogue (accumulators complete) wait on that ring.
-  static constexpr int kCommit = 2;                       // a power of two
-  static constexpr int kAccGroups = kAccSlots / kCommit;
-  static constexpr int kRingMax = kStages > kABufs ? kStages : kABufs;
-  static constexpr int kDoneBars = (kRingMax + kCommit - 1) / kCommit + 1;
-  static_assert(kStages > kGroups, "stage ring must be deeper than the dequant group count");
-  static_assert(kABufs <= kStages, "operand-ring wait must imply the stage's previous phase landed");
-  static_assert(kDCol + kAccSlots * kDStride <= kTmemCols, "TMEM budget");
-  static_assert(!DEC || (kAccSlots % kCommit == 0 && kDoneBars >= kAccGroups), "accumulator ring");
-  static_assert(!DEC || kSRing >= kABufs + kAccSlots, "scale ring must outlive the accumulators");
+  static constexpr int kXOff = kBarBytes;                                    // 1024-aligned
+  static constexpr int kWOff = kXOff + kXStages * kXBytes;
+  static constexpr int kSmemBytes = kWOff + kWStages * kWStageBytes + 1024;  // + align slack
+  // MMA completion is signalled once per kCommit weight tiles (a tcgen05.commit costs the tensor
+  // pipe ~110 cycles, scripts/probes/mma_probe.cu) on a ring of kDoneBars barriers; the
+  // activation producer (stage reuse) and the dequant groups (operand-buffer reuse) wait on it.
+  static constexpr int kRingTiles = kXStages * PAIR > kABufs ? kXStages * PAIR : kABufs;
+  static constexpr int kDoneBars = kRingTiles / kCommit + 2;
+  static constexpr int kNumBars = 2 * kWStages + kXStages + kDoneBars + kABufs + kAccBufs + kAccBufs * PAIR;
+  static_assert(kWStages % kGroups == 0, "a weight stage must always be drained by the same dequant group");
+  static_assert(kWStages % 2 == 0 && kABufs % kCommit == 0, "producer / commit parity");
+  static_assert(kWStageBytes % 128 == 0 && kXBytes % 1024 == 0, "ring alignment");
+  static_assert(kDCol + kAccCols <= kTmemCols, "TMEM budget");
+  static_assert(kSmemBytes <= kMaxSmem, "shared memory budget");
+  static_assert(8 * kNumBars + 8 <= kBarBytes, "barrier block");
 };
 
 struct GemmParams {
@@ -103,10 +115,11 @@ struct GemmParams {
   const uint16_t* scales;
   const uint32_t* qz;
   uint16_t* y;
-  uint4* partials;   // [CTA][2 slots][MTOK x 128 / 4] self-flagging fp32 quads (kPartEmpty = unwritten)
+  uint4* partials;   // [CTA][2 slots][PAIR][MTOK x 128 / 4] self-flagging fp32 quads (kPartEmpty = unwritten)
   int M, K, N, G;
   int KB, NT, MT;
-  int T;        // total (output tile, K block) work items
+  int NTP;      // channel-tile groups: ceil(NT / PAIR)
+  int T;        // total (output unit, K block) work items
   int P;        // CTAs
   int R;        // (scale, zero) rows per K block: max(1, 128 / G)
   int Gdiv;     // K blocks per group: max(1, G / 128)
@@ -115,9 +128,10 @@ struct GemmParams {
 };
 
 #ifdef B200_TRACE
-// event types: 0 producer issues tile, 1 dequant sees tile landed, 2 dequant starts (operand
-// buffer free), 3 dequant done, 4 MMA starts tile, 5 MMA issued, 6 epilogue seg (2*idx: dfull
-// seen, 2*idx+1: segment finished incl. fix-up), 7 misc (0 setup done, 1 exit)
+// event types: 0 producer issues weight tile, 1 dequant sees tile landed, 2 dequant starts (operand
+// buffer free), 3 dequant done, 4 MMA starts weight tile, 5 MMA issued, 6 epilogue seg (2*idx: dfull
+// seen, 2*idx+1: segment finished), 7 misc (0 setup done, 1 exit, 2..4 globaltimer: entry /
+// setup / epilogue done, 5..6 clock at entry / epilogue done)
 #define TR(type, i)                                                                          \
   do {                                                                                       \
     if (p.trace && (i) < 64) p.trace[((size_t)blockIdx.x * 8 + (type)) * 64 + (i)] = (uint32_t)clock64(); \
@@ -135,116 +149,146 @@ struct GemmParams {
 #define TRG(i) do { } while (0)
 #endif
 
-template <int MTOK, bool DEC>
+// The output unit this CTA finishes (it holds the unit's first K block but not all of them), if
+// any: only the first walk segment or the tail segment can be partial, at most one of them starts
+// at a unit boundary.  slot = which of the CTA's two partial slots its own piece sits in.
+struct Owned {
+  int o, slot, last;   // o < 0: none; last = highest CTA contributing to the unit
+};
+__device__ __forceinline__ Owned find_owned(const Walk& walk, int KB, int P, int T, int cta) {
+  Owned r{-1, 0, 0};
+  const int nlook = walk.nseg < 2 ? walk.nseg : 2;
+  for (int idx = 0; idx < nlook; ++idx) {
+    int t0, n;
+    walk.seg(idx, t0, n);
+    if (n != KB && t0 % KB == 0 && owner_of(t0, P, T) == cta) {
+      r.o = t0 / KB;
+      r.slot = idx == 0 ? 0 : 1;
+      r.last = owner_of(t0 + KB - 1, P, T);
+    }
+  }
+  return r;
+}
+
+template <int MTOK, int PAIR>
 __global__ void __launch_bounds__(kThreads, 1)
 w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
-  using C = Cfg<MTOK, DEC>;
+  using C = Cfg<MTOK, PAIR>;
   if (threadIdx.x == 0) { TRG(2); TR(7, 5); }
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
 
   // barrier block
-  constexpr int kDBars = DEC ? C::kAccGroups : 4;               // prefill: dfull[2] + dempty[2]
-  const uint32_t bar_full = smem_base;                          // [kStages]   TMA landed
-  const uint32_t bar_done = bar_full + 8 * C::kStages;          // [kDoneBars] MMA done, per group
-  const uint32_t bar_afull = bar_done + 8 * C::kDoneBars;       // [kABufs]    operand dequantized
-  const uint32_t bar_dfull = bar_afull + 8 * C::kABufs;         // prefill [2] accumulator complete
-  const uint32_t bar_dempty = DEC ? bar_dfull : bar_dfull + 16; // accumulator(s) drained
-  constexpr int kNumBars = C::kStages + C::kDoneBars + C::kABufs + kDBars;
-  const uint32_t tmem_slot = smem_base + 8 * kNumBars;
-  static_assert(8 * kNumBars + 8 <= C::kBarBytes, "barrier block");
+  const uint32_t bar_wfull = smem_base;                          // [kWStages]  weight tile landed
+  const uint32_t bar_wempty = bar_wfull + 8 * C::kWStages;       // [kWStages]  weight tile read by its dequant group
+  const uint32_t bar_xfull = bar_wempty + 8 * C::kWStages;       // [kXStages]  activation tile landed
+  const uint32_t bar_done = bar_xfull + 8 * C::kXStages;         // [kDoneBars] MMAs of kCommit weight tiles done
+  const uint32_t bar_afull = bar_done + 8 * C::kDoneBars;        // [kABufs]    operand dequantized
+  const uint32_t bar_dfull = bar_afull + 8 * C::kABufs;          // [kAccBufs]  accumulator set complete
+  const uint32_t bar_dempty = bar_dfull + 8 * C::kAccBufs;       // [kAccBufs * PAIR] accumulator drained
+  const uint32_t tmem_slot = smem_base + 8 * C::kNumBars;
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(
       smem_gen + (tmem_slot - smem_base));
-  uint16_t* sring = reinterpret_cast<uint16_t*>(smem_gen + C::kBarBytes);   // DEC: [kSRing][128] scales
-  const uint32_t stage0 = smem_base + C::kBarBytes + C::kSRingBytes;
-  uint8_t* stage0_gen = smem_gen + C::kBarBytes + C::kSRingBytes;
+  const uint32_t xring = smem_base + C::kXOff;
+  const uint32_t wring = smem_base + C::kWOff;
+  const uint8_t* wring_gen = smem_gen + C::kWOff;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // This CTA's contiguous slice of the work space, and the order it is walked in.
+  // This CTA's contiguous slice of the work space, and the order it is walked in.  A work item
+  // ("unit step") is one K block of one output unit = PAIR channel tiles x one token tile.
   const int t_begin = range_begin(blockIdx.x, p.T, p.P);
   const int t_end = range_begin(blockIdx.x + 1, p.T, p.P);
   const Walk walk(t_begin, t_end, p.KB);
-  const int n_total = t_end - t_begin;
-  const int npre = n_total < C::kStages ? n_total : C::kStages;
+  const int n_units = t_end - t_begin;
+  const int n_w = n_units * PAIR;                               // weight tiles in stream order
+  const int npre = n_w < C::kWStages ? n_w : C::kWStages;
 
-  // Weight stream of this CTA: tiles in walk order with every address advanced incrementally --
-  // consecutive K blocks of a channel tile are contiguous in the B200 layout, so a step is a
-  // few adds, an mbarrier wait and three bulk copies.  It has to be that lean: a producer is ONE
-  // thread running a dependent chain per tile, and at ~740 cycles per tile (index divisions,
-  // 64-bit multiplies; profiles/r2f_trace_tcdec_57344.log) that chain, not HBM and not the
-  // tensor pipe, paced the whole kernel.  Two producer threads on different sub-partitions
-  // (warps kProducerWarp / kAllocWarp) take the tiles alternately.
+  // Weight stream of this CTA: for every unit step of the walk its PAIR weight tiles, every
+  // address advanced incrementally -- consecutive K blocks of a channel tile are contiguous in
+  // the B200 layout, so a step is a few adds, an mbarrier wait and three bulk copies.  It has
+  // to be that lean: a producer is ONE thread running a dependent chain per tile.  Two producer
+  // threads on different sub-partitions (warps kProducerWarp / kAllocWarp) take the tiles
+  // alternately.  A channel tile beyond the matrix (odd NT, PAIR = 2) re-reads the last one:
+  // its MMAs run, the epilogue drops the result.
   struct WStream {
     const GemmParams& p;
     const Walk& walk;
-    int idx, left, nt, kb, gcnt;
-    uint32_t tx, sbytes, zbytes;
-    const uint32_t* wsrc;
-    const uint16_t* sptr;     // scale row of the current K block
-    const uint32_t* zptr;     // zero row of the current K block
+    int idx, left, h, gcnt;
+    uint32_t sb0, zb0, sb1, zb1;                        // scale / zero row bytes of tile h = 0 / 1
+    const uint32_t *w0, *w1, *z0, *z1;                  // weight tile, zero row
+    const uint16_t *s0, *s1;                            // scale row
     __device__ __forceinline__ WStream(const GemmParams& pp, const Walk& w)
-        : p(pp), walk(w), idx(-1), left(0), nt(0), kb(0), gcnt(0), tx(0), sbytes(0), zbytes(0),
-          wsrc(nullptr), sptr(nullptr), zptr(nullptr) {}
+        : p(pp), walk(w), idx(-1), left(0), h(0), gcnt(0), sb0(0), zb0(0), sb1(0), zb1(0),
+          w0(nullptr), w1(nullptr), z0(nullptr), z1(nullptr), s0(nullptr), s1(nullptr) {}
     __device__ __forceinline__ void open() {
+      h = 0;
       if (++idx >= walk.nseg) return;
       int t0, n;
       walk.seg(idx, t0, n);
       const int o = t0 / p.KB;
-      kb = t0 - o * p.KB;
-      nt = o / p.MT;
+      const int kb = t0 - o * p.KB;
+      const int ntp = o / p.MT;
       left = n;
-      const uint32_t nvalid = (uint32_t)min(kTileN, p.N - nt * kTileN);
-      sbytes = nvalid * 2;
-      zbytes = nvalid / 2;
-      tx = (uint32_t)C::kXBytes + kTileWords * 4 + (uint32_t)p.R * (sbytes + zbytes);
-      wsrc = p.qw + ((size_t)nt * p.KB + kb) * kTileWords;
       const int g0 = p.R > 1 ? kb * p.R : kb / p.Gdiv;
       gcnt = p.R > 1 ? 0 : kb - g0 * p.Gdiv;                  // K blocks into the current group
-      sptr = p.scales + nt * kTileN + (size_t)g0 * p.N;
-      zptr = p.qz + nt * 16 + (size_t)g0 * (p.N >> 3);
+      const int nta = ntp * PAIR;
+      const int ntb = (PAIR == 2 && nta + 1 < p.NT) ? nta + 1 : nta;
+      const uint32_t va = (uint32_t)min(kTileN, p.N - nta * kTileN);
+      const uint32_t vb = (uint32_t)min(kTileN, p.N - ntb * kTileN);
+      sb0 = va * 2; zb0 = va / 2; sb1 = vb * 2; zb1 = vb / 2;
+      w0 = p.qw + ((size_t)nta * p.KB + kb) * kTileWords;
+      w1 = p.qw + ((size_t)ntb * p.KB + kb) * kTileWords;
+      s0 = p.scales + nta * kTileN + (size_t)g0 * p.N;
+      s1 = p.scales + ntb * kTileN + (size_t)g0 * p.N;
+      z0 = p.qz + nta * 16 + (size_t)g0 * (p.N >> 3);
+      z1 = p.qz + ntb * 16 + (size_t)g0 * (p.N >> 3);
     }
-    __device__ __forceinline__ void next() {
-      ++kb;
-      wsrc += kTileWords;
+    __device__ __forceinline__ void next() {                  // to the next weight tile of the stream
+      if (PAIR == 2 && h == 0) { h = 1; return; }
+      h = 0;
+      w0 += kTileWords; w1 += kTileWords;
       if (p.R > 1) {
-        sptr += (size_t)p.R * p.N;
-        zptr += (size_t)p.R * (p.N >> 3);
+        const size_t ds = (size_t)p.R * p.N, dz = (size_t)p.R * (p.N >> 3);
+        s0 += ds; s1 += ds; z0 += dz; z1 += dz;
       } else if (++gcnt == p.Gdiv) {
         gcnt = 0;
-        sptr += p.N;
-        zptr += p.N >> 3;
+        s0 += p.N; s1 += p.N; z0 += p.N >> 3; z1 += p.N >> 3;
       }
       if (--left == 0) open();
     }
   };
   const uint64_t pol_w = (p.flags & 1) ? policy_evict_normal() : policy_evict_first();
   auto issue_w = [&](const WStream& c, int stage) {
-    const uint32_t sb = stage0 + stage * C::kStageBytes;
-    const uint32_t bar = bar_full + 8 * stage;
-    mbar_arrive_expect_tx(bar, c.tx);
-    bulk_g2s_hint(sb + C::kWOff, c.wsrc, kTileWords * 4, bar, pol_w);
-    bulk_g2s(sb + C::kSOff, c.sptr, c.sbytes, bar);
-    bulk_g2s(sb + C::kZOff, c.zptr, c.zbytes, bar);
-    if (!DEC) {
-      for (int r = 1; r < p.R; ++r) {                         // G < 128: several rows per K block
-        bulk_g2s(sb + C::kSOff + r * 256, c.sptr + (size_t)r * p.N, c.sbytes, bar);
-        bulk_g2s(sb + C::kZOff + r * 64, c.zptr + (size_t)r * (p.N >> 3), c.zbytes, bar);
-      }
+    const uint32_t sb = wring + stage * C::kWStageBytes;
+    const uint32_t bar = bar_wfull + 8 * stage;
+    const bool hb = PAIR == 2 && c.h == 1;
+    const uint32_t sbytes = hb ? c.sb1 : c.sb0, zbytes = hb ? c.zb1 : c.zb0;
+    const uint32_t* wsrc = hb ? c.w1 : c.w0;
+    const uint16_t* sptr = hb ? c.s1 : c.s0;
+    const uint32_t* zptr = hb ? c.z1 : c.z0;
+    mbar_arrive_expect_tx(bar, kTileWords * 4 + (uint32_t)p.R * (sbytes + zbytes));
+    bulk_g2s_hint(sb, wsrc, kTileWords * 4, bar, pol_w);
+    bulk_g2s(sb + C::kSOff, sptr, sbytes, bar);
+    bulk_g2s(sb + C::kZOff, zptr, zbytes, bar);
+    for (int r = 1; r < p.R; ++r) {                           // G < 128: several rows per K block
+      bulk_g2s(sb + C::kSOff + r * 256, sptr + (size_t)r * p.N, sbytes, bar);
+      bulk_g2s(sb + C::kZOff + r * 64, zptr + (size_t)r * (p.N >> 3), zbytes, bar);
     }
   };
 
   WStream cw(p, walk);                                      // opened by a producer thread only
   if (warp == kProducerWarp) {
-    // Lane-parallel barrier init, then the weight side of the first npre stages goes out
-    // BEFORE the CTA-wide setup barrier and without ever waiting for the previous kernel:
-    // weights never depend on it, so launch ramp and TMEM allocation overlap the first fetch.
-    for (int b = lane; b < kNumBars; b += 32) {
-      uint32_t count = 1u;                                   // full / done / dfull: one arriver
-      if (b >= C::kStages + C::kDoneBars && b < C::kStages + C::kDoneBars + C::kABufs) count = 128u;
-      else if (DEC ? b >= C::kStages + C::kDoneBars + C::kABufs : b >= kNumBars - 2)
-        count = (uint32_t)kEpiThreads;                       // dempty
+    // Lane-parallel barrier init, then the first npre weight tiles go out BEFORE the CTA-wide
+    // setup barrier and without ever waiting for the previous kernel: weights never depend on
+    // it, so launch ramp and TMEM allocation overlap the first fetch.
+    for (int b = lane; b < C::kNumBars; b += 32) {
+      uint32_t count = 1u;                                   // wfull / xfull / done / dfull: one arriver
+      if (b >= C::kWStages && b < 2 * C::kWStages) count = 4u;                    // wempty: one lane per warp
+      const int a0 = 2 * C::kWStages + C::kXStages + C::kDoneBars;
+      if (b >= a0 && b < a0 + C::kABufs) count = 128u;                            // afull
+      if (b >= a0 + C::kABufs + C::kAccBufs) count = (uint32_t)kEpiThreads;       // dempty
       mbar_init(smem_base + 8 * b, count);
     }
     fence_barrier_init();
@@ -266,272 +310,214 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   if (threadIdx.x == 0) { TR(7, 0); TRG(3); }
 
   if (warp == kProducerWarp || warp == kAllocWarp) {
-    // -- steady state: refill stage it % kStages once the MMAs of tile it - kStages are done
-    // (their commit, one per kCommit tiles, arrives on bar_done[((it - kStages) / kCommit) %
-    // kDoneBars]).  Producer r takes the tiles with it % 2 == r; both walk the same cursor.
-    // elect.sync picks the same lane as before the setup barrier, so warp 22's `cw` carries over.
-    static_assert(C::kCommit == 2, "a producer's tiles advance the commit ring by one per step");
+    // -- steady state: refill weight stage w % kWStages once its dequant group has read tile
+    // w - kWStages.  Producer r takes the tiles with w % 2 == r (kWStages is even: always the
+    // same stages); both walk the same cursor.  elect.sync picks the same lane as before the
+    // setup barrier, so warp 22's `cw` carries over.
     __syncwarp();
-    if (elect_one() && npre < n_total) {
+    if (elect_one() && npre < n_w) {
       const int r = warp == kProducerWarp ? 0 : 1;
       if (r == 1) {
         cw.open();
         for (int i = 0; i < npre; ++i) cw.next();
       }
-      int it = npre;
-      if ((it & 1) != r) { cw.next(); ++it; }
-      int stage = it % C::kStages;
-      const int g0 = (it - C::kStages) / C::kCommit;
-      int dslot = g0 % C::kDoneBars;
-      uint32_t dpar = (uint32_t)(g0 / C::kDoneBars) & 1u;
-      for (; it < n_total; it += 2) {
-        mbar_wait(bar_done + 8 * dslot, dpar);
-        TR(0, it);
+      int w = npre;
+      if ((w & 1) != r) { cw.next(); ++w; }
+      int stage = w % C::kWStages;
+      uint32_t par = (uint32_t)(w / C::kWStages - 1) & 1u;     // phase of wempty[stage] to wait for
+      for (; w < n_w; w += 2) {
+        mbar_wait(bar_wempty + 8 * stage, par);
+        TR(0, w);
         issue_w(cw, stage);
         cw.next();
-        if (it + 1 < n_total) cw.next();
+        if (w + 1 < n_w) cw.next();
         stage += 2;
-        if (stage >= C::kStages) stage -= C::kStages;
-        if (++dslot == C::kDoneBars) { dslot = 0; dpar ^= 1u; }
+        if (stage >= C::kWStages) { stage -= C::kWStages; par ^= 1u; }
       }
     }
   } else if (warp == kXProducerWarp) {
-    // Activation stream (elected thread of warp 21): two 64-column TMA boxes per tile, issued
-    // once the previous kernel's output is visible; ring positions advance incrementally.
+    // Activation stream (elected thread of warp 21): two 64-column TMA boxes per unit step,
+    // issued once the previous kernel's output is visible; stage u % kXStages is refilled when
+    // the MMAs of step u - kXStages have completed, i.e. when the commit group of that step's
+    // LAST weight tile has: group ((u - kXStages) * PAIR + PAIR - 1) / kCommit.
     __syncwarp();
     if (elect_one()) {
       tma_prefetch_desc(&tmap_x);
       asm volatile("griddepcontrol.wait;" ::: "memory");      // x is the previous kernel's output
-      int it = 0, dslot = 0;
-      uint32_t dpar = 0;
-      uint32_t sb = stage0, bar = bar_full;
+      int u = 0;
+      uint32_t sb = xring, bar = bar_xfull;
       for (int idx = 0; idx < walk.nseg; ++idx) {
         int t0, n;
         walk.seg(idx, t0, n);
         const int o = t0 / p.KB;
         int k0 = (t0 - o * p.KB) * kTileK;
         const int m0 = (o % p.MT) * MTOK;
-        for (int i = 0; i < n; ++i, ++it, k0 += kTileK) {
-          if (it >= C::kStages) {
-            mbar_wait(bar_done + 8 * dslot, dpar);            // ((it - kStages) / kCommit) % kDoneBars
-            if ((it - C::kStages) & 1) {
-              if (++dslot == C::kDoneBars) { dslot = 0; dpar ^= 1u; }
-            }
+        for (int i = 0; i < n; ++i, ++u, k0 += kTileK) {
+          if (u >= C::kXStages) {
+            const int g = ((u - C::kXStages) * PAIR + PAIR - 1) / kCommit;
+            mbar_wait(bar_done + 8 * (g % C::kDoneBars), (uint32_t)(g / C::kDoneBars) & 1u);
           }
+          mbar_arrive_expect_tx(bar, (uint32_t)C::kXBytes);
           tma_load_2d(sb, &tmap_x, k0, m0, bar);
           tma_load_2d(sb + MTOK * 128, &tmap_x, k0 + 64, m0, bar);
-          sb += C::kStageBytes;
+          sb += C::kXBytes;
           bar += 8;
-          if (bar == bar_full + 8 * C::kStages) { sb = stage0; bar = bar_full; }
+          if (bar == bar_xfull + 8 * C::kXStages) { sb = xring; bar = bar_xfull; }
         }
       }
     }
   } else if (warp == kMmaWarp) {
     __syncwarp();
     if (elect_one()) {
-      // ONE thread issues every tcgen05.mma of the CTA, so its instruction count per tile IS the
-      // tile period once the dequant warps keep up (measured ~700 cycles per tile with
-      // descriptors rebuilt per MMA and two cold mbarrier waits, profiles/r2e_trace_tcdec_57344.log
-      // -- above both the tensor pipe's 8 x 41 and the HBM tile period).  Hence: descriptors are
-      // a base plus compile-time constants, ring positions advance incrementally (no modulo),
-      // and the mbarrier test for the NEXT tile is issued before this tile's MMAs so its ~90
-      // cycle latency hides behind them.
+      // ONE thread issues every tcgen05.mma of the CTA, so its instruction count per tile is a
+      // floor for the tile period: descriptors are a base plus compile-time constants, ring
+      // positions advance incrementally (no modulo), and the operand barrier of the NEXT weight
+      // tile is tested before this tile's MMAs so its latency hides behind them.
       constexpr uint32_t idesc = make_idesc_f16_m128(MTOK);
-      const uint64_t bdesc0 = make_desc_k_sw128(stage0);        // stage 0, K slice 0
-      constexpr uint32_t kStageStep = C::kStageBytes >> 4;      // descriptor address units (16 B)
-      uint32_t stage_off = 0;                                   // stage * kStageStep
-      uint32_t acol = tmem;                                     // operand buffer `buf`
-      int buf = 0, itg = 0;
+      const uint64_t bdesc0 = make_desc_k_sw128(xring);           // activation stage 0, K slice 0
+      constexpr uint32_t kXStep = C::kXBytes >> 4;                // descriptor address units (16 B)
+      uint32_t x_off = 0;                                         // stage * kXStep
+      uint32_t xbar = bar_xfull, xphase = 0;
+      int buf = 0, w = 0;                                         // operand buffer, weight tile index
       uint32_t aphase = 0;
-      int done_slot = 0;                                        // (itg / kCommit) % kDoneBars
-      int acc_slot = 0, acc_group = 0;                          // DEC: itg % kAccSlots, (itg / kCommit) % kAccGroups
-      uint32_t acc_phase = 1;                                   // DEC: parity to wait for on bar_dempty
-      bool a_ready = n_total > 0 && mbar_try_wait(bar_afull, 0);
+      int done_slot = 0;                                          // (w / kCommit) % kDoneBars
+      bool a_ready = n_w > 0 && mbar_try_wait(bar_afull, 0);
       for (int idx = 0; idx < walk.nseg; ++idx) {
         int t0, n;
         walk.seg(idx, t0, n);
-        const int d = idx & 1;
-        uint32_t dcol = tmem + C::kDCol + d * C::kDStride;
-        if (!DEC) {
-          mbar_wait(bar_dempty + 8 * d, ((idx >> 1) & 1) ^ 1);  // drained by the epilogue warps
-          tc_fence_after();
-        }
+        const int d = idx % C::kAccBufs;                          // accumulator set of this output unit
+        const uint32_t dpar = ((uint32_t)(idx / C::kAccBufs) & 1u) ^ 1u;
         for (int i = 0; i < n; ++i) {
-          if (DEC) {
-            // every tile has its own accumulator; a group of kCommit slots is reused once the
-            // epilogue has drained it
-            if ((itg & (C::kCommit - 1)) == 0) {
-              mbar_wait(bar_dempty + 8 * acc_group, acc_phase);
+          mbar_wait(xbar, xphase);                                // activation tile of this step
+          const uint64_t bd = bdesc0 + x_off;
+#pragma unroll
+          for (int h = 0; h < PAIR; ++h) {
+            if (i == 0) {                                         // first touch of accumulator (d, h):
+              mbar_wait(bar_dempty + 8 * (d * PAIR + h), dpar);   // drained by the epilogue warps
               tc_fence_after();
             }
-            dcol = tmem + C::kDCol + acc_slot * C::kDStride;
-          }
-          // One wait per tile: the dequant group arrives on bar_afull only after it has seen
-          // this stage's bar_full complete (weights, scales, zeros AND the activation TMA
-          // share that barrier), so the activations are covered transitively.
-          if (!a_ready) mbar_wait(bar_afull + 8 * buf, aphase);
-          tc_fence_after();
-          TR(4, itg);
-          // ring positions of the next tile, and an early look at its operand barrier
-          int nbuf = buf + 1;
-          uint32_t nphase = aphase;
-          if (nbuf == C::kABufs) { nbuf = 0; nphase ^= 1u; }
-          a_ready = itg + 1 < n_total && mbar_try_wait(bar_afull + 8 * nbuf, nphase);
-          const uint64_t bd = bdesc0 + stage_off;
+            if (!a_ready) mbar_wait(bar_afull + 8 * buf, aphase);
+            tc_fence_after();
+            TR(4, w);
+            const uint32_t acol = tmem + buf * kTmemACols;
+            const uint32_t dcol = tmem + C::kDCol + (d * PAIR + h) * MTOK;
+            // ring positions of the next weight tile, and an early look at its operand barrier
+            int nbuf = buf + 1;
+            uint32_t nphase = aphase;
+            if (nbuf == C::kABufs) { nbuf = 0; nphase ^= 1u; }
+            a_ready = w + 1 < n_w && mbar_try_wait(bar_afull + 8 * nbuf, nphase);
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk)
-            tc_mma_ts(dcol, acol + kk * 8, bd + (uint32_t)((kk >> 2) * (MTOK * 128 / 16) + (kk & 3) * 2), idesc,
-                      DEC ? (uint32_t)(kk != 0) : (uint32_t)((i | kk) != 0));
-          if ((itg & (C::kCommit - 1)) == C::kCommit - 1 || itg == n_total - 1) {
-            tc_commit(bar_done + 8 * done_slot);
-            if (++done_slot == C::kDoneBars) done_slot = 0;
-            if (DEC && ++acc_group == C::kAccGroups) { acc_group = 0; acc_phase ^= 1u; }
+            for (int kk = 0; kk < 8; ++kk)
+              tc_mma_ts(dcol, acol + kk * 8, bd + (uint32_t)((kk >> 2) * (MTOK * 128 / 16) + (kk & 3) * 2), idesc,
+                        (uint32_t)((i | kk) != 0));
+            ++w;
+            if ((w & (kCommit - 1)) == 0 || w == n_w) {
+              tc_commit(bar_done + 8 * done_slot);
+              if (++done_slot == C::kDoneBars) done_slot = 0;
+            }
+            TR(5, w - 1);
+            buf = nbuf;
+            aphase = nphase;
           }
-          TR(5, itg);
-          ++itg;
-          stage_off += kStageStep;
-          if (stage_off == C::kStages * kStageStep) stage_off = 0;
-          buf = nbuf;
-          aphase = nphase;
-          acol = tmem + buf * kTmemACols;
-          if (DEC && ++acc_slot == C::kAccSlots) acc_slot = 0;
+          x_off += kXStep;
+          xbar += 8;
+          if (xbar == bar_xfull + 8 * C::kXStages) { x_off = 0; xbar = bar_xfull; xphase ^= 1u; }
         }
-        if (!DEC) tc_commit(bar_dfull + 8 * d);
+        tc_commit(bar_dfull + 8 * d);
       }
     }
   } else if (warp < kFirstEpiWarp) {
-    // ---- dequant warpgroups: tile it -> group it % 4, stage it % kStages, operand it % kABufs
-    const int wi = warp - kFirstDequantWarp;
-    const int grp = wi >> 2, q = wi & 3;
+    // ---- dequant warpgroups: weight tile w -> group w % 4, stage w % kWStages, operand w % kABufs
+    const int grp = warp >> 2, q = warp & 3;
     const int c = q * 32 + lane;                              // channel inside the tile
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int zsh = 4 * awq_nibble(c & 7);
-    int stage = grp % C::kStages, buf = grp % C::kABufs;
+    int stage = grp % C::kWStages, buf = grp % C::kABufs;
     uint32_t fphase = 0;
-    for (int it = grp; it < n_total; it += kGroups) {
-      const uint8_t* sb = stage0_gen + stage * C::kStageBytes;
-      // Operand buffer it % kABufs was last read by the MMAs of tile it - kABufs.  This wait
-      // comes FIRST on purpose: the stage this tile sits in was last used by tile it - kStages
-      // (< it - kABufs + 1), and a parity wait on its full barrier is only meaningful once
-      // that earlier phase has completed -- bulk copies of different stages can land out of
-      // order, and a group that runs ahead would otherwise see the stale phase as "landed".
-      if (it >= C::kABufs) {
-        const int g = (it - C::kABufs) / C::kCommit;
-        mbar_wait(bar_done + 8 * (g % C::kDoneBars), (g / C::kDoneBars) & 1);
+    for (int w = grp; w < n_w; w += kGroups) {
+      const uint8_t* sb = wring_gen + stage * C::kWStageBytes;
+      // Operand buffer w % kABufs was last read by the MMAs of weight tile w - kABufs.
+      if (w >= C::kABufs) {
+        const int g = (w - C::kABufs) / kCommit;
+        mbar_wait(bar_done + 8 * (g % C::kDoneBars), (uint32_t)(g / C::kDoneBars) & 1u);
       }
-      mbar_wait(bar_full + 8 * stage, fphase);
-      if ((threadIdx.x & 127) == 0) TR(1, it);
+      // kWStages is a multiple of the group count: this group drained the stage's previous
+      // phase itself, so the parity wait cannot pass on a stale phase.
+      mbar_wait(bar_wfull + 8 * stage, fphase);
+      if ((threadIdx.x & 127) == 0) TR(1, w);
       uint4 wv[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j)
-        wv[j] = *reinterpret_cast<const uint4*>(sb + C::kWOff + j * 2048 + c * 16);
+        wv[j] = *reinterpret_cast<const uint4*>(sb + j * 2048 + c * 16);
       const uint16_t* sS = reinterpret_cast<const uint16_t*>(sb + C::kSOff);
       const uint32_t* sZ = reinterpret_cast<const uint32_t*>(sb + C::kZOff);
-      uint32_t zlo = 0, zhi = 0, s2 = 0;
-      make_zs1((sZ[c >> 3] >> zsh) & 0xFu, sS[c], zlo, zhi, s2);
-      if (DEC) sring[(it % C::kSRing) * kTileN + c] = sS[c];  // for the epilogue, see Cfg::kSRing
+      uint32_t zlo[kScaleRowsMax], zhi[kScaleRowsMax], s2[kScaleRowsMax];
+      make_zs1((sZ[c >> 3] >> zsh) & 0xFu, sS[c], zlo[0], zhi[0], s2[0]);
+      if (p.R > 1) {
+#pragma unroll
+        for (int r = 1; r < kScaleRowsMax; ++r)
+          if (r < p.R) make_zs1((sZ[r * 16 + (c >> 3)] >> zsh) & 0xFu, sS[r * 128 + c], zlo[r], zhi[r], s2[r]);
+      }
+      // everything this thread needs from the stage is in registers: hand it back to the producer
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_wempty + 8 * stage);
       tc_fence_after();
-      if ((threadIdx.x & 127) == 0) TR(2, it);
+      if ((threadIdx.x & 127) == 0) TR(2, w);
       const uint32_t abase = tmem + lane_base + buf * kTmemACols;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (!DEC && p.R > 1) {
+        // rows 32 j .. 32 j + 31 of the tile: (scale, zero) row (32 j) / G when G < 128
+        uint32_t zl = zlo[0], zh = zhi[0], sc = s2[0];
+        if (p.R > 1) {
           const int r = (j * 32) / p.G;
-          if (j == 0 || r != ((j - 1) * 32) / p.G)
-            make_zs1((sZ[r * 16 + (c >> 3)] >> zsh) & 0xFu, sS[r * 128 + c], zlo, zhi, s2);
+#pragma unroll
+          for (int rr = 1; rr < kScaleRowsMax; ++rr)
+            if (r == rr) { zl = zlo[rr]; zh = zhi[rr]; sc = s2[rr]; }
         }
         uint32_t v[16];
-        if (DEC) {
-          unpack_sub_zero(wv[j].x, zlo, zhi, v[0], v[1], v[2], v[3]);
-          unpack_sub_zero(wv[j].y, zlo, zhi, v[4], v[5], v[6], v[7]);
-          unpack_sub_zero(wv[j].z, zlo, zhi, v[8], v[9], v[10], v[11]);
-          unpack_sub_zero(wv[j].w, zlo, zhi, v[12], v[13], v[14], v[15]);
-        } else {
-          dequant_word_zs1(wv[j].x, zlo, zhi, s2, v[0], v[1], v[2], v[3]);
-          dequant_word_zs1(wv[j].y, zlo, zhi, s2, v[4], v[5], v[6], v[7]);
-          dequant_word_zs1(wv[j].z, zlo, zhi, s2, v[8], v[9], v[10], v[11]);
-          dequant_word_zs1(wv[j].w, zlo, zhi, s2, v[12], v[13], v[14], v[15]);
-        }
+        dequant_word_zs1(wv[j].x, zl, zh, sc, v[0], v[1], v[2], v[3]);
+        dequant_word_zs1(wv[j].y, zl, zh, sc, v[4], v[5], v[6], v[7]);
+        dequant_word_zs1(wv[j].z, zl, zh, sc, v[8], v[9], v[10], v[11]);
+        dequant_word_zs1(wv[j].w, zl, zh, sc, v[12], v[13], v[14], v[15]);
         tmem_st_x16(abase + j * 16, v);
       }
       tc_wait_st();
       tc_fence_before();
       mbar_arrive(bar_afull + 8 * buf);
-      if ((threadIdx.x & 127) == 0) TR(3, it);
+      if ((threadIdx.x & 127) == 0) TR(3, w);
       stage += kGroups;
-      if (stage >= C::kStages) { stage -= C::kStages; fphase ^= 1u; }
+      if (stage >= C::kWStages) { stage -= C::kWStages; fphase ^= 1u; }
       buf += kGroups;
       if (buf >= C::kABufs) buf -= C::kABufs;
     }
   } else if (warp < kFirstEpiWarp + kEpiThreads / 32) {
-    // ---- epilogue warpgroup: drains accumulators; a whole tile goes to y, a partial one is
-    // published as self-flagging fp32 quads and finished after the main loop by the CTA that
-    // owns the tile's first K block (deferred stream-K fix-up: nothing here waits on another
-    // CTA mid-stream)
+    // ---- epilogue warpgroup: drains accumulators; a whole unit goes to y, a partial one is
+    // published as self-flagging fp32 quads and finished after the main loop (fix-up below):
+    // nothing here waits on another CTA mid-stream
     const int q = warp - kFirstEpiWarp;
     const int c = q * 32 + lane;                              // channel inside the tile
     const int et = threadIdx.x - kFirstEpiWarp * 32;          // 0..127
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     constexpr int kPartVec = MTOK * kTileN / 4;               // quads per partial tile
-    int own_o = -1, own_slot = 0, own_last = 0;               // tile this CTA finishes, if any
     asm volatile("griddepcontrol.wait;" ::: "memory");        // y / workspace may alias earlier work
-    int itg = 0;                                              // DEC: tiles drained so far
     for (int idx = 0; idx < walk.nseg; ++idx) {
       int t0, n;
       walk.seg(idx, t0, n);
       const int o = t0 / p.KB;
-      const int nt = o / p.MT, mt = o - nt * p.MT;
-      const int d = idx & 1;
+      const int ntp = o / p.MT, mt = o - ntp * p.MT;
+      const int d = idx % C::kAccBufs;
       const bool whole = (n == p.KB);
-      const int n_glob = nt * kTileN + c;
       const int m0 = mt * MTOK;
       const int slot = idx == 0 ? 0 : 1;
-      // partial layout: quad v of channel c holds tokens 4 v .. 4 v + 3 -> [v][c], coalesced
-      uint4* part = p.partials + ((size_t)blockIdx.x * 2 + slot) * kPartVec + c;
-      if (DEC) {
-        // per-tile accumulators: scale by the tile's group scale while draining, sum in registers
-        float tot[MTOK];
-#pragma unroll
-        for (int e = 0; e < MTOK; ++e) tot[e] = 0.f;
+      mbar_wait(bar_dfull + 8 * d, (uint32_t)(idx / C::kAccBufs) & 1u);
+      tc_fence_after();
+      if (et == 0) TR(6, 2 * idx);
 #pragma unroll 1
-        for (int i = 0; i < n; ++i, ++itg) {
-          if (itg % C::kCommit == 0) {
-            const int g = itg / C::kCommit;
-            mbar_wait(bar_done + 8 * (g % C::kDoneBars), (g / C::kDoneBars) & 1);
-            tc_fence_after();
-          }
-          const float sc = __half2float(__ushort_as_half(sring[(itg % C::kSRing) * kTileN + c]));
-          const uint32_t dbase = tmem + lane_base + C::kDCol + (itg % C::kAccSlots) * C::kDStride;
-          uint32_t v[MTOK / 16][16];
-#pragma unroll
-          for (int cc = 0; cc < MTOK / 16; ++cc) tmem_ld_x16(dbase + cc * 16, v[cc]);
-          tc_wait_ld();
-#pragma unroll
-          for (int cc = 0; cc < MTOK / 16; ++cc)
-#pragma unroll
-            for (int e = 0; e < 16; ++e) tot[cc * 16 + e] = fmaf(sc, __uint_as_float(v[cc][e]), tot[cc * 16 + e]);
-          if ((itg + 1) % C::kCommit == 0 || itg == n_total - 1) {
-            tc_fence_before();
-            mbar_arrive(bar_dempty + 8 * ((itg / C::kCommit) % C::kAccGroups));
-          }
-        }
-        if (et == 0) TR(6, 2 * idx);
-        if (whole) {
-          if (n_glob < p.N) {
-#pragma unroll
-            for (int e = 0; e < MTOK; ++e)
-              if (m0 + e < p.M) p.y[(size_t)(m0 + e) * p.N + n_glob] = __half_as_ushort(__float2half_rn(tot[e]));
-          }
-        } else {
-#pragma unroll
-          for (int e = 0; e < MTOK; e += 4)
-            st_volatile_u4(part + (e >> 2) * kTileN, part_pack(tot[e], tot[e + 1], tot[e + 2], tot[e + 3]));
-        }
-      } else {
-        const uint32_t dbase = tmem + lane_base + C::kDCol + d * C::kDStride;
-        mbar_wait(bar_dfull + 8 * d, (idx >> 1) & 1);
-        tc_fence_after();
-        if (et == 0) TR(6, 2 * idx);
+      for (int h = 0; h < PAIR; ++h) {
+        const int n_glob = (ntp * PAIR + h) * kTileN + c;
+        // partial layout: quad v of channel c holds tokens 4 v .. 4 v + 3 -> [v][c], coalesced
+        uint4* part = p.partials + (((size_t)blockIdx.x * 2 + slot) * PAIR + h) * kPartVec + c;
+        const uint32_t dbase = tmem + lane_base + C::kDCol + (d * PAIR + h) * MTOK;
 #pragma unroll 1
         for (int cc = 0; cc < MTOK; cc += 16) {
           uint32_t v[16];
@@ -556,74 +542,100 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           }
         }
         tc_fence_before();
-        mbar_arrive(bar_dempty + 8 * d);
-      }
-      if (!whole) {
-        const int o_lo = o * p.KB;
-        if (owner_of(o_lo, p.P, p.T) == (int)blockIdx.x) {    // at most one such tile per CTA
-          own_o = o;
-          own_slot = slot;
-          own_last = owner_of(o_lo + p.KB - 1, p.P, p.T);
-        }
+        mbar_arrive(bar_dempty + 8 * (d * PAIR + h));
       }
       if (et == 0) TR(6, 2 * idx + 1);
     }
+    if (et == 0) { TRG(4); TR(7, 6); }
+  }
 
-    // ---- deferred fix-up: sum the contributors of the owned tile in CTA order (bit-identical
-    // run to run).  The quads are polled where they land (self-flagging words, one L2 hop) and
-    // handed back empty; the others handled this tile FIRST in their walk, so their partials
-    // are normally long there; every CTA of the grid is resident (grid <= SM count), so the
-    // wait cannot deadlock.
-    if (own_o >= 0) {
-      const int nt = own_o / p.MT, mt = own_o - nt * p.MT;
-      const int n_glob = nt * kTileN + c;
+  // ---- deferred stream-K fix-up, by every dequant and epilogue thread of the CTA that owns a
+  // split unit's first K block: sum the contributors' partial tiles in CTA order (bit-identical
+  // run to run) and write y.  The quads are polled where they land (self-flagging words, one L2
+  // hop) and handed back empty; ALL polls of a thread's pass are issued before the first is
+  // looked at (one round trip per pass instead of one per contributor).  The others handled
+  // this unit FIRST in their walk, so their partials are normally long there; every CTA of the
+  // grid is resident (grid <= SM count), so the wait cannot deadlock.
+  if (warp < kFirstEpiWarp + kEpiThreads / 32) {
+    const Owned own = find_owned(walk, p.KB, p.P, p.T, (int)blockIdx.x);
+    if (own.o >= 0) {
+      asm volatile("griddepcontrol.wait;" ::: "memory");      // the dequant warps write y here
+      constexpr int kPartVec = MTOK * kTileN / 4;
+      constexpr int kQuads = PAIR * kPartVec;
+      const int ntp = own.o / p.MT, mt = own.o - ntp * p.MT;
       const int m0 = mt * MTOK;
-      uint4* mine = p.partials + ((size_t)blockIdx.x * 2 + own_slot) * kPartVec + c;
-      // later contributors start inside the tile: their partial sits in slot 0
-      uint4* others = p.partials + ((size_t)(blockIdx.x + 1) * 2) * kPartVec + c;
-      const int nother = own_last - (int)blockIdx.x;
+      const int nother = own.last - (int)blockIdx.x;
+      uint4* const mine = p.partials + ((size_t)blockIdx.x * 2 + own.slot) * kQuads;
+      uint4* const others = p.partials + ((size_t)(blockIdx.x + 1) * 2) * kQuads;     // their slot 0
+      const size_t cstride = (size_t)2 * kQuads;
+      const int ft = threadIdx.x;                               // 0 .. kFixThreads - 1
+      auto pass = [&](auto kq_, auto kb_) {
+        constexpr int KQ = decltype(kq_)::value, KB = decltype(kb_)::value;
 #pragma unroll 1
-      for (int cc = 0; cc < MTOK; cc += 16) {
-        float4 acc[4];
+        for (int q0 = ft; q0 < kQuads; q0 += kFixThreads * KQ) {
+          uint4 f0[KQ], f[KQ][KB];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          uint4* sl = mine + ((cc >> 2) + e) * kTileN;
-          acc[e] = part_take(sl, ld_first_poll_u4(sl, p.flags));
-        }
-#pragma unroll 1
-        for (int j = 0; j < nother; j += 2) {                 // two contributors in flight
-          uint4 f[2][4];
+          for (int i = 0; i < KQ; ++i) {
+            const int qd = q0 + i * kFixThreads;
+            if (qd < kQuads) f0[i] = ld_first_poll_u4(mine + qd, p.flags);
+          }
 #pragma unroll
-          for (int u = 0; u < 2; ++u)
-            if (j + u < nother) {
+          for (int i = 0; i < KQ; ++i)
 #pragma unroll
-              for (int e = 0; e < 4; ++e)
-                f[u][e] = ld_first_poll_u4(others + (size_t)(j + u) * 2 * kPartVec + ((cc >> 2) + e) * kTileN, p.flags);
+            for (int u = 0; u < KB; ++u) {
+              const int qd = q0 + i * kFixThreads;
+              if (qd < kQuads && u < nother) f[i][u] = ld_first_poll_u4(others + u * cstride + qd, p.flags);
+            }
+          float4 acc[KQ];
+#pragma unroll
+          for (int i = 0; i < KQ; ++i) {
+            const int qd = q0 + i * kFixThreads;
+            if (qd < kQuads) acc[i] = part_take(mine + qd, f0[i]);
+          }
+          for (int base = 0; base < nother; base += KB) {
+            if (base > 0) {
+#pragma unroll
+              for (int i = 0; i < KQ; ++i)
+#pragma unroll
+                for (int u = 0; u < KB; ++u) {
+                  const int qd = q0 + i * kFixThreads;
+                  if (qd < kQuads && base + u < nother)
+                    f[i][u] = ld_first_poll_u4(others + (size_t)(base + u) * cstride + qd, p.flags);
+                }
             }
 #pragma unroll
-          for (int u = 0; u < 2; ++u)
-            if (j + u < nother) {
+            for (int i = 0; i < KQ; ++i)
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float4 g4 = part_take(others + (size_t)(j + u) * 2 * kPartVec + ((cc >> 2) + e) * kTileN, f[u][e]);
-                acc[e].x += g4.x; acc[e].y += g4.y; acc[e].z += g4.z; acc[e].w += g4.w;
+              for (int u = 0; u < KB; ++u) {                    // CTA order: deterministic
+                const int qd = q0 + i * kFixThreads;
+                if (qd < kQuads && base + u < nother) {
+                  const float4 g4 = part_take(others + (size_t)(base + u) * cstride + qd, f[i][u]);
+                  acc[i].x += g4.x; acc[i].y += g4.y; acc[i].z += g4.z; acc[i].w += g4.w;
+                }
               }
-            }
-        }
-        if (n_glob < p.N) {
+          }
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float r[4] = {acc[e].x, acc[e].y, acc[e].z, acc[e].w};
+          for (int i = 0; i < KQ; ++i) {
+            const int qd = q0 + i * kFixThreads;
+            if (qd < kQuads) {
+              const int h = qd / kPartVec, r = qd % kPartVec;
+              const int n_glob = (ntp * PAIR + h) * kTileN + (r % kTileN);
+              const int m = m0 + 4 * (r / kTileN);
+              if (n_glob < p.N) {
+                const float rr[4] = {acc[i].x, acc[i].y, acc[i].z, acc[i].w};
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const int m = m0 + cc + 4 * e + u;
-              if (m < p.M) p.y[(size_t)m * p.N + n_glob] = __half_as_ushort(__float2half_rn(r[u]));
+                for (int u = 0; u < 4; ++u)
+                  if (m + u < p.M) p.y[(size_t)(m + u) * p.N + n_glob] = __half_as_ushort(__float2half_rn(rr[u]));
+              }
             }
           }
         }
-      }
+      };
+      // few contributors (prefill: a unit is split between two or three CTAs): more quads per
+      // pass; many (small decode-like problems): more contributors per pass
+      if (nother <= 3) pass(IntC<2>{}, IntC<3>{});
+      else pass(IntC<1>{}, IntC<7>{});
     }
-    if (et == 0) { TRG(4); TR(7, 6); }
   }
 
   tc_fence_before();
@@ -655,7 +667,7 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-template <int MTOK, bool DEC>
+template <int MTOK, int PAIR>
 int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& plan, bool pdl,
                 cudaStream_t stream) {
   // the opt-in is per device: a process may drive several GPUs
@@ -663,23 +675,23 @@ int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& 
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= kMaxDevices || !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(w4a16_gemm_kernel<MTOK, DEC>,
+    cudaError_t e = cudaFuncSetAttribute(w4a16_gemm_kernel<MTOK, PAIR>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         Cfg<MTOK, DEC>::kSmemBytes);
+                                         Cfg<MTOK, PAIR>::kSmemBytes);
     if (e != cudaSuccess) return (int)e;
     if (dev >= 0 && dev < kMaxDevices) attr_set[dev] = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(plan.ctas);
   cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = Cfg<MTOK, DEC>::kSmemBytes;
+  cfg.dynamicSmemBytes = Cfg<MTOK, PAIR>::kSmemBytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
-  return (int)cudaLaunchKernelEx(&cfg, w4a16_gemm_kernel<MTOK, DEC>, prm, tmap);
+  return (int)cudaLaunchKernelEx(&cfg, w4a16_gemm_kernel<MTOK, PAIR>, prm, tmap);
 }
 
 int gemm_flags() {
@@ -696,25 +708,20 @@ int gemm_flags() {
 
 uint32_t* g_trace = nullptr;
 
-template <int MTOK, bool DEC>
+template <int MTOK, int PAIR>
 void fill_plan(GemmPlan* plan) {
-  plan->stages = Cfg<MTOK, DEC>::kStages;
-  plan->smem_bytes = Cfg<MTOK, DEC>::kSmemBytes;
+  plan->stages = Cfg<MTOK, PAIR>::kWStages;
+  plan->smem_bytes = Cfg<MTOK, PAIR>::kSmemBytes;
 }
 
-}  // namespace
-
-void set_trace_buffer(uint32_t* dev) { g_trace = dev; }
-uint32_t* trace_buffer() { return g_trace; }
-
 // Tuning builds (`make tune`, -DB200_TUNING) can pin the variant with
-// B200_W4A16_KERNEL=tcgen05|decode|tcdecode; the product library dispatches by shape only.
-static int forced_kind() {
+// B200_W4A16_KERNEL=tcgen05|decode and the channel-tile grouping with B200_W4A16_PAIR=1|2; the
+// product library dispatches by shape only.
+int forced_kind() {
 #ifdef B200_TUNING
   static const int k = [] {
     const char* e = getenv("B200_W4A16_KERNEL");
     if (!e) return -1;
-    if (e[0] == 't' && e[1] == 'c' && e[2] == 'd') return (int)kKindTcDecode;
     if (e[0] == 't') return (int)kKindTcgen05;
     if (e[0] == 'd') return (int)kKindDecode;
     return -1;
@@ -724,6 +731,22 @@ static int forced_kind() {
   return -1;
 #endif
 }
+int forced_pair() {
+#ifdef B200_TUNING
+  static const int k = [] {
+    const char* e = getenv("B200_W4A16_PAIR");
+    return e ? atoi(e) : 0;
+  }();
+  return k;
+#else
+  return 0;
+#endif
+}
+
+}  // namespace
+
+void set_trace_buffer(uint32_t* dev) { g_trace = dev; }
+uint32_t* trace_buffer() { return g_trace; }
 
 int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, GemmPlan* plan) {
   (void)split_k_hint;
@@ -731,13 +754,11 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
   if (sm_count > kMaxCtas) sm_count = kMaxCtas;
   plan->n_tiles = (N + kTileN - 1) / kTileN;
   plan->k_blocks = K / kTileK;
+  plan->pair = 1;
   const int fk = forced_kind();
   const bool group_ok = G % kTileK == 0;                  // one (scale, zero) row per 128-row tile
   bool decode = group_ok && M <= kDecodeMaxTokens;
-  bool tcdec = group_ok && !decode && M <= kTcDecodeMaxTokens;
-  if (fk == (int)kKindTcgen05) { decode = false; tcdec = false; }
-  if (fk == (int)kKindTcDecode && group_ok && M <= kTcDecodeMaxTokens) { decode = false; tcdec = true; }
-  if (fk == (int)kKindDecode && group_ok && M <= 16) { decode = true; tcdec = false; }
+  if (fk == (int)kKindTcgen05) decode = false;
   if (decode) {
     // Decode variant: stream-K over (channel tile, K block), one persistent CTA per SM.
     plan->kind = kKindDecode;
@@ -755,14 +776,24 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
     fill_decode_plan(M, plan);
     return 0;
   }
-  plan->kind = tcdec ? kKindTcDecode : kKindTcgen05;
+  plan->kind = kKindTcgen05;
   const int tok = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;
   plan->tok_tile = tok;
   plan->m_tiles = (M + tok - 1) / tok;
-  const long long outs = (long long)plan->n_tiles * plan->m_tiles;
-  const long long T = outs * plan->k_blocks;
+  // Channel tiles in groups of two when that still leaves every SM a long walk (>= 8 unit steps):
+  // one activation tile then feeds two weight tiles.  Small problems keep single tiles, where
+  // the finer work items balance better across the SMs.
+  {
+    const long long units2 = (long long)((plan->n_tiles + 1) / 2) * plan->m_tiles * plan->k_blocks;
+    if (plan->n_tiles >= 2 && units2 >= 8LL * sm_count) plan->pair = 2;
+    const int fp = forced_pair();
+    if (fp == 1) plan->pair = 1;
+    if (fp == 2 && plan->n_tiles >= 2) plan->pair = 2;
+  }
+  const int ntp = (plan->n_tiles + plan->pair - 1) / plan->pair;
+  const long long T = (long long)ntp * plan->m_tiles * plan->k_blocks;
   if (T >= (1LL << 31)) return 1;
-  // Persistent stream-K: one CTA per SM, equal contiguous ranges of (output tile, K block).
+  // Persistent stream-K: one CTA per SM, equal contiguous ranges of (output unit, K block).
   long long ctas = T < sm_count ? T : sm_count;
   if (ctas < 1) ctas = 1;
   plan->ctas = (int)ctas;
@@ -770,20 +801,21 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
   plan->max_split = (plan->k_blocks == 0 || (T % ctas == 0 && per % plan->k_blocks == 0))
                         ? 1
                         : (int)((plan->k_blocks + per - 1) / (per > 0 ? per : 1) + 1);
-  plan->ws_partial_bytes = (size_t)ctas * 2 * tok * kTileN * sizeof(float);
-  if (tcdec) {
+  plan->ws_partial_bytes = (size_t)ctas * 2 * plan->pair * tok * kTileN * sizeof(float);
+  if (plan->pair == 2) {
     switch (tok) {
-      case 16: fill_plan<16, true>(plan); break;
-      case 32: fill_plan<32, true>(plan); break;
-      default: fill_plan<64, true>(plan); break;
+      case 16: fill_plan<16, 2>(plan); break;
+      case 32: fill_plan<32, 2>(plan); break;
+      case 64: fill_plan<64, 2>(plan); break;
+      default: fill_plan<128, 2>(plan); break;
     }
     return 0;
   }
   switch (tok) {
-    case 16: fill_plan<16, false>(plan); break;
-    case 32: fill_plan<32, false>(plan); break;
-    case 64: fill_plan<64, false>(plan); break;
-    default: fill_plan<128, false>(plan); break;
+    case 16: fill_plan<16, 1>(plan); break;
+    case 32: fill_plan<32, 1>(plan); break;
+    case 64: fill_plan<64, 1>(plan); break;
+    default: fill_plan<128, 1>(plan); break;
   }
   return 0;
 }
@@ -812,24 +844,26 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   prm.partials = reinterpret_cast<uint4*>(ws_partials);
   prm.M = M; prm.K = K; prm.N = N; prm.G = G;
   prm.KB = plan.k_blocks; prm.NT = plan.n_tiles; prm.MT = plan.m_tiles;
-  prm.T = plan.n_tiles * plan.m_tiles * plan.k_blocks;
+  prm.NTP = (plan.n_tiles + plan.pair - 1) / plan.pair;
+  prm.T = prm.NTP * plan.m_tiles * plan.k_blocks;
   prm.P = plan.ctas;
   prm.R = G >= kTileK ? 1 : kTileK / G;
   prm.Gdiv = G >= kTileK ? G / kTileK : 1;
   prm.flags = gemm_flags();
   prm.trace = g_trace;
-  if (plan.kind == kKindTcDecode) {
+  if (plan.pair == 2) {
     switch (plan.tok_tile) {
-      case 16: return launch_impl<16, true>(prm, tmap, plan, pdl, stream);
-      case 32: return launch_impl<32, true>(prm, tmap, plan, pdl, stream);
-      default: return launch_impl<64, true>(prm, tmap, plan, pdl, stream);
+      case 16: return launch_impl<16, 2>(prm, tmap, plan, pdl, stream);
+      case 32: return launch_impl<32, 2>(prm, tmap, plan, pdl, stream);
+      case 64: return launch_impl<64, 2>(prm, tmap, plan, pdl, stream);
+      default: return launch_impl<128, 2>(prm, tmap, plan, pdl, stream);
     }
   }
   switch (plan.tok_tile) {
-    case 16: return launch_impl<16, false>(prm, tmap, plan, pdl, stream);
-    case 32: return launch_impl<32, false>(prm, tmap, plan, pdl, stream);
-    case 64: return launch_impl<64, false>(prm, tmap, plan, pdl, stream);
-    default: return launch_impl<128, false>(prm, tmap, plan, pdl, stream);
+    case 16: return launch_impl<16, 1>(prm, tmap, plan, pdl, stream);
+    case 32: return launch_impl<32, 1>(prm, tmap, plan, pdl, stream);
+    case 64: return launch_impl<64, 1>(prm, tmap, plan, pdl, stream);
+    default: return launch_impl<128, 1>(prm, tmap, plan, pdl, stream);
   }
 }
 

@@ -15,16 +15,16 @@ constexpr int kTileWords = 2048;   // int32 words per packed tile (8 KiB)
 constexpr int kMaxCtas = 148;      // one CTA per SM on B200
 constexpr int kDecodeCtasPerSm = 1;    // decode kernel residency (w4a16_decode.cu)
 constexpr int kDecodeMaxTokens = 16;   // mma.sync decode kernel (w4a16_decode.cu) up to here
-constexpr int kTcDecodeMaxTokens = 64; // tcgen05 kernel in decode mode (scale in the epilogue) up to here
 constexpr int kMaxDevices = 64;        // per-device launch state (shared-memory opt-in)
 
-enum GemmKind { kKindTcgen05 = 0, kKindDecode = 1, kKindTcDecode = 2 };
+enum GemmKind { kKindTcgen05 = 0, kKindDecode = 1 };
 
 // How a GEMM is cut into CTAs (stream-K over the (channel tile, token tile, K block) space).
 struct GemmPlan {
-  int kind;          // GemmKind: tcgen05 kernel (prefill / decode mode) or the mma.sync decode kernel
+  int kind;          // GemmKind: tcgen05 kernel or the mma.sync decode kernel
   int tok_tile;      // tokens per MMA tile (tcgen05 N): 16 / 32 / 64 / 128
   int n_tiles;       // ceil(N / 128)
+  int pair;          // tcgen05 kernel: channel tiles per work unit (1 or 2, sharing one activation tile)
   int m_tiles;       // ceil(M / tok_tile)
   int k_blocks;      // K / 128
   int ctas;          // grid size

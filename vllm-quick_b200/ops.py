@@ -21,8 +21,9 @@ from . import _lib
 from ._lib import LAYOUT_AWQ, LAYOUT_B200
 
 PACK_FACTOR = 8
-# fp32 partial tiles of one full wave (148 CTAs x 2 slots x 128 x 128 x 4 B): covers every plan
-_BASE_WORKSPACE_BYTES = 148 * 2 * 128 * 128 * 4
+# fp32 partial tiles of one full wave (148 CTAs x 2 slots x 2 channel tiles x 128 x 128 x 4 B):
+# covers every plan
+_BASE_WORKSPACE_BYTES = 148 * 2 * 2 * 128 * 128 * 4
 
 # Split-K scratch (include/b200_w4a16.h: b200_w4a16_workspace_init).  Eager launches use one
 # workspace per (device, stream) -- GEMMs on different streams may overlap.  Launches recorded
@@ -348,9 +349,11 @@ def quick_gemm_silu_mul(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_fa
     out = torch.empty((M, N // 2), dtype=torch.float16, device=dev)
     with torch.cuda.device(dev):
         ws = _workspace(dev, L.b200_w4a16_workspace_bytes(M, K, N, LAYOUT_B200))
-        st = L.b200_w4a16_gemm_silu_mul(in_feats.data_ptr(), kernel.data_ptr(),
-                                        scaling_factors.data_ptr(), zeros.data_ptr(), out.data_ptr(),
-                                        M, K, N, G, 0, ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+        flag = getattr(_gate, "flag", None)                   # routed-expert gate, see expert_gate()
+        st = L.b200_w4a16_gemm_silu_mul_gated(in_feats.data_ptr(), kernel.data_ptr(),
+                                              scaling_factors.data_ptr(), zeros.data_ptr(), out.data_ptr(),
+                                              M, K, N, G, 0, flag.data_ptr() if flag is not None else None,
+                                              ws.data_ptr(), ws.numel(), _stream_ptr(dev))
     _lib.check(st, "w4a16 gemm + silu_and_mul")
     return out
 
