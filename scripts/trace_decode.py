@@ -27,7 +27,10 @@ def main():
     ap.add_argument("--n", type=int, default=4096)
     ap.add_argument("--launches", type=int, default=6)
     ap.add_argument("--kernel", default=None, choices=["decode", "tcgen05"])
+    ap.add_argument("--flags", default=None, help="B200_W4A16_FLAGS for the trace build")
     args = ap.parse_args()
+    if args.flags:
+        os.environ["B200_W4A16_FLAGS"] = args.flags
     if args.kernel:
         os.environ["B200_W4A16_KERNEL"] = args.kernel      # honoured by tuning / trace builds only
     M, K, N, G = args.m, args.k, args.n, 128
@@ -84,8 +87,9 @@ def main():
     print(f"== launch {nl - 1}: CTAs by exit time (ns after the median dependency release)")
     for cta in list(order[:10]) + list(order[-3:]):
         r = last[cta]
+        fix = f" fix_begin {r[13] - rel0:6d} fix_summed {r[14] - rel0:6d}" if r[13] else ""
         print(f"   cta {cta:3d} tiles {r[9]:3d} segs {r[10]} entry {r[0] - rel0:6d} dep {r[3] - rel0:6d} tile0 {r[4] - rel0:6d} "
-              f"seg0_done {r[5] - rel0:6d} seg0_out {r[6] - rel0:6d} lastseg_done {r[8] - rel0:6d} exit {r[7] - rel0:6d}")
+              f"seg0_done {r[5] - rel0:6d} seg0_out {r[6] - rel0:6d} lastseg_done {r[8] - rel0:6d}{fix} exit {r[7] - rel0:6d}")
     # per-tile stamps of group 0 / warp 0 in the last launch, three CTAs
     for cta in (0, grid // 2, grid - 1):
         rel = ta[nl - 1, cta, 3]  # consumer past griddepcontrol.wait

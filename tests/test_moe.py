@@ -45,7 +45,7 @@ def _fill(moe, oracle, seed, device="cpu"):
     return dense
 
 
-def _reference_block(x, gate_w, dense, experts, top_k, round_half):
+def _reference_block(x, gate_w, dense, experts, top_k, round_half, with_mag=False):
     """The reference's dense loop (mixtral_quant.py:133-157) on dequantized weights."""
     r = (lambda t: t.half().float()) if round_half else (lambda t: t)
     logits = r(x @ gate_w.float().t())
@@ -53,12 +53,16 @@ def _reference_block(x, gate_w, dense, experts, top_k, round_half):
     w, sel = torch.topk(w, top_k, dim=-1)
     w = w / w.sum(dim=-1, keepdim=True)
     out = torch.zeros(x.shape[0], dense[(experts[0], "w2")].shape[1])
+    mag = torch.zeros_like(out)
     for e in experts:
         ew = (w * (sel == e)).sum(dim=-1, keepdim=True)
         h1 = r(F.silu(r(x @ dense[(e, "w1")])))
         h3 = r(x @ dense[(e, "w3")])
         y = r(r(h1 * h3) @ dense[(e, "w2")])
         out = r(out + r(y * ew))
+        mag += (y * ew).abs()
+    if with_mag:       # sum of the experts' absolute contributions: the scale rounding errors live on
+        return out, sel, mag
     return out, sel
 
 
@@ -247,3 +251,36 @@ def test_moe_block_routed_matches_dense_and_reference(pkg, oracle, cuda_lib, tok
     err = (got.float().cpu() - want).abs()
     assert bool((err <= 2e-2 * want.abs().clamp(min=1.0)).all())
     assert torch.equal(got, moe(x.cuda()).reshape(tokens, 256))   # deterministic
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tokens,routed", [(3, False), (16, False), (64, False), (40, True)])
+def test_moe_block_at_mixtral_shapes(pkg, oracle, cuda_lib, tokens, routed):
+    """BASELINE config 5 shapes (hidden 4096, ffn 14336; two local experts keep the host
+    reference affordable): merged w1/w3 GEMM with the activation in its epilogue (<= 16 tokens)
+    or GEMM + paired activation kernel (above), routing-weight accumulate kernel, gated experts;
+    dense loop and routed path against the CPU restatement of the reference's loop."""
+    cfg = _cfg(experts=2, top_k=2, hidden=4096, ffn=14336)
+    torch.set_default_dtype(torch.float16)
+    try:
+        method = pkg.QuickConfig(4, G, True).get_linear_method()
+        with torch.device("cuda"):
+            moe = pkg.MixtralMoE(cfg, method)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    if routed:
+        moe.routed_min_tokens = tokens
+    dense = _fill(moe, oracle, seed=13)
+    g = torch.Generator().manual_seed(tokens)
+    x = (torch.randn(1, tokens, 4096, generator=g) * 0.25).half()
+    want, _, mag = _reference_block(x.reshape(tokens, 4096).float(), moe.gate.weight.data.float().cpu(),
+                                    dense, [0, 1], 2, True, with_mag=True)
+    got = moe(x.cuda()).reshape(tokens, 4096)
+    torch.cuda.synchronize()
+    assert moe.experts[0].w1.qweight.numel() == 0          # merged into one gate/up weight, originals released
+    assert moe.experts[0]._w13["scales"].shape == (4096 // G, 2 * 14336)
+    # K = 14336 makes single expert outputs reach +-45 (fp16 spacing 3e-2) while their weighted
+    # sum can cancel: the bar of the GEMM tests, relative to the experts' absolute contributions
+    err = (got.float().cpu() - want).abs()
+    assert bool((err <= 1e-2 * mag.clamp(min=1.0)).all()), float((err / mag.clamp(min=1.0)).max())
+    assert torch.equal(got, moe(x.cuda()).reshape(tokens, 4096))   # deterministic

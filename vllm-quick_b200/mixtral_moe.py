@@ -1,26 +1,32 @@
-"""Quantized Mixtral expert path: ``MixtralMLP`` and ``MixtralMoE`` with the reference's names,
-constructor arguments, parameter names and result
-(vllm/model_executor/models/mixtral_quant.py:57-160), over the W4A16 linear method.
+"""Quantized Mixtral expert path over the W4A16 linear method -- the caller of the hot path in
+BASELINE config 5 (reference: vllm/model_executor/models/mixtral_quant.py:57-160).
 
-What is the same: experts are split over the tensor-parallel ranks with ``np.array_split``
-(:113-118), every local expert is three ``ReplicatedLinear`` (w1, w2, w3), the router is an
-unquantized ``gate`` matrix, routing is softmax -> top-k -> renormalise (:138-142), an expert's
-output is scaled by the routing weight of the tokens that chose it and zero for the others
-(:147-151), one all-reduce per block (:159).
+Kept from the reference, because checkpoints and model code depend on it: the class names and
+constructor arguments, the parameter names (``experts.<i>.w1|w2|w3.{qweight,qzeros,scales}``,
+``gate.weight``), which experts a tensor-parallel rank owns (contiguous blocks, the remainder
+to the first ranks -- what ``np.array_split`` gives, :113-118), the routing arithmetic
+(softmax in fp32 -> top-k -> renormalise, :136-142) and the result: every local expert's output
+scaled by the routing weight of the tokens that chose it, summed, all-reduced (:143-159).
 
-What is B200-native: the reference runs every local expert on every token whether or not a
-token chose it.  At decode batch sizes the three GEMMs of an expert are pure weight streaming,
-so an expert nobody chose costs as much as one everybody chose.  Here the number of tokens
-routed to each expert is computed on the device and handed to the GEMM launches
-(``ops.expert_gate`` -> ``b200_w4a16_gemm_gated``): a launch whose count is zero streams no
-weights and writes zeros.  No host synchronisation, so the block stays CUDA-graph capturable.
-The result is identical: such an expert's output is multiplied by a zero routing weight.
+What runs instead of the reference's three GEMMs + four eager tensor ops per expert:
+
+* w1 and w3 read the same activations (:87-93): after loading they are ONE merged, channel-paired
+  ``[hidden, 2 * ffn]`` weight; ``silu(w1 x) * w3 x`` comes out of that GEMM's epilogue at decode
+  batches (``b200_w4a16_gemm_silu_mul_gated``), GEMM + one activation kernel above them.
+* the routing-weight multiply and the accumulation over experts (``mul_`` / ``add_``, :152-157)
+  are one kernel (``b200_w4a16_moe_scatter_add``: ``acc[t] = half(acc[t] + half(y[t] * w[t]))``,
+  the same two roundings).
+* the reference streams every local expert's weights for every batch.  At decode sizes that is
+  the whole cost, so the number of tokens routed to each expert is computed on the device and
+  handed to the GEMM launches (``ops.expert_gate``): an expert nobody chose streams nothing
+  and contributes zeros.  No host synchronisation: the block stays CUDA-graph capturable.
+* prefill batches outside graph capture gather each expert's tokens, run the expert on M_e rows
+  instead of T, and scatter-add the weighted result (one host read of the counts).
 """
 from __future__ import annotations
 
-from typing import Optional
+from typing import Any, Dict, List, Optional
 
-import numpy as np
 import torch
 import torch.nn.functional as F
 from torch import nn
@@ -34,8 +40,17 @@ from .parallel_utils.parallel_state import (get_tensor_model_parallel_rank,
                                             get_tensor_model_parallel_world_size)
 
 
+def local_expert_ids(num_experts: int, tp_size: int, rank: int) -> List[int]:
+    """Experts owned by ``rank``: contiguous blocks, the first ``num_experts % tp_size`` ranks
+    one longer (identical to ``np.array_split(range(num_experts), tp_size)[rank]``)."""
+    base, extra = divmod(num_experts, tp_size)
+    first = rank * base + min(rank, extra)
+    return list(range(first, first + base + (1 if rank < extra else 0)))
+
+
 class MixtralMLP(nn.Module):
-    """One expert: ``w2(silu(w1 x) * w3 x)`` (mixtral_quant.py:57-95)."""
+    """One expert: ``w2(silu(w1 x) * w3 x)`` (mixtral_quant.py:57-95).  w1 / w2 / w3 are the
+    checkpoint's parameters; on CUDA the first forward merges w1 and w3 (and frees them)."""
 
     def __init__(self, num_experts: int, hidden_size: int, intermediate_size: int,
                  linear_method: Optional[LinearMethodBase] = None) -> None:
@@ -43,21 +58,43 @@ class MixtralMLP(nn.Module):
         self.num_experts = num_experts
         self.ffn_dim = intermediate_size
         self.hidden_dim = hidden_size
-        self.w1 = ReplicatedLinear(self.hidden_dim, self.ffn_dim, bias=False,
-                                   linear_method=linear_method)
-        self.w2 = ReplicatedLinear(self.ffn_dim, self.hidden_dim, bias=False,
-                                   linear_method=linear_method)
-        self.w3 = ReplicatedLinear(self.hidden_dim, self.ffn_dim, bias=False,
-                                   linear_method=linear_method)
-        self.act_fn = nn.SiLU()
+        self.w1 = ReplicatedLinear(hidden_size, intermediate_size, bias=False, linear_method=linear_method)
+        self.w2 = ReplicatedLinear(intermediate_size, hidden_size, bias=False, linear_method=linear_method)
+        self.w3 = ReplicatedLinear(hidden_size, intermediate_size, bias=False, linear_method=linear_method)
+        self.linear_method = linear_method
+        self._w13: Optional[Dict[str, Any]] = None      # merged [w1 | w3], built after loading
+
+    def process_weights_after_loading(self) -> None:
+        """Build the merged gate/up weight from the loaded w1 and w3 (checkpoint layout, columns
+        concatenated), hand it to the linear method for pairing + interleave, release the two
+        originals.  Idempotent; called by the first CUDA forward if the loader did not."""
+        if self._w13 is not None:
+            return
+        a, b = self.w1.linear_weights, self.w3.linear_weights
+        if a.get("qweight_layout", "awq") != "awq" or b.get("qweight_layout", "awq") != "awq":
+            raise RuntimeError("w1 / w3 were already interleaved separately: merge them right after loading")
+        merged = {k: torch.cat([a[k].data, b[k].data], dim=1).contiguous() for k in ("qweight", "qzeros", "scales")}
+        self._w13 = {k: Parameter(v, requires_grad=False) for k, v in merged.items()}
+        self._w13["qweight_layout"] = "awq"
+        self.linear_method.pair_gate_up(self._w13)
+        self.linear_method._interleave_once(self._w13)
+        for w in (a, b):                                    # the merged copy is the live one
+            for k in ("qweight", "qzeros", "scales"):
+                w[k].data = torch.empty(0, dtype=w[k].dtype, device=w[k].device)
+        self.linear_method._interleave_once(self.w2.linear_weights)
 
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
-        w1_out, _ = self.w1(hidden_states)
-        w1_out = self.act_fn(w1_out)
-        w3_out, _ = self.w3(hidden_states)
-        current_hidden_states = w1_out * w3_out
-        current_hidden_states, _ = self.w2(current_hidden_states)
-        return current_hidden_states
+        fused = hidden_states.is_cuda and hasattr(self.linear_method, "apply_weights_silu_and_mul")
+        if fused:
+            self.process_weights_after_loading()
+            act = self.linear_method.apply_weights_silu_and_mul(self._w13, hidden_states)
+        else:
+            # host-side tests drive this block with a CPU stand-in for the linear method
+            gate, _ = self.w1(hidden_states)
+            up, _ = self.w3(hidden_states)
+            act = F.silu(gate) * up
+        out, _ = self.w2(act)
+        return out
 
 
 class _RouterGate(nn.Module):
@@ -84,6 +121,10 @@ class MixtralMoE(nn.Module):
     (transformers' MixtralConfig has them).  ``skip_idle_experts=False`` gives the reference's
     dense behaviour (every local expert streams its weights for every batch)."""
 
+    # Batches of at least this many tokens, outside CUDA-graph capture, take the routed path
+    # (where it overtakes the dense loop on B200: profiles/r1e_moe_prefill_bench.jsonl).
+    routed_min_tokens = 512
+
     def __init__(self, config, linear_method: Optional[LinearMethodBase] = None,
                  skip_idle_experts: bool = True):
         super().__init__()
@@ -97,19 +138,18 @@ class MixtralMoE(nn.Module):
             raise ValueError(
                 f"Tensor parallel size {self.tp_size} is greater than "
                 f"the number of experts {self.num_total_experts}.")
-        # Split experts equally between ranks
-        self.expert_indicies = np.array_split(range(
-            self.num_total_experts), self.tp_size)[self.rank].tolist()
+        # attribute name (spelling included) as in the reference: model code reads it
+        self.expert_indicies = local_expert_ids(self.num_total_experts, self.tp_size, self.rank)
         if not self.expert_indicies:
-            raise ValueError(
-                f"Rank {self.rank} has no experts assigned to it.")
-        self.experts = nn.ModuleList([
-            MixtralMLP(self.num_total_experts, config.hidden_size, config.intermediate_size,
-                       linear_method=linear_method)
-            if idx in self.expert_indicies else None
-            for idx in range(self.num_total_experts)
-        ])
+            raise ValueError(f"Rank {self.rank} has no experts assigned to it.")
+        # a slot per global expert id so that parameter names match the checkpoint's
+        slots: List[Optional[nn.Module]] = [None] * self.num_total_experts
+        for e in self.expert_indicies:
+            slots[e] = MixtralMLP(self.num_total_experts, config.hidden_size,
+                                  config.intermediate_size, linear_method=linear_method)
+        self.experts = nn.ModuleList(slots)
         self.gate = _RouterGate(config.hidden_size, self.num_total_experts)
+        self._token_ids: Dict[Any, torch.Tensor] = {}       # arange(T) int32 per (device, T)
 
     def route(self, hidden_states: torch.Tensor):
         """softmax -> top-k -> renormalise, as the reference (:136-142).  Returns the routing
@@ -125,15 +165,18 @@ class MixtralMoE(nn.Module):
                             torch.ones_like(selected_experts.reshape(-1), dtype=torch.int32))
         return routing_weights, selected_experts, counts
 
-    # Large batches outside CUDA-graph capture (prefill): the tokens of each local expert are
-    # gathered, the expert runs on M_e rows instead of T, the weighted result is scattered back
-    # (SURVEY 8f-4).  Needs the per-expert counts on the host (ONE sync per block), which a
-    # captured decode step cannot have -- that one keeps the dense loop with device-side gates
-    # below.  Threshold: where the routed path overtakes the dense loop on B200
-    # (profiles/r1e_moe_prefill_bench.jsonl).
-    routed_min_tokens = 512
+    def _all_tokens(self, device: torch.device, tokens: int) -> torch.Tensor:
+        key = (device, tokens)
+        ids = self._token_ids.get(key)
+        if ids is None:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("run the MoE block once eagerly at this batch size before capturing it")
+            ids = torch.arange(tokens, dtype=torch.int32, device=device)
+            self._token_ids[key] = ids
+        return ids
 
     def _forward_routed(self, hidden_states, routing_weights, selected_experts, counts):
+        """Gather each local expert's tokens, run it on M_e rows, scatter-add the weighted rows."""
         final = torch.zeros_like(hidden_states)
         order = torch.argsort(selected_experts.reshape(-1), stable=True)   # by expert, token order kept
         tokens = (order // self.top_k).to(torch.int32)
@@ -142,40 +185,40 @@ class MixtralMoE(nn.Module):
         start = 0
         for expert_idx in range(self.num_total_experts):
             n = host_counts[expert_idx]
-            if n and expert_idx in self.expert_indicies:
+            if n and self.experts[expert_idx] is not None:
                 idx = tokens[start:start + n]
                 out = self.experts[expert_idx](ops.moe_gather(hidden_states, idx))
                 ops.moe_scatter_add(final, out, idx, weights[start:start + n])
             start += n
         return final
 
+    def _forward_dense(self, hidden_states, routing_weights, selected_experts, counts):
+        """Every local expert on every token (the reference's structure); experts without tokens
+        are skipped on the device, the weighted accumulation is one kernel per expert."""
+        on_gpu = hidden_states.is_cuda
+        final = None
+        for expert_idx in self.expert_indicies:
+            per_token = (routing_weights * (selected_experts == expert_idx)).sum(dim=-1)   # fp32 [T]
+            gate = counts[expert_idx:expert_idx + 1] if (self.skip_idle_experts and on_gpu) else None
+            with ops.expert_gate(gate):
+                out = self.experts[expert_idx](hidden_states)
+            if on_gpu:
+                if final is None:
+                    final = torch.zeros_like(out)
+                ops.moe_scatter_add(final, out, self._all_tokens(out.device, out.shape[0]),
+                                    per_token.contiguous())
+            else:                                   # host-side tests: the reference's two tensor ops
+                out = out.mul_(per_token.unsqueeze(-1))
+                final = out if final is None else final.add_(out)
+        return final
+
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
         batch_size, sequence_length, hidden_dim = hidden_states.shape
         hidden_states = hidden_states.view(-1, hidden_dim)
         routing_weights, selected_experts, counts = self.route(hidden_states)
-
-        if (self.skip_idle_experts and hidden_states.is_cuda
-                and hidden_states.shape[0] >= self.routed_min_tokens
-                and not torch.cuda.is_current_stream_capturing()):
-            final_hidden_states = self._forward_routed(hidden_states.contiguous(), routing_weights,
-                                                       selected_experts, counts)
-            return tensor_model_parallel_all_reduce(final_hidden_states).view(
-                batch_size, sequence_length, hidden_dim)
-
-        final_hidden_states = None
-        for expert_idx in self.expert_indicies:
-            expert_layer = self.experts[expert_idx]
-            expert_mask = (selected_experts == expert_idx)
-            expert_weights = (routing_weights * expert_mask).sum(dim=-1, keepdim=True)
-            gate = counts[expert_idx:expert_idx + 1] if (
-                self.skip_idle_experts and hidden_states.is_cuda) else None
-            with ops.expert_gate(gate):
-                current_hidden_states = expert_layer(hidden_states)
-            current_hidden_states = current_hidden_states.mul_(expert_weights)
-            if final_hidden_states is None:
-                final_hidden_states = current_hidden_states
-            else:
-                final_hidden_states.add_(current_hidden_states)
-
-        return tensor_model_parallel_all_reduce(final_hidden_states).view(
-            batch_size, sequence_length, hidden_dim)
+        routed = (self.skip_idle_experts and hidden_states.is_cuda
+                  and hidden_states.shape[0] >= self.routed_min_tokens
+                  and not torch.cuda.is_current_stream_capturing())
+        body = self._forward_routed if routed else self._forward_dense
+        final = body(hidden_states.contiguous(), routing_weights, selected_experts, counts)
+        return tensor_model_parallel_all_reduce(final).view(batch_size, sequence_length, hidden_dim)
