@@ -175,6 +175,19 @@ int b200_w4a16_allreduce(void *const *regions, int rank, int world, const uint16
                          uint16_t *out, size_t n_halfs, size_t max_message_bytes, int barrier,
                          b200_stream_t stream);
 
+/* The same all-reduce as reduce-scatter + all-gather over the same regions, for messages above
+ * the one-shot sizes (every GPU moves 2 (world - 1) / world x the message over NVLink instead of
+ * (world - 1) x): rank r sums chunk range r over all ranks and pushes the result into every
+ * rank's slot, a second NVLink barrier, then a local copy.  Same result bits as
+ * b200_w4a16_allreduce (rank-order fp32 sums), same regions, epochs and mixing rules, CUDA-graph
+ * capturable.  mode: 1 = collective call; 2 / 3 = reduce-scatter / final copy alone, without
+ * staging and cross-GPU waits (single-GPU emulation in the tests only).  world >= 2.
+ * Replaces: the reference's two-stage kernel (csrc/custom_all_reduce.cuh:239-290, dispatch
+ * :520-531) behind tensor_model_parallel_all_reduce (communication_op.py:17-41). */
+int b200_w4a16_allreduce_twoshot(void *const *regions, int rank, int world, const uint16_t *in,
+                                 uint16_t *out, size_t n_halfs, size_t max_message_bytes,
+                                 int mode, b200_stream_t stream);
+
 /* Row-parallel GEMM fused with its all-reduce, decode batches (M <= 16, G % 128 == 0):
  *   y[M,N] = sum over ranks of  x_rank[M,K_rank] . dequant(qweight_rank, ...)      (fp16 out)
  * ONE kernel per rank: a channel tile that finishes its K reduction is rounded to fp16 and

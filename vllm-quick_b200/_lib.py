@@ -40,7 +40,7 @@ EXPORTS = (
     "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan", "b200_w4a16_gemm_variant", "b200_w4a16_gemm_unit_tiles",
     "b200_w4a16_ar_region_bytes", "b200_w4a16_ar_alloc", "b200_w4a16_ar_free",
     "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
-    "b200_w4a16_allreduce", "b200_w4a16_gemm_allreduce", "b200_w4a16_gemm_gated",
+    "b200_w4a16_allreduce", "b200_w4a16_allreduce_twoshot", "b200_w4a16_gemm_allreduce", "b200_w4a16_gemm_gated",
     "b200_w4a16_moe_gather", "b200_w4a16_moe_scatter_add", "b200_w4a16_silu_and_mul", "b200_w4a16_gemm_silu_mul", "b200_w4a16_gemm_silu_mul_gated", "b200_w4a16_add_rms_norm", "b200_w4a16_allreduce_add_rms_norm",
     "b200_w4a16_allreduce_add_rms_norm_ll", "b200_w4a16_allreduce_ll", "b200_w4a16_workspace_init",
 )
@@ -110,6 +110,8 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_ar_unimport.argtypes = [vp]
     L.b200_w4a16_allreduce.restype = i32
     L.b200_w4a16_allreduce.argtypes = [ctypes.POINTER(vp), i32, i32, vp, vp, sz, sz, i32, vp]
+    L.b200_w4a16_allreduce_twoshot.restype = i32
+    L.b200_w4a16_allreduce_twoshot.argtypes = [ctypes.POINTER(vp), i32, i32, vp, vp, sz, sz, i32, vp]
     L.b200_w4a16_gemm_variant.restype = i32
     L.b200_w4a16_gemm_variant.argtypes = [i32, i32, i32, i32]
     L.b200_w4a16_gemm_unit_tiles.restype = i32

@@ -196,6 +196,108 @@ allreduce_ll_kernel(const ArParams p) {
   }
 }
 
+// Two-shot variant for messages the one-shot pull handles badly (every rank reading every peer's
+// WHOLE message: (world - 1) x n bytes into each GPU): reduce-scatter + all-gather, the counterpart
+// of the reference's two-stage kernel (csrc/custom_all_reduce.cuh:239-290, dispatch :520-531).
+//   1. block b stages its chunk set of `in` into the own slot (as the one-shot kernel);
+//   2. per-block NVLink barrier A (flags[b][rank] = epoch);
+//   3. rank r sums chunks [r n / W, (r + 1) n / W) over all ranks (rank order, fp32) and PUSHES
+//      the fp16 result over that chunk in EVERY rank's slot -- the only reader of peer q's copy of
+//      such a chunk is rank r itself, which has read it before it overwrites it;
+//   4. system fence, per-block barrier B (flags2[b][rank] = epoch);
+//   5. the own slot now holds the whole reduced message: block b copies its chunk set to `out`.
+// Each GPU moves 2 (W - 1) / W x n bytes over NVLink instead of (W - 1) x n.  Chunk -> block is
+// the same map in every step and on every rank, so the per-block barriers cover exactly the
+// chunks a block touches.  Epochs, slots and the parity argument are shared with the other
+// kernels (a rank cannot reach call e + 2 before every peer has finished call e: barrier B).
+// `mode` (single-GPU emulation only, see tests/test_gpu_allreduce.py): 1 = all steps with barriers;
+// 2 = step 3 alone (inputs staged by the test); 3 = step 5 alone, on the epoch mode 2 left.
+template <int WORLD>
+__global__ void __launch_bounds__(2 * kArThreads)
+allreduce_twoshot_kernel(const ArParams p) {
+  constexpr int kT = 2 * kArThreads;
+  uint8_t* mine = p.region[p.rank];
+  uint32_t* my_flags = reinterpret_cast<uint32_t*>(mine) + blockIdx.x * kArMaxRanks;
+  uint32_t* my_flags2 = reinterpret_cast<uint32_t*>(mine + kArFlags2Off) + blockIdx.x * kArMaxRanks;
+  uint32_t* my_epoch = reinterpret_cast<uint32_t*>(mine + kArFlagBytes) + blockIdx.x;
+  __shared__ uint32_t s_epoch;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const int mode = p.barrier;
+  if (threadIdx.x == 0) s_epoch = *my_epoch + (mode == 3 ? 0u : 1u);
+  __syncthreads();
+  const uint32_t epoch = s_epoch;
+  const uint32_t slot_off = kArHeaderBytes + (epoch & 1u) * p.slot_bytes;
+  uint4* my_slot = reinterpret_cast<uint4*>(mine + slot_off);
+  const uint32_t first = blockIdx.x * kT + threadIdx.x, stride = gridDim.x * kT;
+
+  auto wait_peers = [&](uint32_t* flags_base_off_own, uint32_t off) {
+    if (threadIdx.x < WORLD) {
+      const int q = threadIdx.x;
+      uint32_t* peer_flag = reinterpret_cast<uint32_t*>(p.region[q] + off) + blockIdx.x * kArMaxRanks + p.rank;
+      st_release_sys(peer_flag, epoch);
+      const long long t0 = clock64();
+      while ((int32_t)(ld_acquire_sys(flags_base_off_own + q) - epoch) < 0) {
+        if (peer_wait_expired(t0)) {
+          printf("b200_w4a16: two-shot all-reduce barrier timeout rank %d block %d peer %d\n", p.rank,
+                 blockIdx.x, q);
+          __trap();
+        }
+      }
+    }
+    __syncthreads();
+  };
+
+  if (mode != 3) {
+    // 1. stage (the emulation stages every rank's input by hand: with the ranks run one after
+    // the other, a later rank's staging would overwrite what an earlier one pushed)
+    if (mode == 1) {
+      for (uint32_t c = first; c < p.nchunks; c += stride) my_slot[c] = p.in[c];
+      __threadfence_system();
+    }
+    __syncthreads();
+    // 2. barrier A
+    if (mode == 1) wait_peers(my_flags, 0u);
+    if (threadIdx.x == 0) *my_epoch = epoch;
+    if (blockIdx.x == 0 && threadIdx.x >= gridDim.x && threadIdx.x < kArMaxBlocks)
+      reinterpret_cast<uint32_t*>(mine + kArFlagBytes)[threadIdx.x] = epoch;
+    // 3. reduce the own range, push it everywhere
+    const uint32_t lo = (uint32_t)(((uint64_t)p.nchunks * (uint32_t)p.rank) / WORLD);
+    const uint32_t hi = (uint32_t)(((uint64_t)p.nchunks * (uint32_t)(p.rank + 1)) / WORLD);
+    for (uint32_t c = first; c < p.nchunks; c += stride) {
+      if (c < lo || c >= hi) continue;
+      uint4 v[WORLD];
+#pragma unroll
+      for (int q = 0; q < WORLD; ++q)
+        v[q] = ld_volatile_v4(reinterpret_cast<const uint4*>(p.region[q] + slot_off) + c);
+      float acc[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+      for (int q = 0; q < WORLD; ++q) add8(acc, v[q]);
+      uint4 o;
+      __half2* oh = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(acc[2 * i], acc[2 * i + 1]);
+#pragma unroll
+      for (int q = 0; q < WORLD; ++q)
+        reinterpret_cast<uint4*>(p.region[q] + slot_off)[c] = o;
+    }
+    __threadfence_system();
+    __syncthreads();
+    // 4. barrier B
+    if (mode == 1) wait_peers(my_flags2, (uint32_t)kArFlags2Off);
+  }
+  // 5. the own slot holds the reduced message
+  if (mode != 2)
+    for (uint32_t c = first; c < p.nchunks; c += stride) p.out[c] = ld_volatile_v4(my_slot + c);
+}
+
+template <int WORLD>
+int launch_ar_twoshot(const ArParams& prm, int blocks, cudaStream_t stream) {
+  allreduce_twoshot_kernel<WORLD><<<blocks, 2 * kArThreads, 0, stream>>>(prm);
+  return (int)cudaGetLastError();
+}
+
 template <int WORLD>
 int launch_ar_ll(const ArParams& prm, int blocks, cudaStream_t stream) {
   allreduce_ll_kernel<WORLD><<<blocks, kArThreads, 0, stream>>>(prm);
@@ -213,6 +315,35 @@ int launch_ar(const ArParams& prm, int blocks, cudaStream_t stream) {
 size_t ar_region_bytes(size_t max_message_bytes) {
   const size_t slot = (max_message_bytes + 255) / 256 * 256;
   return kArHeaderBytes + 2 * slot;
+}
+
+int launch_allreduce_twoshot(void* const* regions, int rank, int world, const uint16_t* in,
+                             uint16_t* out, size_t n_halfs, size_t max_message_bytes, int mode,
+                             cudaStream_t stream) {
+  ArParams prm;
+  prm.ll_off = 0;
+  prm.ll_slot_bytes = 0;
+  for (int q = 0; q < kArMaxRanks; ++q) prm.region[q] = q < world ? static_cast<uint8_t*>(regions[q]) : nullptr;
+  prm.in = reinterpret_cast<const uint4*>(in);
+  prm.out = reinterpret_cast<uint4*>(out);
+  prm.nchunks = (uint32_t)(n_halfs / 8);
+  prm.slot_bytes = (uint32_t)((max_message_bytes + 255) / 256 * 256);
+  prm.rank = rank;
+  prm.world = world;
+  prm.barrier = mode;
+  int blocks = (int)((prm.nchunks + 2 * kArThreads - 1) / (2 * kArThreads));
+  if (blocks < 1) blocks = 1;
+  if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  switch (world) {
+    case 2: return launch_ar_twoshot<2>(prm, blocks, stream);
+    case 3: return launch_ar_twoshot<3>(prm, blocks, stream);
+    case 4: return launch_ar_twoshot<4>(prm, blocks, stream);
+    case 5: return launch_ar_twoshot<5>(prm, blocks, stream);
+    case 6: return launch_ar_twoshot<6>(prm, blocks, stream);
+    case 7: return launch_ar_twoshot<7>(prm, blocks, stream);
+    case 8: return launch_ar_twoshot<8>(prm, blocks, stream);
+    default: return (int)cudaErrorInvalidValue;
+  }
 }
 
 int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* in, uint16_t* out,

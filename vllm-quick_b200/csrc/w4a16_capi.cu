@@ -402,6 +402,24 @@ int b200_w4a16_allreduce(void* const* regions, int rank, int world, const uint16
   return e == 0 ? B200_OK : cuda_fail(e);
 }
 
+int b200_w4a16_allreduce_twoshot(void* const* regions, int rank, int world, const uint16_t* in,
+                                 uint16_t* out, size_t n_halfs, size_t max_message_bytes, int mode,
+                                 b200_stream_t stream) {
+  if (world < 2 || world > b200::kArMaxRanks || rank < 0 || rank >= world) return B200_ERR_BAD_ARG;
+  if (mode < 1 || mode > 3) return B200_ERR_BAD_ARG;
+  if (n_halfs % 8 != 0 || n_halfs * 2 > max_message_bytes || n_halfs / 8 > 0xFFFFFFFFull)
+    return B200_ERR_BAD_SHAPE;
+  if (n_halfs == 0) return B200_OK;
+  if (!regions || !in || !out || !aligned16(in) || !aligned16(out)) return B200_ERR_BAD_ARG;
+  for (int q = 0; q < world; ++q)
+    if (!regions[q] || !aligned16(regions[q])) return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_allreduce_twoshot(regions, rank, world, in, out, n_halfs, max_message_bytes,
+                                         mode, reinterpret_cast<cudaStream_t>(stream));
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
 int b200_w4a16_moe_gather(const uint16_t* x, const int32_t* idx, uint16_t* out, size_t rows,
                           int hidden, b200_stream_t stream) {
   if (hidden <= 0 || hidden % 8 != 0) return B200_ERR_BAD_SHAPE;

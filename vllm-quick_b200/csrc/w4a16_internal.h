@@ -67,17 +67,26 @@ int launch_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int d, i
 
 // NVLink peer-memory all-reduce (w4a16_allreduce.cu).  Region = header + two data slots.
 // Region layout: [0, 2 KiB) flags[block][rank] | [2 KiB, +256) per-block epochs |
-// [3 KiB, +8) fused epoch + done counter | [16 KiB ...) two all-reduce slots, then
+// [3 KiB, +8) fused epoch + done counter | [4 KiB, +2 KiB) flags2[block][rank] |
+// [16 KiB ...) two all-reduce slots, then
 // (fused_bytes > 0) 2 x world fused packet slots.
 constexpr int kArMaxBlocks = 64;
 constexpr int kArFlagBytes = kArMaxBlocks * kArMaxRanks * 4;   // flags[block][rank]
 constexpr int kArFusedCtrOff = 3072;
+constexpr int kArFlags2Off = 4096;                             // second barrier of the two-shot kernel: flags2[block][rank]
 constexpr int kArHeaderBytes = 16384;
 static_assert(kArFlagBytes + kArMaxBlocks * 4 <= kArFusedCtrOff, "all-reduce header layout");
+static_assert(kArFusedCtrOff + 8 <= kArFlags2Off && kArFlags2Off + kArFlagBytes <= kArHeaderBytes, "all-reduce header layout");
 size_t ar_region_bytes(size_t max_message_bytes);
 int launch_allreduce(void* const* regions, int rank, int world, const uint16_t* in, uint16_t* out,
                      size_t n_halfs, size_t max_message_bytes, int barrier, cudaStream_t stream,
                      size_t ll_offset = 0, size_t ll_message_bytes = 0);
+
+// Reduce-scatter + all-gather over the same regions (messages above the one-shot sizes).
+// mode 1 = collective; 2 / 3 = the two halves without barriers (single-GPU emulation).
+int launch_allreduce_twoshot(void* const* regions, int rank, int world, const uint16_t* in,
+                             uint16_t* out, size_t n_halfs, size_t max_message_bytes, int mode,
+                             cudaStream_t stream);
 
 // Residual add + RMSNorm, standalone and fused behind the one-shot all-reduce (w4a16_norm.cu).
 // hidden % 8 == 0, hidden <= norm_max_hidden(); residual_in / residual_out may be nullptr.

@@ -1,8 +1,9 @@
 """NVLink peer-memory all-reduce for the row-parallel linears (Python side).
 
 Counterpart of the reference's vllm/model_executor/parallel_utils/custom_all_reduce.py:26-227
-(init / capture / CustomAllreduce) on top of ``b200_w4a16_allreduce`` (one-shot kernel,
-csrc/w4a16_allreduce.cu).  Differences that matter:
+(init / capture / CustomAllreduce) on top of the kernels of csrc/w4a16_allreduce.cu: flag-in-data
+packets for decode-sized messages, the one-shot pull up to a few hundred KiB, reduce-scatter +
+all-gather (two-shot) up to the registered size.  Differences that matter:
 
 * no buffer registration step at graph capture: inputs are staged into the rank's own
   registered region by the kernel itself, so any tensor can be reduced, eagerly or inside a
@@ -47,6 +48,11 @@ class CustomAllreduce:
         # the same split the reference makes between its one- and two-stage kernels
         # (csrc/custom_all_reduce.cuh:520-531).  A tuning value: tests and benches may raise it.
         self.oneshot_max_bytes = (128 << 10) if self.world <= 2 else (512 << 10)
+        # Above the one-shot size and up to the registered size: reduce-scatter + all-gather
+        # (b200_w4a16_allreduce_twoshot).  Not at two ranks, where it moves the same bytes as the
+        # one-shot kernel behind two barriers instead of one (the reference makes the same
+        # exception, custom_all_reduce.cuh:520-524): those messages go to NCCL.
+        self.use_twoshot = self.world > 2
         self.use_ll = True      # flag-in-data packets when the message fits the packet area
         # packets double the NVLink bytes and every rank receives world - 1 copies: measured to
         # win up to 1 MiB at TP = 2 (r1e_allreduce_norm_bench_tp2.jsonl); not yet measured per
@@ -89,13 +95,23 @@ class CustomAllreduce:
         nbytes = t.numel() * t.element_size()
         return (t.is_cuda and t.dtype == torch.float16 and t.is_contiguous()
                 and nbytes % 16 == 0 and t.data_ptr() % 16 == 0
-                and (0 < nbytes <= min(self.max_bytes, self.oneshot_max_bytes) or self._fits_ll(nbytes)))
+                and (0 < nbytes <= min(self.max_bytes, self.oneshot_max_bytes) or self._fits_ll(nbytes)
+                     or self._fits_twoshot(nbytes)))
 
     def _fits_ll(self, nbytes: int) -> bool:
         return self.use_ll and 0 < nbytes <= min(self.ll_bytes, self.ll_max_bytes)
 
+    def _fits_twoshot(self, nbytes: int) -> bool:
+        return self.use_twoshot and self.oneshot_max_bytes < nbytes <= self.max_bytes
+
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         out = torch.empty_like(t)
+        if not self._fits_ll(t.numel() * 2) and self._fits_twoshot(t.numel() * 2):
+            st = _lib.lib().b200_w4a16_allreduce_twoshot(
+                self._regions, self.rank, self.world, t.data_ptr(), out.data_ptr(), t.numel(),
+                self.max_bytes, 1, torch.cuda.current_stream(t.device).cuda_stream)
+            _lib.check(st, "custom all-reduce (two-shot)")
+            return out
         if self._fits_ll(t.numel() * 2):
             st = _lib.lib().b200_w4a16_allreduce_ll(
                 self._regions, self.rank, self.world, t.data_ptr(), out.data_ptr(), t.numel(),
