@@ -32,8 +32,13 @@ def main():
     ap.add_argument("--min-mb", type=int, default=512)
     ap.add_argument("--kernel", default=None, choices=["decode", "tcgen05"],
                     help="pin the kernel variant (loads the tuning build: make -C vllm-quick_b200/csrc tune)")
+    ap.add_argument("--lib", default=None, help="load lib/<file> instead (tuning builds: make variant / diag)")
     args = ap.parse_args()
-    if args.kernel:
+    if args.lib:
+        if args.kernel:
+            os.environ["B200_W4A16_KERNEL"] = args.kernel
+        pkg._lib.use_library(args.lib)
+    elif args.kernel:
         os.environ["B200_W4A16_KERNEL"] = args.kernel
         pkg._lib.use_library("libb200_w4a16_tune.so")
     dev = torch.device("cuda", 0)

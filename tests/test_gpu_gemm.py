@@ -234,8 +234,7 @@ def test_gemm_mixtral_shapes(pkg, oracle, cuda_lib, M, K, N):
 @pytest.mark.parametrize("M", [17, 24, 32, 33, 48, 64])
 @pytest.mark.parametrize("K,N", [(4096, 4096), (4096, 22016), (11008, 4096), (1024, 8192), (256, 128), (4096, 192)])
 def test_gemm_mid_batches(pkg, oracle, cuda_lib, M, K, N):
-    """17..64 tokens: the tcgen05 kernel with 32- / 64-token tiles (single channel tiles on the
-    small shapes, channel-tile pairs on 4096 -> 22016)."""
+    """17..64 tokens: the tcgen05 kernel with 32- / 64-token tiles."""
     assert cuda_lib.b200_w4a16_gemm_variant(M, K, N, 128) == 0
     x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, 128, seed=M * 7 + N, n_words=min(16, N // 8))
     y = pkg.ops.quick_gemm(x, pkg.ops.quick_repack(qw), s, qz, 8)
@@ -246,11 +245,11 @@ def test_gemm_mid_batches(pkg, oracle, cuda_lib, M, K, N):
 
 
 @pytest.mark.parametrize("M,K,N,G", [
-    (40, 16384, 19 * 128, 128),       # odd channel-tile count with pairs: the phantom tile is dropped
+    (140, 8192, 19 * 128, 128),       # odd channel-tile count with pairs: the phantom tile is dropped
     (300, 5120, 37 * 128, 128),
     (130, 16384, 11 * 128 + 64, 128), # ragged last tile
     (520, 2048, 4096, 64),            # G < 128: two (scale, zero) rows per weight tile
-    (96, 16384, 2560, 32),            # G = 32: four rows per tile
+    (200, 8192, 2560, 32),            # G = 32: four rows per tile
 ])
 def test_gemm_channel_tile_pairs(pkg, oracle, cuda_lib, M, K, N, G):
     """Work units of two channel tiles (one activation tile feeds both) on shapes where the

@@ -280,7 +280,7 @@ def test_moe_block_at_mixtral_shapes(pkg, oracle, cuda_lib, tokens, routed):
     assert moe.experts[0].w1.qweight.numel() == 0          # merged into one gate/up weight, originals released
     assert moe.experts[0]._w13["scales"].shape == (4096 // G, 2 * 14336)
     # K = 14336 makes single expert outputs reach +-45 (fp16 spacing 3e-2) while their weighted
-    # sum can cancel: the bar of the GEMM tests, relative to the experts' absolute contributions
+    # sum can cancel: twice the bar of the GEMM tests (three GEMMs deep), relative to the experts' absolute contributions
     err = (got.float().cpu() - want).abs()
-    assert bool((err <= 1e-2 * mag.clamp(min=1.0)).all()), float((err / mag.clamp(min=1.0)).max())
+    assert bool((err <= 2e-2 * mag.clamp(min=1.0)).all()), float((err / mag.clamp(min=1.0)).max())
     assert torch.equal(got, moe(x.cuda()).reshape(tokens, 4096))   # deterministic

@@ -74,6 +74,20 @@ constexpr int kCommit = 2;                              // weight tiles per tcge
 template <int V>
 struct IntC { static constexpr int value = V; };
 
+// ring depths below 128 tokens (tuning builds may override: make variant)
+#ifndef B200_XST64
+#define B200_XST64 6
+#endif
+#ifndef B200_WST64
+#define B200_WST64 12
+#endif
+#ifndef B200_XST32
+#define B200_XST32 8
+#endif
+#ifndef B200_WST32
+#define B200_WST32 16
+#endif
+
 template <int MTOK, int PAIR>
 struct Cfg {
   // accumulators: PAIR per buffer set; two sets (drain overlaps the next tile's MMAs) unless
@@ -86,12 +100,12 @@ struct Cfg {
   static constexpr int kDCol = kABufs * kTmemACols;    // accumulators start here
   // activation ring
   static constexpr int kXBytes = MTOK * 256;           // two swizzle atoms of [MTOK x 64] fp16
-  static constexpr int kXStages = MTOK >= 128 ? 4 : MTOK == 64 ? 6 : 8;
+  static constexpr int kXStages = MTOK >= 128 ? 4 : MTOK == 64 ? B200_XST64 : B200_XST32;
   // weight ring: [8 KiB tile | 4 x 256 B scale rows | 4 x 64 B zero rows]
   static constexpr int kSOff = kTileWords * 4;
   static constexpr int kZOff = kSOff + kScaleRowsMax * 256;
   static constexpr int kWStageBytes = kZOff + kScaleRowsMax * 64;            // 9472
-  static constexpr int kWStages = MTOK >= 128 ? 8 : MTOK == 64 ? 12 : 16;
+  static constexpr int kWStages = MTOK >= 128 ? 8 : MTOK == 64 ? B200_WST64 : B200_WST32;
   static constexpr int kBarBytes = 1024;
   static constexpr int kXOff = kBarBytes;                                    // 1024-aligned
   static constexpr int kWOff = kXOff + kXStages * kXBytes;
@@ -102,7 +116,10 @@ struct Cfg {
   static constexpr int kRingTiles = kXStages * PAIR > kABufs ? kXStages * PAIR : kABufs;
   static constexpr int kDoneBars = kRingTiles / kCommit + 2;
   static constexpr int kNumBars = 2 * kWStages + kXStages + kDoneBars + kABufs + kAccBufs + kAccBufs * PAIR;
-  static_assert(kWStages % kGroups == 0, "a weight stage must always be drained by the same dequant group");
+  // A dequant group waits for the MMAs of tile w - kABufs before it looks at tile w's stage:
+  // with kWStages >= kABufs the stage's previous tenant (tile w - kWStages) has then been
+  // dequantized, i.e. had landed -- the parity wait cannot pass on a stale phase.
+  static_assert(kWStages >= kABufs, "stage reuse must be covered by the operand-ring wait");
   static_assert(kWStages % 2 == 0 && kABufs % kCommit == 0, "producer / commit parity");
   static_assert(kWStageBytes % 128 == 0 && kXBytes % 1024 == 0, "ring alignment");
   static_assert(kDCol + kAccCols <= kTmemCols, "TMEM budget");
@@ -441,8 +458,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
         const int g = (w - C::kABufs) / kCommit;
         mbar_wait(bar_done + 8 * (g % C::kDoneBars), (uint32_t)(g / C::kDoneBars) & 1u);
       }
-      // kWStages is a multiple of the group count: this group drained the stage's previous
-      // phase itself, so the parity wait cannot pass on a stale phase.
+      // (that wait also covers the stage's previous phase, see Cfg: no stale pass here)
       mbar_wait(bar_wfull + 8 * stage, fphase);
       if ((threadIdx.x & 127) == 0) TR(1, w);
       uint4 wv[4];
@@ -780,12 +796,14 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
   const int tok = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;
   plan->tok_tile = tok;
   plan->m_tiles = (M + tok - 1) / tok;
-  // Channel tiles in groups of two when that still leaves every SM a long walk (>= 8 unit steps):
-  // one activation tile then feeds two weight tiles.  Small problems keep single tiles, where
-  // the finer work items balance better across the SMs.
+  // Channel tiles in groups of two for 128-token tiles (prefill: the activation tile is 4x the
+  // weight tile and L2 -> SM bytes bound the kernel) when that still leaves every SM a long walk
+  // (>= 8 unit steps): one activation tile then feeds two weight tiles.  Below 128 tokens single
+  // tiles measured faster on every shape but one (profiles/r2q_ring_pair_variants.md), and small
+  // problems balance better with the finer work items.
   {
     const long long units2 = (long long)((plan->n_tiles + 1) / 2) * plan->m_tiles * plan->k_blocks;
-    if (plan->n_tiles >= 2 && units2 >= 8LL * sm_count) plan->pair = 2;
+    if (tok == 128 && plan->n_tiles >= 2 && units2 >= 8LL * sm_count) plan->pair = 2;
     const int fp = forced_pair();
     if (fp == 1) plan->pair = 1;
     if (fp == 2 && plan->n_tiles >= 2) plan->pair = 2;
