@@ -83,7 +83,12 @@ int b200_w4a16_workspace_init(void *workspace, size_t workspace_bytes, b200_stre
  * Preconditions (B200_ERR_BAD_SHAPE otherwise): M >= 0, N % 64 == 0, G % 32 == 0,
  * K % G == 0, K % 128 == 0, G in {32, 64} or G % 128 == 0.  M == 0 is a no-op.
  * `split_k_hint` is the reference's split_k_iters: accepted, used only as a tuning hint
- * (<= 0 lets the library choose). */
+ * (<= 0 lets the library choose).
+ * Cost of `layout` = B200_LAYOUT_AWQ: the whole weight is interleaved into the workspace on
+ * EVERY call (a second kernel that reads and writes K * N / 2 bytes, and no programmatic overlap
+ * with the previous launch) -- at decode sizes more than twice the time of a B200_LAYOUT_B200
+ * call.  It exists so that a literal awq_gemm binding works; a linear method should repack once
+ * after loading (b200_w4a16_repack) and pass layout 1 from then on. */
 int b200_w4a16_gemm(const uint16_t *x, const int32_t *qweight, const uint16_t *scales,
                     const int32_t *qzeros, uint16_t *y, int M, int K, int N, int G,
                     int layout, int split_k_hint, void *workspace, size_t workspace_bytes,
