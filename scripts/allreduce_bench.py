@@ -66,7 +66,7 @@ def main():
 
     def variant(ll, oneshot_max, twoshot):
         def fn(t):
-            h.use_ll, h.oneshot_max_bytes, h.use_twoshot = ll, oneshot_max, twoshot
+            h.use_ll, h.oneshot_max_bytes, h.use_twoshot, h.twoshot_min_bytes = ll, oneshot_max, twoshot, 0
             o = pu.custom_all_reduce.maybe_all_reduce(t)
             assert o is not None
             return o

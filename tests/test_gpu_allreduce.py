@@ -243,6 +243,7 @@ def _rank_main(rank, world, port, q):
         # one-shot kernel (same rank-order fp32 sums: same bits) and NCCL; mixed with small calls
         h = pu.custom_all_reduce._handle
         saved = (h.oneshot_max_bytes, h.use_twoshot, h.use_ll)
+        h.twoshot_min_bytes = 0
         for shape in [(256, 8192), (64, 8192), (33, 1000)]:
             x = torch.randn(shape, device=dev, generator=g).half()
             h.oneshot_max_bytes, h.use_twoshot, h.use_ll = 1 << 30, False, False

@@ -868,6 +868,10 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   prm.R = G >= kTileK ? 1 : kTileK / G;
   prm.Gdiv = G >= kTileK ? G / kTileK : 1;
   prm.flags = gemm_flags();
+  // (The weight stream keeps its L2 evict-first hint at every batch size.  Keeping weights
+  // resident across token tiles was measured -- profiles/r2t_kb_prefill_evict_normal.jsonl --
+  // and lost: the operand with the long reuse distance is the ACTIVATION matrix, re-read once
+  // per channel-tile group; 13824 -> 5120 at 2048 tokens fell from 1144 to 932 TFLOP/s.)
   prm.trace = g_trace;
   if (plan.pair == 2) {
     switch (plan.tok_tile) {

@@ -48,11 +48,18 @@ class CustomAllreduce:
         # the same split the reference makes between its one- and two-stage kernels
         # (csrc/custom_all_reduce.cuh:520-531).  A tuning value: tests and benches may raise it.
         self.oneshot_max_bytes = (128 << 10) if self.world <= 2 else (512 << 10)
-        # Above the one-shot size and up to the registered size: reduce-scatter + all-gather
-        # (b200_w4a16_allreduce_twoshot).  Not at two ranks, where it moves the same bytes as the
-        # one-shot kernel behind two barriers instead of one (the reference makes the same
-        # exception, custom_all_reduce.cuh:520-524): those messages go to NCCL.
-        self.use_twoshot = self.world > 2
+        # (the r2 sweeps: the packet kernel below beats the one-shot kernel at every size both
+        # fit -- 7.5 vs 21 us at 16 KiB, 18 vs 25 us at 256 KiB on 8 ranks -- so the one-shot
+        # kernel only serves messages the packet area cannot hold)
+        # Reduce-scatter + all-gather (b200_w4a16_allreduce_twoshot) for the largest messages.
+        # Measured per size against NCCL 2.28 (profiles/r2p_allreduce_bench_tp2.jsonl,
+        # r2r_allreduce_bench_tp{4,8}.jsonl): at 8 ranks it wins from 4 MiB up (49 vs 58 us, 66 vs
+        # 76 us at 8 MiB) and loses at 1-2 MiB (40-42 vs 33-36 us: two NVLink barriers); at 4 ranks
+        # NCCL wins everywhere above the packet sizes; at two ranks it moves the same bytes as the
+        # one-shot kernel behind two barriers (the reference makes the same exception,
+        # custom_all_reduce.cuh:520-524).  Tuning values: tests and benches may change them.
+        self.use_twoshot = self.world >= 6
+        self.twoshot_min_bytes = (2 << 20) + 1
         self.use_ll = True      # flag-in-data packets when the message fits the packet area
         # packets double the NVLink bytes and every rank receives world - 1 copies: measured to
         # win up to 1 MiB at TP = 2 (r1e_allreduce_norm_bench_tp2.jsonl); not yet measured per
@@ -102,7 +109,7 @@ class CustomAllreduce:
         return self.use_ll and 0 < nbytes <= min(self.ll_bytes, self.ll_max_bytes)
 
     def _fits_twoshot(self, nbytes: int) -> bool:
-        return self.use_twoshot and self.oneshot_max_bytes < nbytes <= self.max_bytes
+        return self.use_twoshot and max(self.oneshot_max_bytes + 1, self.twoshot_min_bytes) <= nbytes <= self.max_bytes
 
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         out = torch.empty_like(t)
