@@ -35,13 +35,6 @@
 #include <stdlib.h>
 #include <string.h>
 
-// B200_DIAG (tuning builds only, `make diag`): bit 0 no scale / zero copies, bit 1 consumers skip
-// the math, bit 2 no activation copies, bit 3 ring of 9 stages, bit 4 no HMMA, bit 5 no unpack,
-// bit 6 ring of 12 stages.  Results are garbage in every such build; only the timing is read.
-#ifndef B200_DIAG
-#define B200_DIAG 0
-#endif
-
 namespace b200 {
 
 namespace {
@@ -74,8 +67,7 @@ struct DCfg {
   static constexpr int kZOff = kSOff + 256;
   static constexpr int kStageBytes = ((kZOff + 64 + 127) / 128) * 128;
   // ring depth: as many stages as fit next to the hand-off buffer, a multiple of kDecGroups
-  static constexpr int kStages = (B200_DIAG & 8) ? 9 : (B200_DIAG & 64) ? 12 :
-                                 kDecGroups == 4 ? (MT == 1 ? 16 : 12) :
+  static constexpr int kStages = kDecGroups == 4 ? (MT == 1 ? 16 : 12) :
                                  kDecGroups == 2 ? (MT == 1 ? 18 : 14) : (MT == 1 ? 18 : 15);
   static constexpr int kBarBytes = 512;
   static constexpr int kPartFloats = kGroupThreads * 8 * MT;     // fp32 partial tile
@@ -249,16 +241,14 @@ w4a16_decode_kernel(const DecodeParams p) {
     auto issue_w = [&](const Cur& c) {                        // lane 0 only
       const int kb = c.kb0 + c.i;
       const uint32_t nvalid = (uint32_t)min(kTileN, p.N - c.nt * kTileN);
-      const uint32_t tx = (B200_DIAG & 1) ? kTileWords * 4 : kTileWords * 4 + nvalid * 2 + nvalid / 2;
+      const uint32_t tx = kTileWords * 4 + nvalid * 2 + nvalid / 2;
       const uint32_t sb = stage0 + c.stage * C::kStageBytes;
       const uint32_t bar = bar_full + 8 * c.stage;
       const uint32_t g0 = p.Gdiv == 1 ? (uint32_t)kb : (uint32_t)kb / (uint32_t)p.Gdiv;
       mbar_arrive_expect_tx(bar, tx);
       bulk_g2s_hint(sb + C::kWOff, p.qw + ((size_t)c.nt * p.KB + kb) * kTileWords, kTileWords * 4, bar, pol_w);
-      if (!(B200_DIAG & 1)) {
-        bulk_g2s(sb + C::kSOff, p.scales + c.nt * kTileN + (size_t)g0 * srow, nvalid * 2, bar);
-        bulk_g2s(sb + C::kZOff, p.qz + c.nt * 16 + (size_t)g0 * zrow, nvalid / 2, bar);
-      }
+      bulk_g2s(sb + C::kSOff, p.scales + c.nt * kTileN + (size_t)g0 * srow, nvalid * 2, bar);
+      bulk_g2s(sb + C::kZOff, p.qz + c.nt * 16 + (size_t)g0 * zrow, nvalid / 2, bar);
     };
     auto issue_x = [&](const Cur& c) {                        // all lanes
       const int kb = c.kb0 + c.i;
@@ -268,7 +258,7 @@ w4a16_decode_kernel(const DecodeParams p) {
       for (int j = 0; j < 4; ++j)
 #pragma unroll
         for (int i = 0; i < MT; ++i)
-          if (!(B200_DIAG & 4)) cp_async_16(dst + (j * MT + i) * 512, xrow[i] + koff + j * 64, xsz[i]);
+          cp_async_16(dst + (j * MT + i) * 512, xrow[i] + koff + j * 64, xsz[i]);
       cp_async_mbar_arrive_noinc(bar_full + 8 * c.stage);
     };
     Cur c0{0, 0, 0, 0, 0, 0, pw, 0u};
@@ -433,72 +423,29 @@ w4a16_decode_kernel(const DecodeParams p) {
 #pragma unroll
             for (int e = 0; e < 4; ++e) acc[b][i][e] = 0.f;
 #pragma unroll
-        for (int j = 0; j < ((B200_DIAG & (2 | 512)) ? 0 : 4); ++j) {
+        for (int j = 0; j < 4; ++j) {
           uint4 xf[MT];
 #pragma unroll
           for (int i = 0; i < MT; ++i)
-            xf[i] = (B200_DIAG & 256) ? make_uint4(lane + j, lane ^ i, 0x3c003c00u, 0x3c003c00u + wi)
-                                      : *reinterpret_cast<const uint4*>(sb + C::kXOff + ((j * MT + i) * 32 + lane) * 16);
+            xf[i] = *reinterpret_cast<const uint4*>(sb + C::kXOff + ((j * MT + i) * 32 + lane) * 16);
 #pragma unroll
           for (int b = 0; b < 2; ++b) {
             const uint8_t* wp = sb + C::kWOff + j * 2048 + (cbase + 16 * b) * 16 + t * 4;
-            const uint32_t w0 = (B200_DIAG & 128) ? (uint32_t)(size_t)wp * 0x9e3779b1u : *reinterpret_cast<const uint32_t*>(wp);
-            const uint32_t w1 = (B200_DIAG & 128) ? (uint32_t)(size_t)wp * 0x85ebca6bu : *reinterpret_cast<const uint32_t*>(wp + 128);
+            const uint32_t w0 = *reinterpret_cast<const uint32_t*>(wp);
+            const uint32_t w1 = *reinterpret_cast<const uint32_t*>(wp + 128);
             uint32_t a[4], c[4];
-            if (B200_DIAG & 32) {
-              a[0] = w0; a[1] = w0 ^ zlo[b][0]; a[2] = w0 + zhi[b][0]; a[3] = ~w0;
-              c[0] = w1; c[1] = w1 ^ zlo[b][1]; c[2] = w1 + zhi[b][1]; c[3] = ~w1;
-            } else {
-              unpack_sub_zero(w0, zlo[b][0], zhi[b][0], a[0], a[1], a[2], a[3]);
-              unpack_sub_zero(w1, zlo[b][1], zhi[b][1], c[0], c[1], c[2], c[3]);
-            }
+            unpack_sub_zero(w0, zlo[b][0], zhi[b][0], a[0], a[1], a[2], a[3]);
+            unpack_sub_zero(w1, zlo[b][1], zhi[b][1], c[0], c[1], c[2], c[3]);
 #pragma unroll
             for (int i = 0; i < MT; ++i) {
-              if (B200_DIAG & 16) {
-                acc[b][i][0] += __uint_as_float((a[0] ^ c[1] ^ xf[i].x) & 0x3fffffffu);
-                acc[b][i][1] += __uint_as_float((a[1] ^ c[0] ^ xf[i].y) & 0x3fffffffu);
-                acc[b][i][2] += __uint_as_float((a[2] ^ c[3] ^ xf[i].z) & 0x3fffffffu);
-                acc[b][i][3] += __uint_as_float((a[3] ^ c[2] ^ xf[i].w) & 0x3fffffffu);
-              } else {
-                mma_16816(acc[b][i], a[0], c[0], a[1], c[1], xf[i].x, xf[i].y);
-                mma_16816(acc[b][i], a[2], c[2], a[3], c[3], xf[i].z, xf[i].w);
-              }
+              mma_16816(acc[b][i], a[0], c[0], a[1], c[1], xf[i].x, xf[i].y);
+              mma_16816(acc[b][i], a[2], c[2], a[3], c[3], xf[i].z, xf[i].w);
             }
           }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_empty + 8 * stage);    // every lane's loads have returned
         if (grp == 0 && ct == 0) TDT(wi / kDecGroups, 2);
-        if (B200_DIAG & 512) {
-          // register-only dummy work after the stage has been released: which instruction class
-          // (bit 10 HMMA, bit 11 ALU, bit 12 FMA) slows the weight stream down?
-          uint32_t d0 = zlo[0][0] ^ wi, d1 = zhi[0][1] + lane, d2 = zlo[1][0] * 3u, d3 = zhi[1][1] ^ 0x5555u;
-          if (B200_DIAG & 1024) {
-#pragma unroll
-            for (int r = 0; r < 16 * MT / 4; ++r)
-#pragma unroll
-              for (int b = 0; b < 2; ++b)
-#pragma unroll
-                for (int i = 0; i < 2; ++i) mma_16816(acc[b][i % MT], d0, d1, d2, d3, d1 + r, d2 + b);
-          }
-          if (B200_DIAG & 2048) {
-#pragma unroll
-            for (int r = 0; r < 12; ++r) {
-              d0 = lop3_and_or(d0 >> 1, d1, d2); d1 = lop3_and_or(d1 >> 3, d2, d3);
-              d2 = lop3_and_or(d2 >> 5, d3, d0); d3 = lop3_and_or(d3 >> 7, d0, d1);
-            }
-            acc[0][0][0] += __uint_as_float((d0 ^ d1 ^ d2 ^ d3) & 0x3fffffffu);
-          }
-          if (B200_DIAG & 4096) {
-            float f0 = __uint_as_float(d0 & 0x3fffffffu), f1 = __uint_as_float(d1 & 0x3fffffffu);
-            float f2 = sc[0][0], f3 = sc[1][1];
-#pragma unroll
-            for (int r = 0; r < 25; ++r) {
-              f0 = fmaf(f0, f1, f2); f1 = fmaf(f1, f2, f3); f2 = fmaf(f2, f3, f0); f3 = fmaf(f3, f0, f1);
-            }
-            acc[0][0][1] += f0 + f1 + f2 + f3;
-          }
-        }
 #pragma unroll
         for (int b = 0; b < 2; ++b)
 #pragma unroll
