@@ -236,7 +236,8 @@ def kernel_name(pkg, M, K, N):
     plan = pkg._lib.gemm_plan(M, K, N)
     if plan["variant"] == "decode":
         return f"w4a16_decode_kernel<{plan['tok_tile'] // 8}>"
-    return f"w4a16_gemm_kernel<{plan['tok_tile']}, {plan['unit_tiles']}>"
+    ut = plan["unit_tiles"]
+    return f"w4a16_gemm_kernel<{plan['tok_tile']}, {min(ut, 2)}, {'true' if ut == 4 else 'false'}>"
 
 
 def rand_awq(torch, dev, g, K, N):

@@ -141,9 +141,10 @@ int b200_w4a16_gemm_plan(int M, int K, int N, int G, int split_k_hint, int *tok_
 enum { B200_VARIANT_TCGEN05 = 0, B200_VARIANT_DECODE = 1 };
 int b200_w4a16_gemm_variant(int M, int K, int N, int G);
 
-/* Introspection: channel tiles per work unit of the tcgen05 kernel for this problem -- 2 when
- * one activation tile feeds two adjacent 128-channel weight tiles (large problems), else 1
- * (always 1 for B200_VARIANT_DECODE).  Negative: -b200_status_t. */
+/* Introspection: channel tiles per work unit of the tcgen05 kernel for this problem -- 1; 2 when
+ * one activation tile feeds two adjacent 128-channel weight tiles of a CTA; 4 when a CTA pair
+ * (tcgen05 cta_group::2) shares the activation tile, two channel tiles per CTA (large problems
+ * with 128-token tiles).  Always 1 for B200_VARIANT_DECODE.  Negative: -b200_status_t. */
 int b200_w4a16_gemm_unit_tiles(int M, int K, int N, int G);
 
 /* ---- NVLink peer-memory all-reduce for the row-parallel linears --------------------------

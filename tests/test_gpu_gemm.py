@@ -252,10 +252,11 @@ def test_gemm_mid_batches(pkg, oracle, cuda_lib, M, K, N):
     (200, 8192, 2560, 32),            # G = 32: four rows per tile
 ])
 def test_gemm_channel_tile_pairs(pkg, oracle, cuda_lib, M, K, N, G):
-    """Work units of two channel tiles (one activation tile feeds both) on shapes where the
-    pairing has an edge -- odd tile counts, ragged N, G < 128: every token row, a sample of
-    channels that always includes the first and the last ones."""
-    assert cuda_lib.b200_w4a16_gemm_unit_tiles(M, K, N, G) == 2
+    """Work units of two channel tiles per CTA (one activation tile feeds both) and of four per
+    CTA pair (cta_group::2, the activation tile split between two SMs) on shapes where the
+    grouping has an edge -- tile counts that are not multiples of 2 / 4, ragged N, G < 128: every
+    token row, a sample of channels that always includes the first and the last ones."""
+    assert cuda_lib.b200_w4a16_gemm_unit_tiles(M, K, N, G) in (2, 4)    # pairs within a CTA / CTA pairs
     x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, G, seed=M + N, n_words=12, edge_words=4)
     r = pkg.ops.quick_repack(qw)
     y = pkg.ops.quick_gemm(x, r, s, qz, 8)

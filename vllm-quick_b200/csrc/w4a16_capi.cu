@@ -162,7 +162,7 @@ int b200_w4a16_gemm_unit_tiles(int M, int K, int N, int G) {
   b200::GemmPlan plan;
   if (b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, 0, sm_count_or_default(), &plan))
     return -B200_ERR_BAD_SHAPE;
-  return plan.pair;
+  return plan.pair * (plan.two_cta ? 2 : 1);
 }
 
 int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,

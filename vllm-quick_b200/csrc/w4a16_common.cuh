@@ -337,6 +337,82 @@ __device__ __forceinline__ void tmem_st_x32(uint32_t taddr, const uint32_t (&v)[
       : "memory");
 }
 
+// ----------------------------------------------------------------------------- CTA pairs (cta_group::2)
+// Two CTAs of a cluster on the SMs of one TPC issue ONE tcgen05.mma of M = 256: each holds 128
+// rows of A (its own TMEM) and of D, and HALF of the B operand (N / 2 rows) in its own shared
+// memory.  Only the leader (cluster rank 0) issues MMAs and owns the barriers the MMA thread
+// waits on; the peer signals them remotely.  Forms as in CUTLASS (cute/arch/mma_sm100_umma.hpp
+// SM100_MMA_F16BF16_2x1SM_TS, copy_sm100_tma.hpp SM100_TMA_2SM_LOAD_2D, cutlass/arch/barrier.h
+// umma_arrive_multicast_2x1SM, tmem_allocator_sm100.hpp Allocator2Sm).
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cta address -> the same offset in CTA `rank` of the cluster (shared::cluster address)
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+// Remote arrive with the default (CTA-scope release) semantics, as CUTLASS's ClusterBarrier does:
+// an explicit .release.cluster costs a full drain of the SM's memory pipeline per arrive -- every
+// dequant group of the peer CTA then finished ~2000 cycles late, all at the same instant
+// (profiles/r2u_trace_prefill_two_release_cluster.txt).  The TMEM data it publishes is ordered by
+// tcgen05.wait::st + tcgen05.fence::before_thread_sync on this side and fence::after_thread_sync
+// on the MMA issuer's.
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_slot) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_slot),
+               "n"(COLS)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS)
+               : "memory");
+}
+// MMA completion -> arrive on the barrier at this offset in BOTH CTAs of the pair.
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {
+  const uint16_t mask = 3;
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"(mask)
+      : "memory");
+}
+// D[tmem, both CTAs] (+)= A[tmem, 128 rows per CTA] . B[smem desc, N / 2 rows per CTA]
+__device__ __forceinline__ void tc_mma_ts_pair(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc,
+                                               uint32_t idesc, uint32_t accumulate) {
+  const uint32_t z = 0;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(z)
+      : "memory");
+}
+// 2-D tiled TMA load whose bytes are counted on the LEADER's barrier (peer bit cleared).
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const void* tmap, int c0, int c1,
+                                                 uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(tmap), "r"(c0), "r"(c1), "r"(bar & 0xFEFFFFFFu)
+      : "memory");
+}
+// Instruction descriptor, kind::f16, fp16 A/B (K-major), fp32 D, M = m (128 or 256 for a pair), N = n.
+__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {
+  return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
 // One thread of a converged warp.  Code under `if (elect_one())` is known by the compiler to
 // run on a single thread, so operands of UBLKCP / UTMALDG / UTCHMMA move to uniform registers
 // directly instead of through a per-instruction waterfall loop (which `lane == 0` triggers).

@@ -69,11 +69,15 @@ constexpr int kScaleRowsMax = 4;                        // G = 32 -> four (scale
 constexpr int kTmemACols = 64;                          // one dequantized tile: 128 fp16 per lane
 constexpr int kTmemCols = 512;
 constexpr int kMaxSmem = 227 * 1024;
-constexpr int kCommit = 2;                              // weight tiles per tcgen05.commit
 
 template <int V>
 struct IntC { static constexpr int value = V; };
 
+// CTA pairs (cta_group::2) for 128-token tiles: measured +2-10 % on 10 of 12 Llama-2-13B prefill points
+// (profiles/r2x_kb_ab_two{0,1}.jsonl); B200_W4A16_TWO=0 in a tuning build switches them off
+#ifndef B200_GEMM_TWO_CTA_DEFAULT
+#define B200_GEMM_TWO_CTA_DEFAULT 1
+#endif
 // ring depths below 128 tokens (tuning builds may override: make variant)
 #ifndef B200_XST64
 #define B200_XST64 6
@@ -88,7 +92,9 @@ struct IntC { static constexpr int value = V; };
 #define B200_WST32 16
 #endif
 
-template <int MTOK, int PAIR>
+// TWO: a pair of CTAs (cluster of 2 on one TPC) issues tcgen05.mma.cta_group::2 -- each CTA holds its
+// own channel tiles (A, D) and HALF of the activation tile (MTOK / 2 tokens) in shared memory.
+template <int MTOK, int PAIR, bool TWO = false>
 struct Cfg {
   // accumulators: PAIR per buffer set; two sets (drain overlaps the next tile's MMAs) unless
   // 2 x 128 columns per set leave no room (MTOK = 128, PAIR = 2: one set, drained half by half)
@@ -99,17 +105,27 @@ struct Cfg {
   static constexpr int kABufs = kABufsFit >= 6 ? 6 : 4;
   static constexpr int kDCol = kABufs * kTmemACols;    // accumulators start here
   // activation ring
-  static constexpr int kXBytes = MTOK * 256;           // two swizzle atoms of [MTOK x 64] fp16
-  static constexpr int kXStages = MTOK >= 128 ? 4 : MTOK == 64 ? B200_XST64 : B200_XST32;
+  static constexpr int kXRows = TWO ? MTOK / 2 : MTOK; // token rows of the activation tile in THIS CTA
+  static constexpr int kXBytes = kXRows * 256;         // two swizzle atoms of [kXRows x 64] fp16
+  static constexpr int kXStages = TWO ? 6 : MTOK >= 128 ? 4 : MTOK == 64 ? B200_XST64 : B200_XST32;
   // weight ring: [8 KiB tile | 4 x 256 B scale rows | 4 x 64 B zero rows]
   static constexpr int kSOff = kTileWords * 4;
   static constexpr int kZOff = kSOff + kScaleRowsMax * 256;
   static constexpr int kWStageBytes = kZOff + kScaleRowsMax * 64;            // 9472
-  static constexpr int kWStages = MTOK >= 128 ? 8 : MTOK == 64 ? B200_WST64 : B200_WST32;
+  static constexpr int kWStages = TWO ? 12 : MTOK >= 128 ? 8 : MTOK == 64 ? B200_WST64 : B200_WST32;
   static constexpr int kBarBytes = 1024;
   static constexpr int kXOff = kBarBytes;                                    // 1024-aligned
   static constexpr int kWOff = kXOff + kXStages * kXBytes;
   static constexpr int kSmemBytes = kWOff + kWStages * kWStageBytes + 1024;  // + align slack
+  // Weight tiles per tcgen05.commit.  The commit frees the tile's operand buffer: with 128-token tiles
+  // (a tile's MMAs take 512 cycles) the operand ring, not memory, paced the kernel -- a buffer's cycle
+  // is dequant (~900) + wait + the MMAs up to the commit + wake-up, and with one commit per TWO
+  // tiles four buffers gave 650-670 cycles per tile in every configuration measured, CTA pairs
+  // included (profiles/r2v_trace_prefill_two.txt).  Below 128 tokens two tiles share a commit.
+#ifndef B200_COMMIT128
+#define B200_COMMIT128 1
+#endif
+  static constexpr int kCommit = MTOK >= 128 ? B200_COMMIT128 : 2;
   // MMA completion is signalled once per kCommit weight tiles (a tcgen05.commit costs the tensor
   // pipe ~110 cycles, scripts/probes/mma_probe.cu) on a ring of kDoneBars barriers; the
   // activation producer (stage reuse) and the dequant groups (operand-buffer reuse) wait on it.
@@ -187,10 +203,15 @@ __device__ __forceinline__ Owned find_owned(const Walk& walk, int KB, int P, int
   return r;
 }
 
-template <int MTOK, int PAIR>
+template <int MTOK, int PAIR, bool TWO>
 __global__ void __launch_bounds__(kThreads, 1)
 w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
-  using C = Cfg<MTOK, PAIR>;
+  using C = Cfg<MTOK, PAIR, TWO>;
+  // CTA pair: rank in the cluster (0 = leader: issues the MMAs, owns the barriers their issuer waits
+  // on); the work space is cut per PAIR of CTAs, both walk the same (token tile, K block) steps
+  const uint32_t crank = TWO ? cluster_ctarank() : 0u;
+  const int vblock = TWO ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int VP = TWO ? p.P >> 1 : p.P;
   if (threadIdx.x == 0) { TRG(2); TR(7, 5); }
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -215,8 +236,8 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
 
   // This CTA's contiguous slice of the work space, and the order it is walked in.  A work item
   // ("unit step") is one K block of one output unit = PAIR channel tiles x one token tile.
-  const int t_begin = range_begin(blockIdx.x, p.T, p.P);
-  const int t_end = range_begin(blockIdx.x + 1, p.T, p.P);
+  const int t_begin = range_begin(vblock, p.T, VP);
+  const int t_end = range_begin(vblock + 1, p.T, VP);
   const Walk walk(t_begin, t_end, p.KB);
   const int n_units = t_end - t_begin;
   const int n_w = n_units * PAIR;                               // weight tiles in stream order
@@ -232,12 +253,13 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   struct WStream {
     const GemmParams& p;
     const Walk& walk;
+    int crank_;
     int idx, left, h, gcnt;
     uint32_t sb0, zb0, sb1, zb1;                        // scale / zero row bytes of tile h = 0 / 1
     const uint32_t *w0, *w1, *z0, *z1;                  // weight tile, zero row
     const uint16_t *s0, *s1;                            // scale row
-    __device__ __forceinline__ WStream(const GemmParams& pp, const Walk& w)
-        : p(pp), walk(w), idx(-1), left(0), h(0), gcnt(0), sb0(0), zb0(0), sb1(0), zb1(0),
+    __device__ __forceinline__ WStream(const GemmParams& pp, const Walk& w, int cr)
+        : p(pp), walk(w), crank_(cr), idx(-1), left(0), h(0), gcnt(0), sb0(0), zb0(0), sb1(0), zb1(0),
           w0(nullptr), w1(nullptr), z0(nullptr), z1(nullptr), s0(nullptr), s1(nullptr) {}
     __device__ __forceinline__ void open() {
       h = 0;
@@ -250,7 +272,9 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       left = n;
       const int g0 = p.R > 1 ? kb * p.R : kb / p.Gdiv;
       gcnt = p.R > 1 ? 0 : kb - g0 * p.Gdiv;                  // K blocks into the current group
-      const int nta = ntp * PAIR;
+      // channel tiles of this CTA in the group (a tile beyond the matrix re-reads the last one)
+      int nta = (TWO ? ntp * 2 + crank_ : ntp) * PAIR;
+      if (nta >= p.NT) nta = p.NT - 1;
       const int ntb = (PAIR == 2 && nta + 1 < p.NT) ? nta + 1 : nta;
       const uint32_t va = (uint32_t)min(kTileN, p.N - nta * kTileN);
       const uint32_t vb = (uint32_t)min(kTileN, p.N - ntb * kTileN);
@@ -295,7 +319,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     }
   };
 
-  WStream cw(p, walk);                                      // opened by a producer thread only
+  WStream cw(p, walk, (int)crank);                          // opened by a producer thread only
   if (warp == kProducerWarp) {
     // Lane-parallel barrier init, then the first npre weight tiles go out BEFORE the CTA-wide
     // setup barrier and without ever waiting for the previous kernel: weights never depend on
@@ -304,8 +328,8 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       uint32_t count = 1u;                                   // wfull / xfull / done / dfull: one arriver
       if (b >= C::kWStages && b < 2 * C::kWStages) count = 4u;                    // wempty: one lane per warp
       const int a0 = 2 * C::kWStages + C::kXStages + C::kDoneBars;
-      if (b >= a0 && b < a0 + C::kABufs) count = 128u;                            // afull
-      if (b >= a0 + C::kABufs + C::kAccBufs) count = (uint32_t)kEpiThreads;       // dempty
+      if (b >= a0 && b < a0 + C::kABufs) count = TWO ? 256u : 128u;               // afull (pair: both CTAs' dequant groups)
+      if (b >= a0 + C::kABufs + C::kAccBufs) count = (uint32_t)kEpiThreads * (TWO ? 2u : 1u);   // dempty
       mbar_init(smem_base + 8 * b, count);
     }
     fence_barrier_init();
@@ -318,10 +342,11 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     }
     __syncwarp();
   } else if (warp == kAllocWarp) {
-    tmem_alloc<kTmemCols>(tmem_slot);
+    if (TWO) tmem_alloc_pair<kTmemCols>(tmem_slot); else tmem_alloc<kTmemCols>(tmem_slot);
   }
   tc_fence_before();
   __syncthreads();
+  if (TWO) cluster_sync_all();          // both CTAs' barriers exist before anything signals across
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_gen;
   if (threadIdx.x == 0) { TR(7, 0); TRG(3); }
@@ -368,15 +393,21 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
         walk.seg(idx, t0, n);
         const int o = t0 / p.KB;
         int k0 = (t0 - o * p.KB) * kTileK;
-        const int m0 = (o % p.MT) * MTOK;
+        const int m0 = (o % p.MT) * MTOK + (TWO ? (int)crank * C::kXRows : 0);   // pair: this CTA's token half
         for (int i = 0; i < n; ++i, ++u, k0 += kTileK) {
           if (u >= C::kXStages) {
-            const int g = ((u - C::kXStages) * PAIR + PAIR - 1) / kCommit;
+            const int g = ((u - C::kXStages) * PAIR + PAIR - 1) / C::kCommit;
             mbar_wait(bar_done + 8 * (g % C::kDoneBars), (uint32_t)(g / C::kDoneBars) & 1u);
           }
-          mbar_arrive_expect_tx(bar, (uint32_t)C::kXBytes);
-          tma_load_2d(sb, &tmap_x, k0, m0, bar);
-          tma_load_2d(sb + MTOK * 128, &tmap_x, k0 + 64, m0, bar);
+          if (TWO) {                                          // both halves are counted on the leader's barrier
+            if (crank == 0) mbar_arrive_expect_tx(bar, 2u * (uint32_t)C::kXBytes);
+            tma_load_2d_pair(sb, &tmap_x, k0, m0, bar);
+            tma_load_2d_pair(sb + C::kXRows * 128, &tmap_x, k0 + 64, m0, bar);
+          } else {
+            mbar_arrive_expect_tx(bar, (uint32_t)C::kXBytes);
+            tma_load_2d(sb, &tmap_x, k0, m0, bar);
+            tma_load_2d(sb + C::kXRows * 128, &tmap_x, k0 + 64, m0, bar);
+          }
           sb += C::kXBytes;
           bar += 8;
           if (bar == bar_xfull + 8 * C::kXStages) { sb = xring; bar = bar_xfull; }
@@ -385,12 +416,12 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     }
   } else if (warp == kMmaWarp) {
     __syncwarp();
-    if (elect_one()) {
+    if (elect_one() && crank == 0) {                          // pair: the leader issues for both CTAs
       // ONE thread issues every tcgen05.mma of the CTA, so its instruction count per tile is a
       // floor for the tile period: descriptors are a base plus compile-time constants, ring
       // positions advance incrementally (no modulo), and the operand barrier of the NEXT weight
       // tile is tested before this tile's MMAs so its latency hides behind them.
-      constexpr uint32_t idesc = make_idesc_f16_m128(MTOK);
+      constexpr uint32_t idesc = make_idesc_f16(TWO ? 256 : 128, MTOK);
       const uint64_t bdesc0 = make_desc_k_sw128(xring);           // activation stage 0, K slice 0
       constexpr uint32_t kXStep = C::kXBytes >> 4;                // descriptor address units (16 B)
       uint32_t x_off = 0;                                         // stage * kXStep
@@ -424,12 +455,14 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
             if (nbuf == C::kABufs) { nbuf = 0; nphase ^= 1u; }
             a_ready = w + 1 < n_w && mbar_try_wait(bar_afull + 8 * nbuf, nphase);
 #pragma unroll
-            for (int kk = 0; kk < 8; ++kk)
-              tc_mma_ts(dcol, acol + kk * 8, bd + (uint32_t)((kk >> 2) * (MTOK * 128 / 16) + (kk & 3) * 2), idesc,
-                        (uint32_t)((i | kk) != 0));
+            for (int kk = 0; kk < 8; ++kk) {
+              const uint64_t bk = bd + (uint32_t)((kk >> 2) * (C::kXRows * 128 / 16) + (kk & 3) * 2);
+              if (TWO) tc_mma_ts_pair(dcol, acol + kk * 8, bk, idesc, (uint32_t)((i | kk) != 0));
+              else tc_mma_ts(dcol, acol + kk * 8, bk, idesc, (uint32_t)((i | kk) != 0));
+            }
             ++w;
-            if ((w & (kCommit - 1)) == 0 || w == n_w) {
-              tc_commit(bar_done + 8 * done_slot);
+            if ((w & (C::kCommit - 1)) == 0 || w == n_w) {
+              if (TWO) tc_commit_pair(bar_done + 8 * done_slot); else tc_commit(bar_done + 8 * done_slot);
               if (++done_slot == C::kDoneBars) done_slot = 0;
             }
             TR(5, w - 1);
@@ -440,7 +473,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           xbar += 8;
           if (xbar == bar_xfull + 8 * C::kXStages) { x_off = 0; xbar = bar_xfull; xphase ^= 1u; }
         }
-        tc_commit(bar_dfull + 8 * d);
+        if (TWO) tc_commit_pair(bar_dfull + 8 * d); else tc_commit(bar_dfull + 8 * d);
       }
     }
   } else if (warp < kFirstEpiWarp) {
@@ -455,7 +488,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       const uint8_t* sb = wring_gen + stage * C::kWStageBytes;
       // Operand buffer w % kABufs was last read by the MMAs of weight tile w - kABufs.
       if (w >= C::kABufs) {
-        const int g = (w - C::kABufs) / kCommit;
+        const int g = (w - C::kABufs) / C::kCommit;
         mbar_wait(bar_done + 8 * (g % C::kDoneBars), (uint32_t)(g / C::kDoneBars) & 1u);
       }
       // (that wait also covers the stage's previous phase, see Cfg: no stale pass here)
@@ -499,7 +532,8 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       }
       tc_wait_st();
       tc_fence_before();
-      mbar_arrive(bar_afull + 8 * buf);
+      if (TWO && crank != 0) mbar_arrive_cluster(map_to_cta(bar_afull + 8 * buf, 0));   // the leader's barrier
+      else mbar_arrive(bar_afull + 8 * buf);
       if ((threadIdx.x & 127) == 0) TR(3, w);
       stage += kGroups;
       if (stage >= C::kWStages) { stage -= C::kWStages; fphase ^= 1u; }
@@ -530,7 +564,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       if (et == 0) TR(6, 2 * idx);
 #pragma unroll 1
       for (int h = 0; h < PAIR; ++h) {
-        const int n_glob = (ntp * PAIR + h) * kTileN + c;
+        const int n_glob = ((TWO ? ntp * 2 + (int)crank : ntp) * PAIR + h) * kTileN + c;
         // partial layout: quad v of channel c holds tokens 4 v .. 4 v + 3 -> [v][c], coalesced
         uint4* part = p.partials + (((size_t)blockIdx.x * 2 + slot) * PAIR + h) * kPartVec + c;
         const uint32_t dbase = tmem + lane_base + C::kDCol + (d * PAIR + h) * MTOK;
@@ -558,7 +592,8 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           }
         }
         tc_fence_before();
-        mbar_arrive(bar_dempty + 8 * (d * PAIR + h));
+        if (TWO && crank != 0) mbar_arrive_cluster(map_to_cta(bar_dempty + 8 * (d * PAIR + h), 0));
+        else mbar_arrive(bar_dempty + 8 * (d * PAIR + h));
       }
       if (et == 0) TR(6, 2 * idx + 1);
     }
@@ -573,17 +608,18 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   // this unit FIRST in their walk, so their partials are normally long there; every CTA of the
   // grid is resident (grid <= SM count), so the wait cannot deadlock.
   if (warp < kFirstEpiWarp + kEpiThreads / 32) {
-    const Owned own = find_owned(walk, p.KB, p.P, p.T, (int)blockIdx.x);
+    const Owned own = find_owned(walk, p.KB, VP, p.T, vblock);
     if (own.o >= 0) {
       asm volatile("griddepcontrol.wait;" ::: "memory");      // the dequant warps write y here
       constexpr int kPartVec = MTOK * kTileN / 4;
       constexpr int kQuads = PAIR * kPartVec;
       const int ntp = own.o / p.MT, mt = own.o - ntp * p.MT;
       const int m0 = mt * MTOK;
-      const int nother = own.last - (int)blockIdx.x;
+      const int nother = own.last - vblock;
+      constexpr int kStep = TWO ? 2 : 1;                      // pair: the same-rank CTA of the next pair
       uint4* const mine = p.partials + ((size_t)blockIdx.x * 2 + own.slot) * kQuads;
-      uint4* const others = p.partials + ((size_t)(blockIdx.x + 1) * 2) * kQuads;     // their slot 0
-      const size_t cstride = (size_t)2 * kQuads;
+      uint4* const others = p.partials + ((size_t)(blockIdx.x + kStep) * 2) * kQuads;   // their slot 0
+      const size_t cstride = (size_t)kStep * 2 * kQuads;
       const int ft = threadIdx.x;                               // 0 .. kFixThreads - 1
       auto pass = [&](auto kq_, auto kb_) {
         constexpr int KQ = decltype(kq_)::value, KB = decltype(kb_)::value;
@@ -635,7 +671,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
             const int qd = q0 + i * kFixThreads;
             if (qd < kQuads) {
               const int h = qd / kPartVec, r = qd % kPartVec;
-              const int n_glob = (ntp * PAIR + h) * kTileN + (r % kTileN);
+              const int n_glob = ((TWO ? ntp * 2 + (int)crank : ntp) * PAIR + h) * kTileN + (r % kTileN);
               const int m = m0 + 4 * (r / kTileN);
               if (n_glob < p.N) {
                 const float rr[4] = {acc[i].x, acc[i].y, acc[i].z, acc[i].w};
@@ -656,10 +692,11 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
 
   tc_fence_before();
   __syncthreads();
+  if (TWO) cluster_sync_all();          // the peer may still read our shared memory / signal our barriers
   if (threadIdx.x == 0) TR(7, 1);
   if (warp == kAllocWarp) {
     tc_fence_after();
-    tmem_dealloc<kTmemCols>(tmem);
+    if (TWO) tmem_dealloc_pair<kTmemCols>(tmem); else tmem_dealloc<kTmemCols>(tmem);
   }
 }
 
@@ -683,7 +720,7 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-template <int MTOK, int PAIR>
+template <int MTOK, int PAIR, bool TWO = false>
 int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& plan, bool pdl,
                 cudaStream_t stream) {
   // the opt-in is per device: a process may drive several GPUs
@@ -691,23 +728,34 @@ int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& 
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= kMaxDevices || !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(w4a16_gemm_kernel<MTOK, PAIR>,
+    cudaError_t e = cudaFuncSetAttribute(w4a16_gemm_kernel<MTOK, PAIR, TWO>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         Cfg<MTOK, PAIR>::kSmemBytes);
+                                         Cfg<MTOK, PAIR, TWO>::kSmemBytes);
     if (e != cudaSuccess) return (int)e;
     if (dev >= 0 && dev < kMaxDevices) attr_set[dev] = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(plan.ctas);
   cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = Cfg<MTOK, PAIR>::kSmemBytes;
+  cfg.dynamicSmemBytes = Cfg<MTOK, PAIR, TWO>::kSmemBytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (TWO) {                                              // CTA pairs: clusters of two on one TPC
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = pdl ? 1 : 0;
-  return (int)cudaLaunchKernelEx(&cfg, w4a16_gemm_kernel<MTOK, PAIR>, prm, tmap);
+  cfg.numAttrs = na;
+  return (int)cudaLaunchKernelEx(&cfg, w4a16_gemm_kernel<MTOK, PAIR, TWO>, prm, tmap);
 }
 
 int gemm_flags() {
@@ -724,10 +772,10 @@ int gemm_flags() {
 
 uint32_t* g_trace = nullptr;
 
-template <int MTOK, int PAIR>
+template <int MTOK, int PAIR, bool TWO = false>
 void fill_plan(GemmPlan* plan) {
-  plan->stages = Cfg<MTOK, PAIR>::kWStages;
-  plan->smem_bytes = Cfg<MTOK, PAIR>::kSmemBytes;
+  plan->stages = Cfg<MTOK, PAIR, TWO>::kWStages;
+  plan->smem_bytes = Cfg<MTOK, PAIR, TWO>::kSmemBytes;
 }
 
 // Tuning builds (`make tune`, -DB200_TUNING) can pin the variant with
@@ -741,6 +789,17 @@ int forced_kind() {
     if (e[0] == 't') return (int)kKindTcgen05;
     if (e[0] == 'd') return (int)kKindDecode;
     return -1;
+  }();
+  return k;
+#else
+  return -1;
+#endif
+}
+int forced_two() {
+#ifdef B200_TUNING
+  static const int k = [] {
+    const char* e = getenv("B200_W4A16_TWO");
+    return e ? atoi(e) : -1;
   }();
   return k;
 #else
@@ -771,6 +830,7 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
   plan->n_tiles = (N + kTileN - 1) / kTileN;
   plan->k_blocks = K / kTileK;
   plan->pair = 1;
+  plan->two_cta = 0;
   const int fk = forced_kind();
   const bool group_ok = G % kTileK == 0;                  // one (scale, zero) row per 128-row tile
   bool decode = group_ok && M <= kDecodeMaxTokens;
@@ -808,18 +868,40 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
     if (fp == 1) plan->pair = 1;
     if (fp == 2 && plan->n_tiles >= 2) plan->pair = 2;
   }
-  const int ntp = (plan->n_tiles + plan->pair - 1) / plan->pair;
+  // CTA pairs (cta_group::2): with channel-tile pairs, groups of FOUR channel tiles per work unit,
+  // two per CTA, the activation tile split between the two SMs -- 16 instead of 24 KiB into an SM
+  // per 128 x 128 x 128 MMA block.  Needs an even grid and a long walk per pair.
+  {
+    const long long units4 = (long long)((plan->n_tiles + 3) / 4) * plan->m_tiles * plan->k_blocks;
+    const int pairs = sm_count / 2;
+    if (plan->pair == 2 && plan->n_tiles >= 4 && pairs >= 1 && units4 >= 8LL * pairs) plan->two_cta = B200_GEMM_TWO_CTA_DEFAULT;
+    const int ft = forced_two();
+    if (ft == 0) plan->two_cta = 0;
+    if (ft == 1 && plan->pair == 2 && plan->n_tiles >= 4 && pairs >= 1 && units4 >= pairs) plan->two_cta = 1;
+  }
+  const int per_unit = plan->pair * (plan->two_cta ? 2 : 1);   // channel tiles per work unit
+  const int ntp = (plan->n_tiles + per_unit - 1) / per_unit;
   const long long T = (long long)ntp * plan->m_tiles * plan->k_blocks;
   if (T >= (1LL << 31)) return 1;
-  // Persistent stream-K: one CTA per SM, equal contiguous ranges of (output unit, K block).
+  // Persistent stream-K: one CTA (or CTA pair) per SM (pair), equal contiguous ranges of (output
+  // unit, K block).
   long long ctas = T < sm_count ? T : sm_count;
+  if (plan->two_cta) {
+    const long long workers = T < sm_count / 2 ? T : sm_count / 2;
+    ctas = 2 * workers;
+  }
   if (ctas < 1) ctas = 1;
   plan->ctas = (int)ctas;
-  const long long per = T / ctas;  // shortest range
-  plan->max_split = (plan->k_blocks == 0 || (T % ctas == 0 && per % plan->k_blocks == 0))
+  const long long workers_ = plan->two_cta ? ctas / 2 : ctas;
+  const long long per = T / workers_;  // shortest range
+  plan->max_split = (plan->k_blocks == 0 || (T % workers_ == 0 && per % plan->k_blocks == 0))
                         ? 1
                         : (int)((plan->k_blocks + per - 1) / (per > 0 ? per : 1) + 1);
   plan->ws_partial_bytes = (size_t)ctas * 2 * plan->pair * tok * kTileN * sizeof(float);
+  if (plan->two_cta) {
+    fill_plan<128, 2, true>(plan);
+    return 0;
+  }
   if (plan->pair == 2) {
     switch (tok) {
       case 16: fill_plan<16, 2>(plan); break;
@@ -846,7 +928,7 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   CUtensorMap tmap;
   const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)M};
   const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
-  const cuuint32_t box[2] = {64u, (cuuint32_t)plan.tok_tile};
+  const cuuint32_t box[2] = {64u, (cuuint32_t)(plan.two_cta ? plan.tok_tile / 2 : plan.tok_tile)};
   const cuuint32_t estr[2] = {1u, 1u};
   CUresult r = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<uint16_t*>(x), dims,
                       strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -862,7 +944,8 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   prm.partials = reinterpret_cast<uint4*>(ws_partials);
   prm.M = M; prm.K = K; prm.N = N; prm.G = G;
   prm.KB = plan.k_blocks; prm.NT = plan.n_tiles; prm.MT = plan.m_tiles;
-  prm.NTP = (plan.n_tiles + plan.pair - 1) / plan.pair;
+  const int per_unit = plan.pair * (plan.two_cta ? 2 : 1);
+  prm.NTP = (plan.n_tiles + per_unit - 1) / per_unit;
   prm.T = prm.NTP * plan.m_tiles * plan.k_blocks;
   prm.P = plan.ctas;
   prm.R = G >= kTileK ? 1 : kTileK / G;
@@ -873,6 +956,7 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   // and lost: the operand with the long reuse distance is the ACTIVATION matrix, re-read once
   // per channel-tile group; 13824 -> 5120 at 2048 tokens fell from 1144 to 932 TFLOP/s.)
   prm.trace = g_trace;
+  if (plan.two_cta) return launch_impl<128, 2, true>(prm, tmap, plan, pdl, stream);
   if (plan.pair == 2) {
     switch (plan.tok_tile) {
       case 16: return launch_impl<16, 2>(prm, tmap, plan, pdl, stream);

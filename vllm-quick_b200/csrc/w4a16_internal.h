@@ -24,7 +24,8 @@ struct GemmPlan {
   int kind;          // GemmKind: tcgen05 kernel or the mma.sync decode kernel
   int tok_tile;      // tokens per MMA tile (tcgen05 N): 16 / 32 / 64 / 128
   int n_tiles;       // ceil(N / 128)
-  int pair;          // tcgen05 kernel: channel tiles per work unit (1 or 2, sharing one activation tile)
+  int pair;          // tcgen05 kernel: channel tiles per CTA and work unit (1 or 2, sharing one activation tile)
+  int two_cta;       // tcgen05 kernel: CTA pairs (cta_group::2), the activation tile split between two SMs
   int m_tiles;       // ceil(M / tok_tile)
   int k_blocks;      // K / 128
   int ctas;          // grid size
