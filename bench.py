@@ -145,6 +145,8 @@ def workload_config(args, model, tp):
         layers = MODELS[model][5] if args.layers is None else args.layers
         what = (f"{model} AWQ W4 g{GROUP} decode step: quantized linear layers (qkv,o,gate_up,down x {layers} "
                 f"layers), batch M={M}, tensor-parallel={tp}")
+        if getattr(args, "layer_ops", False):
+            what += " + the layer's RMSNorms (fused behind the all-reduce) and SiLU-and-multiply (gate_up epilogue)"
     elif args.workload == "gemm1":
         what = f"single QUICK-AWQ W4 g{GROUP} GEMM M={M} K=4096 N=4096 fp16, 64 distinct weight sets per step"
     else:
@@ -347,6 +349,11 @@ def main():
                     help="force GEMM, then the packet all-reduce kernel")
     ap.add_argument("--unfused-allreduce", action="store_true",
                     help="row-parallel GEMM and the one-shot barrier all-reduce as two kernels")
+    ap.add_argument("--layer-ops", action="store_true",
+                    help="decode workload as the whole linear path of a decoder layer: residual add + RMSNorm "
+                         "before qkv / gate_up (fused behind the all-reduce at TP > 1: SURVEY 8f-1), SiLU-and-"
+                         "multiply in the gate_up epilogue (8f-2), real data flowing o_proj -> norm -> gate_up "
+                         "-> down_proj -> norm; same metric (algorithmic bytes of the GEMMs)")
     ap.add_argument("--nccl-allreduce", action="store_true",
                     help="row-parallel all-reduce through NCCL instead of the NVLink peer-memory kernels")
     args = ap.parse_args()
@@ -439,6 +446,35 @@ def main():
                     inp = x_in if K == hidden and not row else xs[K]
                     out, _ = layer(inp)          # row-parallel layers all-reduce inside
             return out
+
+        if args.layer_ops:
+            # ---- the layer as models/llama.py:205-222 + :76-80 run it on this library: two RMSNorms
+            # (weights = ones), row-parallel layers WITHOUT their own all-reduce feeding
+            # RMSNorm.forward_reduced (all-reduce + residual add + norm in one kernel at TP > 1),
+            # gate_up with the activation in its epilogue.  Attention stays a stand-in (fixed o_proj
+            # input of the right per-rank shape); everything else is real data flow.
+            norms = []
+            for lyr in layers:
+                lyr[1].reduce_results = False
+                lyr[3].reduce_results = False
+                norms.append((pkg.RMSNorm(hidden).to(dev).half(), pkg.RMSNorm(hidden).to(dev).half()))
+            for lyr in layers:                  # channel-pair the gate_up weights once, before any capture
+                lyr[2].forward_silu_and_mul(xs[hidden])
+            residual0 = torch.randn((M, hidden), device=dev, generator=g).half()
+
+            def step(x_in):                     # noqa: F811
+                residual = residual0.clone()
+                h = x_in.clone()
+                for lyr, (n_in, n_post) in zip(layers, norms):
+                    h, residual = n_in(h, residual)                      # input_layernorm
+                    lyr[0](h)                                            # qkv_proj (attention: stand-in below)
+                    o_partial, _ = lyr[1](xs[shapes[1][1]])              # o_proj on this rank's K shard
+                    h, residual = n_post.forward_reduced(o_partial, residual)   # all-reduce + add + norm
+                    act = lyr[2].forward_silu_and_mul(h)                 # gate_up + SiLU-and-multiply
+                    h, _ = lyr[3](act)                                   # down_proj (partial sums at TP > 1)
+                    if tp > 1:                                           # reduced by the NEXT layer's norm in a model;
+                        h = pu.tensor_model_parallel_all_reduce(h)       # here: the packet all-reduce
+                return h
     else:
         # ---- plain GEMM lists through the operator (ops.quick_gemm), rotating weight sets
         work = []
@@ -474,6 +510,9 @@ def main():
         fused_ar = decode and world > 1 and pu.custom_all_reduce.fused_handle(M, MODELS[model][0], GROUP) is not None
         ar_launches = 2 * gemms[0][5] if (decode and world > 1 and pu.custom_all_reduce.is_initialized()
                                           and not fused_ar) else 0
+        if decode and args.layer_ops:        # two norm kernels per layer (+ the packet all-reduce at TP > 1)
+            fused_ar = False
+            ar_launches = (2 + (1 if world > 1 else 0)) * gemms[0][5]
 
         def barrier():
             torch.cuda.synchronize(dev)
@@ -513,7 +552,35 @@ def main():
 
         # ---- parity of what was just timed (after the timed regions; not part of them)
         parity = {"ok": True, "max_rel": 0.0, "checks": []}
-        if decode:
+        if decode and args.layer_ops:
+            # the fused step against the same layers run op by op (separate all-reduce, norm and
+            # activation kernels): the library's own unfused path, bit-identical by construction
+            def unfused(x_in):
+                residual = residual0.clone()
+                h = x_in.clone()
+                for lyr, (n_in, n_post) in zip(layers[:2], norms[:2]):
+                    h, residual = n_in(h, residual)
+                    o_partial, _ = lyr[1](xs[shapes[1][1]])
+                    o_full = pu.tensor_model_parallel_all_reduce(o_partial) if tp > 1 else o_partial
+                    h, residual = n_post(o_full.clone(), residual)
+                    w = lyr[2].linear_weights
+                    full = pkg.ops.quick_gemm(h, w["qweight"].data, w["scales"].data, w["qzeros"].data, 8)
+                    act = torch.empty((M, full.shape[1] // 2), dtype=torch.float16, device=dev)
+                    pkg.ops.silu_and_mul_paired(act, full)
+                    h, _ = lyr[3](act)
+                    if tp > 1:
+                        h = pu.tensor_model_parallel_all_reduce(h)
+                return h
+            keep = layers, norms
+            layers, norms = layers[:2], norms[:2]
+            got2 = step(x_dev)
+            layers, norms = keep
+            want2 = unfused(x_dev)
+            d = (got2.float() - want2.float()).abs() / want2.float().abs().clamp_min(1.0)
+            parity["checks"].append({"what": "two decoder layers, fused ops (benchmarked path) vs the same layers "
+                                             "op by op (separate all-reduce / norm / activation kernels)",
+                                     "max_rel": float(d.max()), "finite": bool(torch.isfinite(got2).all())})
+        elif decode:
             for i, ((name, K, N, row), layer) in enumerate(zip(shapes, layers[0])):
                 w = layer.linear_weights
                 inp = xs[K]
@@ -584,7 +651,10 @@ def main():
             "config": workload_config(args, model, tp),
             "tokens_per_s": M / (ms_step * 1e-3) * (1 if decode else world),
             "gpu_launches": (launches_per_step + ar_launches) * args.steps,
+            "layer_ops": bool(decode and args.layer_ops),
             "allreduce": None if not (decode and world > 1) else (
+                "o_proj: all-reduce + residual add + RMSNorm in one kernel (packets); down_proj: packet kernel"
+                if args.layer_ops and pu.custom_all_reduce.is_initialized() else
                 "fused into the row-parallel GEMM, packet exchange (b200_w4a16_gemm_allreduce)" if fused_ar else
                 ("nvlink packet kernel after the GEMM (b200_w4a16_allreduce_ll)"
                  if pu.custom_all_reduce._handle.use_ll else
