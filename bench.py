@@ -238,8 +238,8 @@ def kernel_name(pkg, M, K, N):
     plan = pkg._lib.gemm_plan(M, K, N)
     if plan["variant"] == "decode":
         return f"w4a16_decode_kernel<{plan['tok_tile'] // 8}>"
-    ut = plan["unit_tiles"]
-    return f"w4a16_gemm_kernel<{plan['tok_tile']}, {min(ut, 2)}, {'true' if ut == 4 else 'false'}>"
+    two = plan["cta_pair"]
+    return f"w4a16_gemm_kernel<{plan['tok_tile']}, {plan['unit_tiles'] // (2 if two else 1)}, {'true' if two else 'false'}>"
 
 
 def rand_awq(torch, dev, g, K, N):
@@ -318,6 +318,10 @@ def run_extras(torch, pkg, dev, peaks):
         gem = [(n, M, K, N, 8) for (n, K, N, _) in layer_shapes("llama2-7b", 1)]
         r = bench_gemm_list(torch, pkg, dev, gem)
         out[f"config2_llama2-7b_layer_M{M}"] = {**r, "hbm_frac": r["GBps"] / peaks["hbm"]}
+    for M in (1, 8):        # the default workload's model at the other decode batch sizes (M = 16 is the headline)
+        gem = [(n, M, K, N, 2) for (n, K, N, _) in layer_shapes("llama2-70b", 1)]
+        r = bench_gemm_list(torch, pkg, dev, gem)
+        out[f"config4_llama2-70b_layer_M{M}"] = {**r, "hbm_frac": r["GBps"] / peaks["hbm"]}
     for M in (512, 2048, 8192):
         gem = [(n, M, K, N, 2) for (n, K, N, _) in layer_shapes("llama2-13b", 1)]
         r = bench_gemm_list(torch, pkg, dev, gem, iters=4, warm=2)

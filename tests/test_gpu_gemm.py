@@ -193,6 +193,28 @@ def test_cuda_graph_capture(pkg, oracle, cuda_lib):
     assert torch.isfinite(out2).all()
 
 
+def test_cuda_graph_capture_of_cta_pair_launch(pkg, oracle, cuda_lib):
+    """The 128-token kernel on CTA pairs is a cluster launch (cudaLaunchAttributeClusterDimension +
+    programmatic stream serialization): it must capture into a CUDA graph and replay like the others."""
+    M, K, N = 300, 5120, 37 * 128
+    assert cuda_lib.b200_w4a16_gemm_cta_pair(M, K, N, 128) == 1
+    x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, 128, seed=77, n_words=8, edge_words=2)
+    r = pkg.ops.quick_repack(qw)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        eager = pkg.ops.quick_gemm(x, r, s, qz, 8)
+        st.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=st):
+            out = pkg.ops.quick_gemm(x, r, s, qz, 8)
+            out2 = pkg.ops.quick_gemm(x, r, s, qz, 8)          # back to back: programmatic dependent launch
+        for _ in range(3):
+            graph.replay()
+        st.synchronize()
+    assert torch.equal(out, eager) and torch.equal(out2, eager)
+    gemm_check(out[:, cols], Yf, TOL, (M, K, N))
+
+
 # ---- the exact shapes the driver-run benchmarks use (stream-K segment boundaries depend on
 # (channel tiles, K blocks, 148): every new shape is a new split pattern)
 LLAMA70B_TP = {  # per-rank (K, N) of qkv / o / gate_up / down, vLLM sharding (linear.py:312-552)

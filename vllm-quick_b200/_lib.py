@@ -37,7 +37,7 @@ REPACK_AWQ_TO_B200, REPACK_B200_TO_AWQ = 0, 1
 EXPORTS = (
     "b200_w4a16_version", "b200_w4a16_strerror", "b200_w4a16_last_cuda_error",
     "b200_w4a16_repacked_words", "b200_w4a16_workspace_bytes", "b200_w4a16_gemm",
-    "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan", "b200_w4a16_gemm_variant", "b200_w4a16_gemm_unit_tiles",
+    "b200_w4a16_dequant", "b200_w4a16_repack", "b200_w4a16_gemm_plan", "b200_w4a16_gemm_variant", "b200_w4a16_gemm_unit_tiles", "b200_w4a16_gemm_cta_pair",
     "b200_w4a16_ar_region_bytes", "b200_w4a16_ar_alloc", "b200_w4a16_ar_free",
     "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
     "b200_w4a16_allreduce", "b200_w4a16_allreduce_twoshot", "b200_w4a16_gemm_allreduce", "b200_w4a16_gemm_gated",
@@ -116,6 +116,8 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_gemm_variant.argtypes = [i32, i32, i32, i32]
     L.b200_w4a16_gemm_unit_tiles.restype = i32
     L.b200_w4a16_gemm_unit_tiles.argtypes = [i32, i32, i32, i32]
+    L.b200_w4a16_gemm_cta_pair.restype = i32
+    L.b200_w4a16_gemm_cta_pair.argtypes = [i32, i32, i32, i32]
     f32 = ctypes.c_float
     L.b200_w4a16_moe_gather.restype = i32
     L.b200_w4a16_moe_gather.argtypes = [vp, vp, vp, sz, i32, vp]
@@ -163,4 +165,5 @@ def gemm_plan(M: int, K: int, N: int, G: int = 128, split_k_hint: int = 0) -> di
     return {"tok_tile": tok.value, "split_k": split.value, "grid": grid.value,
             "smem_bytes": smem.value,
             "variant": {0: "tcgen05", 1: "decode"}.get(variant, str(variant)),
-            "unit_tiles": lib().b200_w4a16_gemm_unit_tiles(M, K, N, G)}
+            "unit_tiles": lib().b200_w4a16_gemm_unit_tiles(M, K, N, G),
+            "cta_pair": bool(lib().b200_w4a16_gemm_cta_pair(M, K, N, G))}

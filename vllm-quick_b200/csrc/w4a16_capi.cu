@@ -165,6 +165,14 @@ int b200_w4a16_gemm_unit_tiles(int M, int K, int N, int G) {
   return plan.pair * (plan.two_cta ? 2 : 1);
 }
 
+int b200_w4a16_gemm_cta_pair(int M, int K, int N, int G) {
+  if (!gemm_shape_ok(M, K, N, G)) return -B200_ERR_BAD_SHAPE;
+  b200::GemmPlan plan;
+  if (b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, 0, sm_count_or_default(), &plan))
+    return -B200_ERR_BAD_SHAPE;
+  return plan.two_cta ? 1 : 0;
+}
+
 int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
                     const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G, int layout,
                     int split_k_hint, void* workspace, size_t workspace_bytes,

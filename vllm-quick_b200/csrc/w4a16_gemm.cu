@@ -875,9 +875,16 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
     const long long units4 = (long long)((plan->n_tiles + 3) / 4) * plan->m_tiles * plan->k_blocks;
     const int pairs = sm_count / 2;
     if (plan->pair == 2 && plan->n_tiles >= 4 && pairs >= 1 && units4 >= 8LL * pairs) plan->two_cta = B200_GEMM_TWO_CTA_DEFAULT;
+    // Short K and not too many token tiles: ONE channel tile per CTA of the pair -- two accumulator
+    // sets again (a pair's drain stall is paid once per output unit, i.e. per K / 128 steps), finer
+    // work units; +8-27 % at 512-2048 tokens on the K = 5120 layers, a loss at K = 13824 and at
+    // 8192 tokens (profiles/r3c_kb_pair{1,2}_two.jsonl).
+    if (plan->two_cta && plan->k_blocks < 64 && plan->m_tiles <= 32) plan->pair = 1;
     const int ft = forced_two();
     if (ft == 0) plan->two_cta = 0;
     if (ft == 1 && plan->pair == 2 && plan->n_tiles >= 4 && pairs >= 1 && units4 >= pairs) plan->two_cta = 1;
+    // tuning: CTA pairs with ONE channel tile per CTA (two accumulator sets again)
+    if (ft == 1 && tok == 128 && plan->pair == 1 && plan->n_tiles >= 2 && pairs >= 1) plan->two_cta = 1;
   }
   const int per_unit = plan->pair * (plan->two_cta ? 2 : 1);   // channel tiles per work unit
   const int ntp = (plan->n_tiles + per_unit - 1) / per_unit;
@@ -899,7 +906,7 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
                         : (int)((plan->k_blocks + per - 1) / (per > 0 ? per : 1) + 1);
   plan->ws_partial_bytes = (size_t)ctas * 2 * plan->pair * tok * kTileN * sizeof(float);
   if (plan->two_cta) {
-    fill_plan<128, 2, true>(plan);
+    if (plan->pair == 2) fill_plan<128, 2, true>(plan); else fill_plan<128, 1, true>(plan);
     return 0;
   }
   if (plan->pair == 2) {
@@ -956,7 +963,10 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   // and lost: the operand with the long reuse distance is the ACTIVATION matrix, re-read once
   // per channel-tile group; 13824 -> 5120 at 2048 tokens fell from 1144 to 932 TFLOP/s.)
   prm.trace = g_trace;
-  if (plan.two_cta) return launch_impl<128, 2, true>(prm, tmap, plan, pdl, stream);
+  if (plan.two_cta) {
+    if (plan.pair == 2) return launch_impl<128, 2, true>(prm, tmap, plan, pdl, stream);
+    return launch_impl<128, 1, true>(prm, tmap, plan, pdl, stream);
+  }
   if (plan.pair == 2) {
     switch (plan.tok_tile) {
       case 16: return launch_impl<16, 2>(prm, tmap, plan, pdl, stream);
