@@ -24,8 +24,9 @@
 //  * the group scale is applied to the fp32 group accumulator (one FFMA per accumulator per
 //    128 rows) instead of to every weight: (q - z) stays exact, the GEMM result differs from
 //    fp16-rounded-W arithmetic by < 2^-11 relative per term (tolerance 1e-2, test_gpu_gemm).
-//  * one persistent CTA per SM; under programmatic dependent launch the next kernel's CTAs
-//    prefetch their whole weight ring while this kernel's tail (fix-up, exchange) drains.
+//  * one persistent CTA per SM: four consumer groups of four warps (one tile in flight each) and
+//    four producer warps; under programmatic dependent launch the next kernel's CTAs prefetch
+//    their whole weight ring while this kernel's tail (fix-up, exchange) drains.
 //  * row-parallel fusion (ar.world > 1): finished fp16 tiles go to every rank as 16-byte
 //    packets {data, epoch, data, epoch} -- the receiver polls the packets themselves.
 #include "w4a16_common.cuh"

@@ -15,10 +15,19 @@
 //    recycled when the MMAs that read them have completed.  (One shared ring of 5 x 41 KiB
 //    stages starved the tensor pipe at 128 tokens: 852 cycles per tile where the MMAs need 512,
 //    profiles/r2j_trace_prefill_m2048_5120x15360.txt.)
-//  * PAIR = 2 (large problems): a CTA works on TWO adjacent channel tiles per activation tile --
-//    256 channels x MTOK tokens per K block -- so an activation tile is fetched from L2 once
-//    per two weight tiles: 24 instead of 40 KiB of L2 -> SM traffic per 128 x 128 x 128 MMA
-//    block at MTOK = 128 (the old kernel moved 10 TB/s out of L2 at 1.0 PFLOP/s).
+//  * PAIR = 2 (128-token tiles, long K): a CTA works on TWO adjacent channel tiles per activation
+//    tile -- 256 channels x 128 tokens per K block -- so an activation tile is fetched from L2 once
+//    per two weight tiles (24 instead of 40 KiB of L2 -> SM traffic per 128 x 128 x 128 MMA block).
+//  * TWO (128-token tiles): CTA pairs.  The two CTAs of a cluster (the SMs of one TPC) walk the same
+//    (token tile, K block) steps on different channel tiles; the leader's MMA thread issues
+//    tcgen05.mma.cta_group::2 (M = 256) for both, each CTA holds HALF of the activation tile in its
+//    shared memory (2-SM TMA loads counted on the leader's barrier), dequantizes its own weight tiles
+//    into its own TMEM and signals the leader's operand barrier remotely; commits are multicast to
+//    both CTAs' barriers.  With short K each CTA of a pair takes ONE channel tile (two accumulator
+//    sets), with long K two (one set, drained half by half).
+//  * one tcgen05.commit per weight tile at 128 tokens: the commit frees the tile's TMEM operand
+//    buffer, and the operand ring -- dequant latency + MMAs up to the commit -- not memory, paced
+//    the kernel at 650-670 cycles per tile with one commit per two tiles; 592 now (MMAs need 512).
 //  * four dequant warpgroups take weight tiles round-robin.  A thread reads one 16-byte word
 //    group (bank-conflict free), expands it in registers with the reference's exact lop3 / sub /
 //    fma sequence, and writes the fp16 pairs straight into TENSOR MEMORY with tcgen05.st:
