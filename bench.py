@@ -239,7 +239,8 @@ def kernel_name(pkg, M, K, N):
     if plan["variant"] == "decode":
         return f"w4a16_decode_kernel<{plan['tok_tile'] // 8}>"
     two = plan["cta_pair"]
-    return f"w4a16_gemm_kernel<{plan['tok_tile']}, {plan['unit_tiles'] // (2 if two else 1)}, {'true' if two else 'false'}>"
+    return (f"w4a16_gemm_kernel<{plan['tok_tile']}, {plan['unit_tiles'] // (2 if two else 1)}, "
+            f"{'true' if two else 'false'}, {plan['token_tiles']}>")
 
 
 def rand_awq(torch, dev, g, K, N):

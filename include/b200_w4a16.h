@@ -147,8 +147,9 @@ int b200_w4a16_gemm_variant(int M, int K, int N, int G);
  * with 128-token tiles).  Always 1 for B200_VARIANT_DECODE.  Negative: -b200_status_t. */
 int b200_w4a16_gemm_unit_tiles(int M, int K, int N, int G);
 
-/* Introspection: 1 when the tcgen05 kernel runs this problem on CTA pairs (clusters of two CTAs
- * issuing tcgen05.mma.cta_group::2, the activation tile split between the two SMs), else 0. */
+/* Introspection: 0 = single CTAs; 1 = the tcgen05 kernel runs this problem on CTA pairs (clusters
+ * of two CTAs issuing tcgen05.mma.cta_group::2, the activation tile split between the two SMs);
+ * 2 = CTA pairs whose work units span two 128-token tiles (one dequantized weight tile feeds both). */
 int b200_w4a16_gemm_cta_pair(int M, int K, int N, int G);
 
 /* ---- NVLink peer-memory all-reduce for the row-parallel linears --------------------------

@@ -197,7 +197,7 @@ def test_cuda_graph_capture_of_cta_pair_launch(pkg, oracle, cuda_lib):
     """The 128-token kernel on CTA pairs is a cluster launch (cudaLaunchAttributeClusterDimension +
     programmatic stream serialization): it must capture into a CUDA graph and replay like the others."""
     M, K, N = 300, 5120, 37 * 128
-    assert cuda_lib.b200_w4a16_gemm_cta_pair(M, K, N, 128) == 1
+    assert cuda_lib.b200_w4a16_gemm_cta_pair(M, K, N, 128) >= 1
     x, qw, s, qz, cols, Yf = sampled_case(oracle, M, K, N, 128, seed=77, n_words=8, edge_words=2)
     r = pkg.ops.quick_repack(qw)
     st = torch.cuda.Stream()
@@ -272,6 +272,8 @@ def test_gemm_mid_batches(pkg, oracle, cuda_lib, M, K, N):
     (130, 16384, 11 * 128 + 64, 128), # ragged last tile
     (520, 2048, 4096, 64),            # G < 128: two (scale, zero) rows per weight tile
     (200, 8192, 2560, 32),            # G = 32: four rows per tile
+    (4100, 8192, 2560, 128),          # token-tile pairs with an odd token-tile count (33): phantom token tile
+    (4096, 5120, 64 * 128, 128),      # token-tile pairs, wide layer
 ])
 def test_gemm_channel_tile_pairs(pkg, oracle, cuda_lib, M, K, N, G):
     """Work units of two channel tiles per CTA (one activation tile feeds both) and of four per

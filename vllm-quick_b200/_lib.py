@@ -166,4 +166,5 @@ def gemm_plan(M: int, K: int, N: int, G: int = 128, split_k_hint: int = 0) -> di
             "smem_bytes": smem.value,
             "variant": {0: "tcgen05", 1: "decode"}.get(variant, str(variant)),
             "unit_tiles": lib().b200_w4a16_gemm_unit_tiles(M, K, N, G),
-            "cta_pair": bool(lib().b200_w4a16_gemm_cta_pair(M, K, N, G))}
+            "cta_pair": lib().b200_w4a16_gemm_cta_pair(M, K, N, G) > 0,
+            "token_tiles": max(1, lib().b200_w4a16_gemm_cta_pair(M, K, N, G))}

@@ -170,7 +170,7 @@ int b200_w4a16_gemm_cta_pair(int M, int K, int N, int G) {
   b200::GemmPlan plan;
   if (b200::make_gemm_plan(M > 0 ? M : 1, K, N, G, 0, sm_count_or_default(), &plan))
     return -B200_ERR_BAD_SHAPE;
-  return plan.two_cta ? 1 : 0;
+  return plan.two_cta ? plan.tok_pair : 0;
 }
 
 int b200_w4a16_gemm(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,

@@ -28,6 +28,9 @@
 //  * one tcgen05.commit per weight tile at 128 tokens: the commit frees the tile's TMEM operand
 //    buffer, and the operand ring -- dequant latency + MMAs up to the commit -- not memory, paced
 //    the kernel at 650-670 cycles per tile with one commit per two tiles; 592 now (MMAs need 512).
+//  * TP = 2 (CTA pairs, >= 32 token tiles): one dequantized weight tile in TMEM feeds the MMAs of
+//    two 128-token tiles -- half the dequant work and weight bytes per flop; steady state = the
+//    tensor pipe (513 cycles per 128 x 128 x 128 block).
 //  * four dequant warpgroups take weight tiles round-robin.  A thread reads one 16-byte word
 //    group (bank-conflict free), expands it in registers with the reference's exact lop3 / sub /
 //    fma sequence, and writes the fp16 pairs straight into TENSOR MEMORY with tcgen05.st:
@@ -103,25 +106,29 @@ struct IntC { static constexpr int value = V; };
 
 // TWO: a pair of CTAs (cluster of 2 on one TPC) issues tcgen05.mma.cta_group::2 -- each CTA holds its
 // own channel tiles (A, D) and HALF of the activation tile (MTOK / 2 tokens) in shared memory.
-template <int MTOK, int PAIR, bool TWO = false>
+// TP: token tiles per work unit (1 or 2): with 2, ONE dequantized weight tile in TMEM feeds the MMAs
+// of two 128-token tiles -- half the dequant work and half the weight bytes per flop.
+template <int MTOK, int PAIR, bool TWO = false, int TP = 1>
 struct Cfg {
   // accumulators: PAIR per buffer set; two sets (drain overlaps the next tile's MMAs) unless
   // 2 x 128 columns per set leave no room (MTOK = 128, PAIR = 2: one set, drained half by half)
-  static constexpr int kAccBufs = (MTOK * PAIR > 128) ? 1 : 2;
-  static constexpr int kAccCols = kAccBufs * PAIR * MTOK;
+  static constexpr int kAccSlots = PAIR * TP;          // accumulators per set: (channel tile, token tile)
+  static constexpr int kAccBufs = (MTOK * kAccSlots > 128) ? 1 : 2;
+  static constexpr int kAccCols = kAccBufs * kAccSlots * MTOK;
   // dequantized-operand ring in TMEM: what the accumulators leave, at most 6, even
   static constexpr int kABufsFit = (kTmemCols - kAccCols) / kTmemACols;
   static constexpr int kABufs = kABufsFit >= 6 ? 6 : 4;
   static constexpr int kDCol = kABufs * kTmemACols;    // accumulators start here
   // activation ring
   static constexpr int kXRows = TWO ? MTOK / 2 : MTOK; // token rows of the activation tile in THIS CTA
-  static constexpr int kXBytes = kXRows * 256;         // two swizzle atoms of [kXRows x 64] fp16
-  static constexpr int kXStages = TWO ? 6 : MTOK >= 128 ? 4 : MTOK == 64 ? B200_XST64 : B200_XST32;
+  static constexpr int kXTileBytes = kXRows * 256;     // two swizzle atoms of [kXRows x 64] fp16
+  static constexpr int kXBytes = kXTileBytes * TP;      // one stage: the unit's TP token tiles
+  static constexpr int kXStages = TWO ? (TP == 2 ? 4 : 6) : MTOK >= 128 ? 4 : MTOK == 64 ? B200_XST64 : B200_XST32;
   // weight ring: [8 KiB tile | 4 x 256 B scale rows | 4 x 64 B zero rows]
   static constexpr int kSOff = kTileWords * 4;
   static constexpr int kZOff = kSOff + kScaleRowsMax * 256;
   static constexpr int kWStageBytes = kZOff + kScaleRowsMax * 64;            // 9472
-  static constexpr int kWStages = TWO ? 12 : MTOK >= 128 ? 8 : MTOK == 64 ? B200_WST64 : B200_WST32;
+  static constexpr int kWStages = TWO ? (TP == 2 ? 8 : 12) : MTOK >= 128 ? 8 : MTOK == 64 ? B200_WST64 : B200_WST32;
   static constexpr int kBarBytes = 1024;
   static constexpr int kXOff = kBarBytes;                                    // 1024-aligned
   static constexpr int kWOff = kXOff + kXStages * kXBytes;
@@ -140,7 +147,7 @@ struct Cfg {
   // activation producer (stage reuse) and the dequant groups (operand-buffer reuse) wait on it.
   static constexpr int kRingTiles = kXStages * PAIR > kABufs ? kXStages * PAIR : kABufs;
   static constexpr int kDoneBars = kRingTiles / kCommit + 2;
-  static constexpr int kNumBars = 2 * kWStages + kXStages + kDoneBars + kABufs + kAccBufs + kAccBufs * PAIR;
+  static constexpr int kNumBars = 2 * kWStages + kXStages + kDoneBars + kABufs + kAccBufs + kAccBufs * kAccSlots;
   // A dequant group waits for the MMAs of tile w - kABufs before it looks at tile w's stage:
   // with kWStages >= kABufs the stage's previous tenant (tile w - kWStages) has then been
   // dequantized, i.e. had landed -- the parity wait cannot pass on a stale phase.
@@ -212,10 +219,11 @@ __device__ __forceinline__ Owned find_owned(const Walk& walk, int KB, int P, int
   return r;
 }
 
-template <int MTOK, int PAIR, bool TWO>
+template <int MTOK, int PAIR, bool TWO, int TP>
 __global__ void __launch_bounds__(kThreads, 1)
 w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
-  using C = Cfg<MTOK, PAIR, TWO>;
+  using C = Cfg<MTOK, PAIR, TWO, TP>;
+  constexpr int kAS = C::kAccSlots;
   // CTA pair: rank in the cluster (0 = leader: issues the MMAs, owns the barriers their issuer waits
   // on); the work space is cut per PAIR of CTAs, both walk the same (token tile, K block) steps
   const uint32_t crank = TWO ? cluster_ctarank() : 0u;
@@ -233,7 +241,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   const uint32_t bar_done = bar_xfull + 8 * C::kXStages;         // [kDoneBars] MMAs of kCommit weight tiles done
   const uint32_t bar_afull = bar_done + 8 * C::kDoneBars;        // [kABufs]    operand dequantized
   const uint32_t bar_dfull = bar_afull + 8 * C::kABufs;          // [kAccBufs]  accumulator set complete
-  const uint32_t bar_dempty = bar_dfull + 8 * C::kAccBufs;       // [kAccBufs * PAIR] accumulator drained
+  const uint32_t bar_dempty = bar_dfull + 8 * C::kAccBufs;       // [kAccBufs * kAccSlots] accumulator drained
   const uint32_t tmem_slot = smem_base + 8 * C::kNumBars;
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(
       smem_gen + (tmem_slot - smem_base));
@@ -402,7 +410,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
         walk.seg(idx, t0, n);
         const int o = t0 / p.KB;
         int k0 = (t0 - o * p.KB) * kTileK;
-        const int m0 = (o % p.MT) * MTOK + (TWO ? (int)crank * C::kXRows : 0);   // pair: this CTA's token half
+        const int m0 = (o % p.MT) * (TP * MTOK) + (TWO ? (int)crank * C::kXRows : 0);   // pair: this CTA's token half
         for (int i = 0; i < n; ++i, ++u, k0 += kTileK) {
           if (u >= C::kXStages) {
             const int g = ((u - C::kXStages) * PAIR + PAIR - 1) / C::kCommit;
@@ -410,12 +418,18 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           }
           if (TWO) {                                          // both halves are counted on the leader's barrier
             if (crank == 0) mbar_arrive_expect_tx(bar, 2u * (uint32_t)C::kXBytes);
-            tma_load_2d_pair(sb, &tmap_x, k0, m0, bar);
-            tma_load_2d_pair(sb + C::kXRows * 128, &tmap_x, k0 + 64, m0, bar);
+#pragma unroll
+            for (int t = 0; t < TP; ++t) {
+              tma_load_2d_pair(sb + t * C::kXTileBytes, &tmap_x, k0, m0 + t * MTOK, bar);
+              tma_load_2d_pair(sb + t * C::kXTileBytes + C::kXRows * 128, &tmap_x, k0 + 64, m0 + t * MTOK, bar);
+            }
           } else {
             mbar_arrive_expect_tx(bar, (uint32_t)C::kXBytes);
-            tma_load_2d(sb, &tmap_x, k0, m0, bar);
-            tma_load_2d(sb + C::kXRows * 128, &tmap_x, k0 + 64, m0, bar);
+#pragma unroll
+            for (int t = 0; t < TP; ++t) {
+              tma_load_2d(sb + t * C::kXTileBytes, &tmap_x, k0, m0 + t * MTOK, bar);
+              tma_load_2d(sb + t * C::kXTileBytes + C::kXRows * 128, &tmap_x, k0 + 64, m0 + t * MTOK, bar);
+            }
           }
           sb += C::kXBytes;
           bar += 8;
@@ -449,26 +463,30 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           const uint64_t bd = bdesc0 + x_off;
 #pragma unroll
           for (int h = 0; h < PAIR; ++h) {
-            if (i == 0) {                                         // first touch of accumulator (d, h):
-              mbar_wait(bar_dempty + 8 * (d * PAIR + h), dpar);   // drained by the epilogue warps
+            if (i == 0) {                                         // first touch of accumulators (d, h, *):
+#pragma unroll
+              for (int t = 0; t < TP; ++t) mbar_wait(bar_dempty + 8 * ((d * PAIR + h) * TP + t), dpar);   // drained by the epilogue warps
               tc_fence_after();
             }
             if (!a_ready) mbar_wait(bar_afull + 8 * buf, aphase);
             tc_fence_after();
             TR(4, w);
             const uint32_t acol = tmem + buf * kTmemACols;
-            const uint32_t dcol = tmem + C::kDCol + (d * PAIR + h) * MTOK;
+            const uint32_t dcol0 = tmem + C::kDCol + (d * PAIR + h) * TP * MTOK;
             // ring positions of the next weight tile, and an early look at its operand barrier
             int nbuf = buf + 1;
             uint32_t nphase = aphase;
             if (nbuf == C::kABufs) { nbuf = 0; nphase ^= 1u; }
             a_ready = w + 1 < n_w && mbar_try_wait(bar_afull + 8 * nbuf, nphase);
 #pragma unroll
-            for (int kk = 0; kk < 8; ++kk) {
-              const uint64_t bk = bd + (uint32_t)((kk >> 2) * (C::kXRows * 128 / 16) + (kk & 3) * 2);
-              if (TWO) tc_mma_ts_pair(dcol, acol + kk * 8, bk, idesc, (uint32_t)((i | kk) != 0));
-              else tc_mma_ts(dcol, acol + kk * 8, bk, idesc, (uint32_t)((i | kk) != 0));
-            }
+            for (int t = 0; t < TP; ++t)                          // the operand buffer feeds every token tile of the unit
+#pragma unroll
+              for (int kk = 0; kk < 8; ++kk) {
+                const uint64_t bk = bd + (uint32_t)(t * (C::kXTileBytes / 16) + (kk >> 2) * (C::kXRows * 128 / 16) + (kk & 3) * 2);
+                const uint32_t dcol = dcol0 + t * MTOK;
+                if (TWO) tc_mma_ts_pair(dcol, acol + kk * 8, bk, idesc, (uint32_t)((i | kk) != 0));
+                else tc_mma_ts(dcol, acol + kk * 8, bk, idesc, (uint32_t)((i | kk) != 0));
+              }
             ++w;
             if ((w & (C::kCommit - 1)) == 0 || w == n_w) {
               if (TWO) tc_commit_pair(bar_done + 8 * done_slot); else tc_commit(bar_done + 8 * done_slot);
@@ -566,17 +584,18 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       const int ntp = o / p.MT, mt = o - ntp * p.MT;
       const int d = idx % C::kAccBufs;
       const bool whole = (n == p.KB);
-      const int m0 = mt * MTOK;
       const int slot = idx == 0 ? 0 : 1;
       mbar_wait(bar_dfull + 8 * d, (uint32_t)(idx / C::kAccBufs) & 1u);
       tc_fence_after();
       if (et == 0) TR(6, 2 * idx);
 #pragma unroll 1
-      for (int h = 0; h < PAIR; ++h) {
+      for (int a = 0; a < kAS; ++a) {                         // accumulator a = (channel tile h, token tile t)
+        const int h = a / TP, t = a % TP;
+        const int m0 = (mt * TP + t) * MTOK;
         const int n_glob = ((TWO ? ntp * 2 + (int)crank : ntp) * PAIR + h) * kTileN + c;
         // partial layout: quad v of channel c holds tokens 4 v .. 4 v + 3 -> [v][c], coalesced
-        uint4* part = p.partials + (((size_t)blockIdx.x * 2 + slot) * PAIR + h) * kPartVec + c;
-        const uint32_t dbase = tmem + lane_base + C::kDCol + (d * PAIR + h) * MTOK;
+        uint4* part = p.partials + (((size_t)blockIdx.x * 2 + slot) * kAS + a) * kPartVec + c;
+        const uint32_t dbase = tmem + lane_base + C::kDCol + (d * kAS + a) * MTOK;
 #pragma unroll 1
         for (int cc = 0; cc < MTOK; cc += 16) {
           uint32_t v[16];
@@ -601,8 +620,8 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           }
         }
         tc_fence_before();
-        if (TWO && crank != 0) mbar_arrive_cluster(map_to_cta(bar_dempty + 8 * (d * PAIR + h), 0));
-        else mbar_arrive(bar_dempty + 8 * (d * PAIR + h));
+        if (TWO && crank != 0) mbar_arrive_cluster(map_to_cta(bar_dempty + 8 * (d * kAS + a), 0));
+        else mbar_arrive(bar_dempty + 8 * (d * kAS + a));
       }
       if (et == 0) TR(6, 2 * idx + 1);
     }
@@ -621,9 +640,8 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     if (own.o >= 0) {
       asm volatile("griddepcontrol.wait;" ::: "memory");      // the dequant warps write y here
       constexpr int kPartVec = MTOK * kTileN / 4;
-      constexpr int kQuads = PAIR * kPartVec;
+      constexpr int kQuads = kAS * kPartVec;
       const int ntp = own.o / p.MT, mt = own.o - ntp * p.MT;
-      const int m0 = mt * MTOK;
       const int nother = own.last - vblock;
       constexpr int kStep = TWO ? 2 : 1;                      // pair: the same-rank CTA of the next pair
       uint4* const mine = p.partials + ((size_t)blockIdx.x * 2 + own.slot) * kQuads;
@@ -679,9 +697,10 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
           for (int i = 0; i < KQ; ++i) {
             const int qd = q0 + i * kFixThreads;
             if (qd < kQuads) {
-              const int h = qd / kPartVec, r = qd % kPartVec;
+              const int a = qd / kPartVec, r = qd % kPartVec;
+              const int h = a / TP, t = a % TP;
               const int n_glob = ((TWO ? ntp * 2 + (int)crank : ntp) * PAIR + h) * kTileN + (r % kTileN);
-              const int m = m0 + 4 * (r / kTileN);
+              const int m = (mt * TP + t) * MTOK + 4 * (r / kTileN);
               if (n_glob < p.N) {
                 const float rr[4] = {acc[i].x, acc[i].y, acc[i].z, acc[i].w};
 #pragma unroll
@@ -729,7 +748,7 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-template <int MTOK, int PAIR, bool TWO = false>
+template <int MTOK, int PAIR, bool TWO = false, int TP = 1>
 int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& plan, bool pdl,
                 cudaStream_t stream) {
   // the opt-in is per device: a process may drive several GPUs
@@ -737,16 +756,16 @@ int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& 
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= kMaxDevices || !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(w4a16_gemm_kernel<MTOK, PAIR, TWO>,
+    cudaError_t e = cudaFuncSetAttribute(w4a16_gemm_kernel<MTOK, PAIR, TWO, TP>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         Cfg<MTOK, PAIR, TWO>::kSmemBytes);
+                                         Cfg<MTOK, PAIR, TWO, TP>::kSmemBytes);
     if (e != cudaSuccess) return (int)e;
     if (dev >= 0 && dev < kMaxDevices) attr_set[dev] = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(plan.ctas);
   cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = Cfg<MTOK, PAIR, TWO>::kSmemBytes;
+  cfg.dynamicSmemBytes = Cfg<MTOK, PAIR, TWO, TP>::kSmemBytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   int na = 0;
@@ -764,7 +783,7 @@ int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& 
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  return (int)cudaLaunchKernelEx(&cfg, w4a16_gemm_kernel<MTOK, PAIR, TWO>, prm, tmap);
+  return (int)cudaLaunchKernelEx(&cfg, w4a16_gemm_kernel<MTOK, PAIR, TWO, TP>, prm, tmap);
 }
 
 int gemm_flags() {
@@ -781,10 +800,10 @@ int gemm_flags() {
 
 uint32_t* g_trace = nullptr;
 
-template <int MTOK, int PAIR, bool TWO = false>
+template <int MTOK, int PAIR, bool TWO = false, int TP = 1>
 void fill_plan(GemmPlan* plan) {
-  plan->stages = Cfg<MTOK, PAIR, TWO>::kWStages;
-  plan->smem_bytes = Cfg<MTOK, PAIR, TWO>::kSmemBytes;
+  plan->stages = Cfg<MTOK, PAIR, TWO, TP>::kWStages;
+  plan->smem_bytes = Cfg<MTOK, PAIR, TWO, TP>::kSmemBytes;
 }
 
 // Tuning builds (`make tune`, -DB200_TUNING) can pin the variant with
@@ -815,6 +834,17 @@ int forced_two() {
   return -1;
 #endif
 }
+int forced_tp() {
+#ifdef B200_TUNING
+  static const int k = [] {
+    const char* e = getenv("B200_W4A16_TP");
+    return e ? atoi(e) : 0;
+  }();
+  return k;
+#else
+  return 0;
+#endif
+}
 int forced_pair() {
 #ifdef B200_TUNING
   static const int k = [] {
@@ -840,6 +870,7 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
   plan->k_blocks = K / kTileK;
   plan->pair = 1;
   plan->two_cta = 0;
+  plan->tok_pair = 1;
   const int fk = forced_kind();
   const bool group_ok = G % kTileK == 0;                  // one (scale, zero) row per 128-row tile
   bool decode = group_ok && M <= kDecodeMaxTokens;
@@ -895,9 +926,22 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
     // tuning: CTA pairs with ONE channel tile per CTA (two accumulator sets again)
     if (ft == 1 && tok == 128 && plan->pair == 1 && plan->n_tiles >= 2 && pairs >= 1) plan->two_cta = 1;
   }
+  // Token-tile pairs on CTA pairs with one channel tile per CTA: one dequantized weight tile in TMEM
+  // feeds the MMAs of TWO 128-token tiles (half the dequant work and weight bytes per flop: the
+  // steady state is then the tensor pipe itself, 513 cycles per 128 x 128 x 128 block,
+  // profiles/r3h_trace_tp2.txt).  Units are twice as long and the accumulators single-buffered,
+  // which loses on short walks: from 32 token tiles up, on wide or deep layers (+5-14 % at
+  // 4096-8192 tokens, up to 1.37 PFLOP/s; profiles/r3h_kb_{policy,tp2}.jsonl).
+  if (plan->two_cta && plan->m_tiles >= 32 && (plan->n_tiles >= 64 || plan->k_blocks >= 64)) {
+    plan->pair = 1;
+    plan->tok_pair = 2;
+  }
+  if (forced_tp() == 1) plan->tok_pair = 1;
+  if (forced_tp() == 2 && plan->two_cta && plan->m_tiles >= 2) { plan->pair = 1; plan->tok_pair = 2; }
   const int per_unit = plan->pair * (plan->two_cta ? 2 : 1);   // channel tiles per work unit
   const int ntp = (plan->n_tiles + per_unit - 1) / per_unit;
-  const long long T = (long long)ntp * plan->m_tiles * plan->k_blocks;
+  const int mtp = (plan->m_tiles + plan->tok_pair - 1) / plan->tok_pair;
+  const long long T = (long long)ntp * mtp * plan->k_blocks;
   if (T >= (1LL << 31)) return 1;
   // Persistent stream-K: one CTA (or CTA pair) per SM (pair), equal contiguous ranges of (output
   // unit, K block).
@@ -913,9 +957,10 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
   plan->max_split = (plan->k_blocks == 0 || (T % workers_ == 0 && per % plan->k_blocks == 0))
                         ? 1
                         : (int)((plan->k_blocks + per - 1) / (per > 0 ? per : 1) + 1);
-  plan->ws_partial_bytes = (size_t)ctas * 2 * plan->pair * tok * kTileN * sizeof(float);
+  plan->ws_partial_bytes = (size_t)ctas * 2 * plan->pair * plan->tok_pair * tok * kTileN * sizeof(float);
   if (plan->two_cta) {
-    if (plan->pair == 2) fill_plan<128, 2, true>(plan); else fill_plan<128, 1, true>(plan);
+    if (plan->tok_pair == 2) fill_plan<128, 1, true, 2>(plan);
+    else if (plan->pair == 2) fill_plan<128, 2, true>(plan); else fill_plan<128, 1, true>(plan);
     return 0;
   }
   if (plan->pair == 2) {
@@ -959,10 +1004,11 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   prm.y = y;
   prm.partials = reinterpret_cast<uint4*>(ws_partials);
   prm.M = M; prm.K = K; prm.N = N; prm.G = G;
-  prm.KB = plan.k_blocks; prm.NT = plan.n_tiles; prm.MT = plan.m_tiles;
+  prm.KB = plan.k_blocks; prm.NT = plan.n_tiles;
+  prm.MT = (plan.m_tiles + plan.tok_pair - 1) / plan.tok_pair;      // token-tile groups
   const int per_unit = plan.pair * (plan.two_cta ? 2 : 1);
   prm.NTP = (plan.n_tiles + per_unit - 1) / per_unit;
-  prm.T = prm.NTP * plan.m_tiles * plan.k_blocks;
+  prm.T = prm.NTP * prm.MT * plan.k_blocks;
   prm.P = plan.ctas;
   prm.R = G >= kTileK ? 1 : kTileK / G;
   prm.Gdiv = G >= kTileK ? G / kTileK : 1;
@@ -973,6 +1019,7 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   // per channel-tile group; 13824 -> 5120 at 2048 tokens fell from 1144 to 932 TFLOP/s.)
   prm.trace = g_trace;
   if (plan.two_cta) {
+    if (plan.tok_pair == 2) return launch_impl<128, 1, true, 2>(prm, tmap, plan, pdl, stream);
     if (plan.pair == 2) return launch_impl<128, 2, true>(prm, tmap, plan, pdl, stream);
     return launch_impl<128, 1, true>(prm, tmap, plan, pdl, stream);
   }

@@ -26,6 +26,7 @@ struct GemmPlan {
   int n_tiles;       // ceil(N / 128)
   int pair;          // tcgen05 kernel: channel tiles per CTA and work unit (1 or 2, sharing one activation tile)
   int two_cta;       // tcgen05 kernel: CTA pairs (cta_group::2), the activation tile split between two SMs
+  int tok_pair;      // tcgen05 kernel: token tiles per work unit (2: one dequantized weight tile feeds two)
   int m_tiles;       // ceil(M / tok_tile)
   int k_blocks;      // K / 128
   int ctas;          // grid size
