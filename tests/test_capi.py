@@ -121,3 +121,29 @@ def test_gemm_plan(pkg, M, K, N, tok, grid):
     ws = pkg._lib.lib().b200_w4a16_workspace_bytes(M, K, N, 1)
     assert 256 <= ws <= 148 * 2 * 2 * 128 * 128 * 4
     assert pkg._lib.lib().b200_w4a16_workspace_bytes(M, K, N, 0) >= ws + K * N // 2
+
+
+def test_gemm_plan_invariants_over_the_benchmark_shapes(pkg):
+    """Planner invariants the kernels rely on, over every (M, K, N) the benchmarks and BASELINE
+    configs use: every CTA resident (grid <= 148), CTA pairs only with an even grid and 128-token
+    tiles, shared memory within the opt-in limit, split-K scratch within the base workspace."""
+    L = pkg._lib.lib()
+    shapes = [(4096, 4096), (4096, 12288), (4096, 22016), (11008, 4096),            # Llama-2-7B
+              (5120, 15360), (5120, 5120), (5120, 27648), (13824, 5120),             # 13B
+              (8192, 10240), (8192, 8192), (8192, 57344), (28672, 8192),             # 70B TP1
+              (8192, 1280), (1024, 8192), (8192, 7168), (3584, 8192),                # 70B TP8
+              (4096, 28672), (14336, 4096), (4096, 768), (512, 4096)]                # Mixtral
+    base = 148 * 2 * 2 * 128 * 128 * 4
+    for (K, N) in shapes:
+        for M in (1, 8, 16, 17, 64, 128, 256, 512, 2048, 4096, 8192):
+            plan = pkg._lib.gemm_plan(M, K, N)
+            assert 1 <= plan["grid"] <= 148 and plan["smem_bytes"] <= 227 * 1024, (M, K, N, plan)
+            assert plan["variant"] == ("decode" if M <= 16 else "tcgen05"), (M, K, N, plan)
+            if plan["cta_pair"]:
+                assert plan["grid"] % 2 == 0 and plan["tok_tile"] == 128, (M, K, N, plan)
+                assert plan["unit_tiles"] in (2, 4) and plan["token_tiles"] in (1, 2), (M, K, N, plan)
+            else:
+                assert plan["unit_tiles"] in (1, 2) and plan["token_tiles"] == 1, (M, K, N, plan)
+            if plan["tok_tile"] < 128:
+                assert plan["unit_tiles"] == 1, (M, K, N, plan)      # pairs only for 128-token tiles
+            assert 256 <= L.b200_w4a16_workspace_bytes(M, K, N, 1) <= base, (M, K, N)
