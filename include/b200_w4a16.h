@@ -233,6 +233,50 @@ int b200_w4a16_moe_gather(const uint16_t *x, const int32_t *idx, uint16_t *out, 
 int b200_w4a16_moe_scatter_add(const uint16_t *y, const int32_t *idx, const float *w,
                                uint16_t *acc, size_t rows, int hidden, b200_stream_t stream);
 
+/* The local experts of a mixture-of-experts block as ONE launch at decode batches (M <= 16,
+ * G % 128 == 0, n_experts <= 8, all experts the same K, N, G; weights in the B200 layout):
+ *   y[e][M, N'] = x_e[M, K] . dequant(qweight[e], scales[e], qzeros[e])   for every local expert e
+ *                 with counts[e] > 0;   y[e] of the others is NOT written.
+ * `qweight` / `scales` / `qzeros` are HOST arrays of n_experts device pointers; `counts` is a
+ * device int32[n_experts] = tokens routed to each local expert (the router's output: read on
+ * the device, no host synchronisation, CUDA-graph capturable).  x_expert_stride = halfs between
+ * the experts' activations (0: all experts read the same x -- the merged w1 | w3 projection;
+ * M * K: expert e reads x + e * M * K -- the w2 projection behind it); y[e] = y + e * M * N'.
+ * act == 0: N' = N.  act == 1: SiLU-and-multiply in the epilogue over channel-paired gate / up
+ * weights (see b200_w4a16_gemm_silu_mul), N' = N / 2.  The (expert, channel tile, K block)
+ * space is cut into equal ranges over the experts WITH tokens only: every SM streams an equal
+ * share of the live weights whatever the routing.  Per expert bit-identical to
+ * b200_w4a16_gemm / b200_w4a16_gemm_silu_mul when one expert is live (same walk, same fix-up order).
+ * Replaces: the per-expert launches of the dense loop in MixtralMoE.forward
+ *           (vllm/model_executor/models/mixtral_quant.py:143-157; expert body :84-93). */
+int b200_w4a16_moe_grouped_gemm(const uint16_t *x, const int32_t *const *qweight,
+                                const uint16_t *const *scales, const int32_t *const *qzeros,
+                                uint16_t *y, int M, int K, int N, int G, int n_experts,
+                                const int32_t *counts, size_t x_expert_stride, int act,
+                                void *workspace, size_t workspace_bytes, b200_stream_t stream);
+
+/* The router of a mixture-of-experts block as one launch (plus a memset node for `counts`):
+ *   logits = half(x[tokens, hidden] . gate_w[n_experts, hidden]^T)     fp32 accumulate, fp16 result
+ *   p = softmax(float(logits));  (topk_w, topk_idx) = top_k largest of p, descending;
+ *   topk_w /= sum(topk_w);  dense_w[t, e] = topk_w of e for token t, 0 where e was not chosen;
+ *   counts[e] = tokens that chose e.
+ * topk_w fp32 [tokens, top_k], topk_idx int64 [tokens, top_k], dense_w fp32 [tokens, n_experts],
+ * counts int32 [n_experts]; hidden % 8 == 0, n_experts <= 32, top_k <= n_experts.
+ * Replaces: self.gate(hidden_states), F.softmax(..., dtype=torch.float), torch.topk and the
+ *           renormalisation of MixtralMoE.forward (vllm/model_executor/models/mixtral_quant.py:133-142)
+ *           plus the token counting the expert gates need. */
+int b200_w4a16_moe_route(const uint16_t *x, const uint16_t *gate_w, float *topk_w,
+                         int64_t *topk_idx, float *dense_w, int32_t *counts, size_t tokens,
+                         int hidden, int n_experts, int top_k, b200_stream_t stream);
+
+/* out[t, :] = sum over e < n_experts with counts[e] > 0, in index order, of
+ *   half(float(out[t, :]) + float(half(float(y[e][t, :]) * w[t * w_stride + e])))   (out starts 0)
+ * -- the `mul_(expert_weights)` / `add_` pair of mixtral_quant.py:152-157 for all local experts
+ * in one pass over y[n_experts][rows, hidden] (the grouped launch's output).  w fp32. */
+int b200_w4a16_moe_combine(const uint16_t *y, const float *w, const int32_t *counts,
+                           uint16_t *out, int n_experts, int w_stride, size_t rows, int hidden,
+                           b200_stream_t stream);
+
 /* ---- SiLU-and-multiply behind the gate_up projection ----------------------
  * out[rows, d] = half(silu(gate)) * up, silu(x) = half(float(x) / (1 + expf(-float(x)))), the
  * reference's arithmetic.  paired == 0: in[rows, 2 d] = [gate | up] halves, the reference's

@@ -92,9 +92,12 @@ def main():
     for T in (int(v) for v in args.tokens.split(",")):
         x = torch.randn(1, T, hidden, device="cuda", generator=gen).half()
         res = {}
-        for skip in (True, False):
+        # grouped: one launch per projection over the local experts with tokens (<= 16 tokens);
+        # gated: one gated launch per expert; False: the reference's dense loop
+        for skip in (True, "gated", False):
             for moe in blocks:
-                moe.skip_idle_experts = skip
+                moe.skip_idle_experts = bool(skip)
+                moe.grouped_max_tokens = 0 if skip == "gated" else 16
             st = torch.cuda.Stream()
             with torch.cuda.stream(st):
                 for moe in blocks:
@@ -122,6 +125,7 @@ def main():
         print(json.dumps({"tokens": T, "local_experts": args.experts_per_rank,
                           "active_experts_mean": round(mean_active, 2),
                           "us_per_block_skip_idle": round(res[True], 1),
+                          "us_per_block_gated_launch_per_expert": round(res["gated"], 1),
                           "us_per_block_dense_reference_loop": round(res[False], 1),
                           "speedup": round(res[False] / res[True], 2),
                           "GBps_active_weights": round(mean_active * bytes_expert / res[True] / 1e3, 1)}))

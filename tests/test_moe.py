@@ -66,6 +66,12 @@ def _reference_block(x, gate_w, dense, experts, top_k, round_half, with_mag=Fals
     return out, sel
 
 
+def _close(a, b, tol=4e-3):
+    """Agreement up to the fp32 summation order inside the GEMMs (a few fp16 ulps after them)."""
+    a, b = a.float(), b.float()
+    return bool(((a - b).abs() <= tol * b.abs().clamp(min=1.0)).all())
+
+
 def test_moe_cpu_matches_reference_loop(pkg, oracle):
     class OracleMethod(pkg.AWQLinearMethod):
         def apply_weights(self, weights, x, bias=None):
@@ -160,8 +166,13 @@ def test_moe_block_parity_and_idle_expert_skipping(pkg, oracle, cuda_lib, tokens
     got = moe(xd).reshape(tokens, 256)
     got_dense = dense_moe(xd).reshape(tokens, 256)
     torch.cuda.synchronize()
-    # same arithmetic whether idle experts stream their weights or not
-    assert torch.equal(got, got_dense)
+    # The grouped launch cuts the (live expert, tile, K block) space differently from eight
+    # single launches: other fp32 summation order inside the GEMMs, same roundings after them.
+    assert _close(got, got_dense)
+    moe.grouped_max_tokens = 0                             # one gated launch per expert instead
+    assert torch.equal(moe(xd).reshape(tokens, 256), got_dense)   # idle experts skipped or not: same bits
+    moe.grouped_max_tokens = 16
+    assert torch.equal(moe(xd).reshape(tokens, 256), got)          # deterministic
     err = (got.float().cpu() - want).abs()
     tol = 1e-2 * want.abs().clamp(min=1.0)                 # bar of the GEMM tests, three GEMMs deep: x2
     assert bool((err <= 2 * tol).all()), float((err / want.abs().clamp(min=1.0)).max())
@@ -181,7 +192,8 @@ def test_moe_block_parity_and_idle_expert_skipping(pkg, oracle, cuda_lib, tokens
         static_x.copy_(x2)
         graph.replay()
         st.synchronize()
-    assert torch.equal(static_y, dense_moe(x2))
+    assert torch.equal(static_y, moe(x2))
+    assert _close(static_y, dense_moe(x2))
 
 
 @pytest.mark.gpu
@@ -284,3 +296,142 @@ def test_moe_block_at_mixtral_shapes(pkg, oracle, cuda_lib, tokens, routed):
     err = (got.float().cpu() - want).abs()
     assert bool((err <= 2e-2 * mag.clamp(min=1.0)).all()), float((err / mag.clamp(min=1.0)).max())
     assert torch.equal(got, moe(x.cuda()).reshape(tokens, 4096))   # deterministic
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M", [1, 8, 16])
+@pytest.mark.parametrize("act", [False, True])
+def test_grouped_gemm_matches_per_expert_launches(pkg, oracle, cuda_lib, M, act):
+    """b200_w4a16_moe_grouped_gemm: five experts in one launch against one launch per expert;
+    experts without tokens are neither streamed nor written; one live expert = the single
+    launch bit for bit (same walk)."""
+    from gpu_util import to_dev, bits
+    K, N, E = 1024, 768, 5
+    ws = []
+    for e in range(E):
+        x, qw, s, qz = oracle.make_inputs(M, K, N, G, seed=100 + 7 * e + M)
+        ws.append((to_dev(x), pkg.ops.quick_repack(to_dev(qw)), to_dev(s), to_dev(qz)))
+    single = (lambda x, w: pkg.ops.quick_gemm_silu_mul(x, w[1], w[2], w[3])) if act else \
+             (lambda x, w: pkg.ops.quick_gemm(x, w[1], w[2], w[3], 8))
+    xs = torch.stack([w[0] for w in ws]).contiguous()      # [E, M, K]
+    NO = N // 2 if act else N
+    for shared_x in (True, False):
+        xin = ws[0][0] if shared_x else xs
+        for counts in ([2, 0, 1, 0, 3], [0, 0, 0, 4, 0], [1, 1, 1, 1, 1], [0, 0, 0, 0, 0]):
+            dc = torch.tensor(counts, dtype=torch.int32, device="cuda")
+            out = torch.full((E, M, NO), 7.0, dtype=torch.float16, device="cuda")
+            got = pkg.ops.moe_grouped_gemm(xin, [w[1] for w in ws], [w[2] for w in ws], [w[3] for w in ws],
+                                           dc, act=act, out=out)
+            again = pkg.ops.moe_grouped_gemm(xin, [w[1] for w in ws], [w[2] for w in ws], [w[3] for w in ws],
+                                             dc, act=act)
+            torch.cuda.synchronize()
+            assert got.data_ptr() == out.data_ptr()
+            for e in range(E):
+                if counts[e] == 0:
+                    assert bool((got[e] == 7.0).all())     # untouched
+                    continue
+                want = single(ws[0][0] if shared_x else ws[e][0], ws[e])
+                assert _close(got[e], want), (counts, e)
+                assert torch.equal(got[e], again[e])
+                if sum(c > 0 for c in counts) == 1:
+                    assert np.array_equal(bits(got[e]), bits(want))
+    # the plain launches still work after grouped ones (workspace handed back clean)
+    assert np.array_equal(bits(single(ws[1][0], ws[1])), bits(single(ws[1][0], ws[1])))
+
+
+@pytest.mark.gpu
+def test_grouped_gemm_and_combine_arguments(pkg, oracle, cuda_lib):
+    from gpu_util import to_dev
+    K, N = 256, 256
+    x, qw, s, qz = oracle.make_inputs(4, K, N, G, seed=3)
+    w = (pkg.ops.quick_repack(to_dev(qw)), to_dev(s), to_dev(qz))
+    c1 = torch.ones(1, dtype=torch.int32, device="cuda")
+    with pytest.raises(ValueError):                        # nine experts
+        pkg.ops.moe_grouped_gemm(to_dev(x), [w[0]] * 9, [w[1]] * 9, [w[2]] * 9,
+                                 torch.ones(9, dtype=torch.int32, device="cuda"))
+    x17 = torch.zeros((17, K), dtype=torch.float16, device="cuda")
+    with pytest.raises(ValueError):                        # above the decode kernel's batch sizes
+        pkg.ops.moe_grouped_gemm(x17, [w[0]], [w[1]], [w[2]], c1)
+    with pytest.raises(ValueError):                        # counts must be int32 [E]
+        pkg.ops.moe_grouped_gemm(to_dev(x), [w[0]], [w[1]], [w[2]], torch.ones(2, dtype=torch.int32, device="cuda"))
+    with pytest.raises(ValueError):
+        pkg.ops.moe_grouped_gemm(to_dev(x), [w[0]], [w[1]], [w[2]], torch.ones(1, dtype=torch.int64, device="cuda"))
+    with pytest.raises(ValueError):                        # x per expert: [E, M, K]
+        pkg.ops.moe_grouped_gemm(torch.zeros((2, 4, K), dtype=torch.float16, device="cuda"), [w[0]], [w[1]], [w[2]], c1)
+    empty = pkg.ops.moe_grouped_gemm(torch.zeros((0, K), dtype=torch.float16, device="cuda"), [w[0]], [w[1]], [w[2]], c1)
+    assert empty.shape == (1, 0, N)
+    with pytest.raises(ValueError):
+        pkg.ops.moe_combine(torch.zeros((2, 3, 64), dtype=torch.float16, device="cuda"),
+                            torch.zeros((3, 1), device="cuda"), torch.ones(2, dtype=torch.int32, device="cuda"))
+
+
+@pytest.mark.gpu
+def test_moe_combine_kernel(pkg, cuda_lib):
+    """b200_w4a16_moe_combine against NumPy: per live expert, in index order, mul_ (fp32 product,
+    one rounding) then add_ (fp16 sum, one rounding) -- mixtral_quant.py:152-157, exact."""
+    from gpu_util import bits, to_dev
+    rng = np.random.default_rng(1)
+    E, T, H, total = 4, 13, 512, 8
+    y = rng.standard_normal((E, T, H)).astype(np.float16)
+    y[2] = np.float16(np.nan)                              # expert 2 has no tokens: its slice is never read
+    w = rng.random((T, total)).astype(np.float32)
+    counts = np.array([3, 1, 0, 5], dtype=np.int32)
+    first = 3
+    dw = torch.from_numpy(w).cuda()
+    got = pkg.ops.moe_combine(to_dev(y), dw[:, first:first + E], torch.from_numpy(counts).cuda())
+    want = np.zeros((T, H), dtype=np.float16)
+    for e in range(E):
+        if counts[e] > 0:
+            scaled = (y[e].astype(np.float32) * w[:, first + e, None]).astype(np.float16)
+            want = (want.astype(np.float32) + scaled.astype(np.float32)).astype(np.float16)
+    assert np.array_equal(bits(got), want.view(np.uint16))
+    none = pkg.ops.moe_combine(to_dev(y), dw[:, first:first + E], torch.zeros(E, dtype=torch.int32, device="cuda"))
+    assert not none.any()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("T,E,H,k", [(1, 8, 4096, 2), (16, 8, 4096, 2), (333, 8, 256, 2), (40, 20, 512, 3)])
+def test_router_kernel_matches_the_reference_arithmetic(pkg, cuda_lib, T, E, H, k):
+    """b200_w4a16_moe_route against mixtral_quant.py:133-142 in float64 on the host (fp16 logits,
+    softmax, top-k, renormalise); outputs consistent with each other exactly."""
+    g = torch.Generator().manual_seed(T + E)
+    x = torch.randn(T, H, generator=g).half()
+    gw = (torch.randn(E, H, generator=g) * (2.0 / H ** 0.5)).half()
+    w, idx, counts, dense = pkg.ops.moe_route(x.cuda(), gw.cuda(), k)
+    torch.cuda.synchronize()
+    w, idx, counts, dense = w.cpu(), idx.cpu(), counts.cpu(), dense.cpu()
+    logits = (x.double() @ gw.double().t()).half().double()
+    p = torch.softmax(logits, dim=1)
+    rw, ridx = torch.topk(p, k, dim=-1)
+    nxt = torch.topk(p, k + 1, dim=-1)[0][:, k] if E > k else torch.zeros(T, dtype=torch.float64)
+    # an fp16 logit can round the other way in another summation order (2^-11 relative):
+    # compare where no two adjacent ranks are that close
+    gaps = torch.cat([rw, nxt[:, None]], dim=1)
+    clear = ((gaps[:, :-1] - gaps[:, 1:]) > 4e-3 * gaps[:, :-1]).all(dim=1)
+    assert int(clear.sum()) >= T // 2 or T == 1
+    assert torch.equal(idx[clear], ridx[clear])
+    rw = rw / rw.sum(dim=-1, keepdim=True)
+    assert torch.allclose(w[clear].double(), rw[clear], rtol=5e-3, atol=1e-6)
+    # self-consistency, exact
+    assert idx.dtype == torch.int64 and w.dtype == torch.float32 and counts.dtype == torch.int32
+    assert torch.equal(counts.long(), torch.bincount(idx.reshape(-1), minlength=E))
+    assert all(len(set(r)) == k for r in idx.tolist())               # an expert at most once per token
+    assert bool((w[:, :-1] >= w[:, 1:]).all())                        # descending, as torch.topk
+    assert torch.equal(torch.zeros(T, E).scatter_(1, idx, w), dense)
+    assert torch.allclose(w.sum(dim=1), torch.ones(T), atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_router_kernel_arguments(pkg, cuda_lib):
+    x = torch.zeros((0, 64), dtype=torch.float16, device="cuda")
+    gw = torch.zeros((4, 64), dtype=torch.float16, device="cuda")
+    w, idx, counts, dense = pkg.ops.moe_route(x, gw, 2)
+    assert w.shape == (0, 2) and not counts.any()
+    with pytest.raises(ValueError):
+        pkg.ops.moe_route(torch.zeros((2, 64), dtype=torch.float16, device="cuda"), gw, 5)      # top_k > experts
+    with pytest.raises(ValueError):
+        pkg.ops.moe_route(torch.zeros((2, 60), dtype=torch.float16, device="cuda"),
+                          torch.zeros((4, 60), dtype=torch.float16, device="cuda"), 2)            # hidden % 8
+    with pytest.raises(ValueError):
+        pkg.ops.moe_route(torch.zeros((2, 64), dtype=torch.float16, device="cuda"),
+                          torch.zeros((33, 64), dtype=torch.float16, device="cuda"), 2)           # > 32 experts

@@ -453,6 +453,84 @@ int b200_w4a16_moe_scatter_add(const uint16_t* y, const int32_t* idx, const floa
   return e == 0 ? B200_OK : cuda_fail(e);
 }
 
+int b200_w4a16_moe_grouped_gemm(const uint16_t* x, const int32_t* const* qweight,
+                                const uint16_t* const* scales, const int32_t* const* qzeros,
+                                uint16_t* y, int M, int K, int N, int G, int n_experts,
+                                const int32_t* counts, size_t x_expert_stride, int act,
+                                void* workspace, size_t workspace_bytes, b200_stream_t stream) {
+  if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
+  if (M > b200::kDecodeMaxTokens || G % b200::kTileK != 0) return B200_ERR_BAD_SHAPE;
+  if (n_experts < 1 || n_experts > b200::kMaxGroupExperts) return B200_ERR_BAD_SHAPE;
+  if ((act != 0 && act != 1) || (act && N % 16 != 0)) return B200_ERR_BAD_SHAPE;
+  if (x_expert_stride != 0 && x_expert_stride != (size_t)M * K) return B200_ERR_BAD_SHAPE;
+  if (M == 0) return B200_OK;
+  if (!x || !qweight || !scales || !qzeros || !y || !counts) return B200_ERR_BAD_ARG;
+  if (!aligned16(x) || !aligned16(y) || (reinterpret_cast<uintptr_t>(counts) & 3u)) return B200_ERR_BAD_ARG;
+  b200::ExpertGroup grp{};
+  for (int e = 0; e < n_experts; ++e) {
+    if (!qweight[e] || !scales[e] || !qzeros[e] || !aligned16(qweight[e]) || !aligned16(scales[e]) ||
+        !aligned16(qzeros[e]))
+      return B200_ERR_BAD_ARG;
+    grp.qw[e] = qweight[e];
+    grp.scales[e] = scales[e];
+    grp.qz[e] = qzeros[e];
+  }
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  b200::GemmPlan plan;                                      // one expert's plan: grid and tile counts
+  if (b200::make_gemm_plan(M, K, N, G, 0, dev.sm_count, &plan) || plan.kind != b200::kKindDecode)
+    return B200_ERR_BAD_SHAPE;
+  if ((long long)plan.n_tiles * plan.k_blocks * n_experts >= (1LL << 31)) return B200_ERR_BAD_SHAPE;
+  const size_t part_bytes = align_up(plan.ws_partial_bytes, 256);
+  if (part_bytes > kMaxPartialBytes || !workspace || workspace_bytes < part_bytes || !aligned16(workspace))
+    return B200_ERR_WORKSPACE;
+  grp.counts = counts;
+  grp.n_experts = n_experts;
+  grp.x_stride = (long long)x_expert_stride;
+  grp.y_stride = (long long)M * (act ? N / 2 : N);
+  int e = b200::launch_decode_grouped(x, grp, y, M, K, N, G, plan, workspace, use_pdl(),
+                                      reinterpret_cast<cudaStream_t>(stream), act);
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+int b200_w4a16_moe_route(const uint16_t* x, const uint16_t* gate_w, float* topk_w, int64_t* topk_idx,
+                         float* dense_w, int32_t* counts, size_t tokens, int hidden, int n_experts,
+                         int top_k, b200_stream_t stream) {
+  if (hidden <= 0 || hidden % 8 != 0 || n_experts < 1 || n_experts > b200::kMaxRouteExperts ||
+      top_k < 1 || top_k > n_experts || tokens > (size_t)0x7fffffff)
+    return B200_ERR_BAD_SHAPE;
+  if (!counts || (reinterpret_cast<uintptr_t>(counts) & 3u)) return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (tokens == 0) {                                        // nobody chose anybody
+    cudaError_t e = cudaMemsetAsync(counts, 0, (size_t)n_experts * sizeof(int32_t), s);
+    return e == cudaSuccess ? B200_OK : cuda_fail((int)e);
+  }
+  if (!x || !gate_w || !topk_w || !topk_idx || !dense_w || !aligned16(x) || !aligned16(gate_w) ||
+      (reinterpret_cast<uintptr_t>(topk_w) & 3u) || (reinterpret_cast<uintptr_t>(topk_idx) & 7u) ||
+      (reinterpret_cast<uintptr_t>(dense_w) & 3u))
+    return B200_ERR_BAD_ARG;
+  int e = b200::launch_moe_route(x, gate_w, topk_w, reinterpret_cast<long long*>(topk_idx), dense_w,
+                                 counts, tokens, hidden, n_experts, top_k, s);
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+int b200_w4a16_moe_combine(const uint16_t* y, const float* w, const int32_t* counts, uint16_t* out,
+                           int n_experts, int w_stride, size_t rows, int hidden,
+                           b200_stream_t stream) {
+  if (hidden <= 0 || hidden % 8 != 0 || n_experts < 1 || w_stride < n_experts) return B200_ERR_BAD_SHAPE;
+  if (rows == 0) return B200_OK;
+  if (!y || !w || !counts || !out || !aligned16(y) || !aligned16(out) ||
+      (reinterpret_cast<uintptr_t>(w) & 3u) || (reinterpret_cast<uintptr_t>(counts) & 3u))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_moe_combine(y, w, counts, out, n_experts, w_stride, rows, hidden,
+                                   reinterpret_cast<cudaStream_t>(stream));
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
 int b200_w4a16_add_rms_norm(const uint16_t* in, const uint16_t* residual_in, const uint16_t* weight,
                       uint16_t* out, uint16_t* residual_out, float eps, size_t rows, int hidden,
                       b200_stream_t stream) {

@@ -105,6 +105,9 @@ struct DecodeParams {
   // Row-parallel fusion (ar.world > 1): finished tiles are pushed to every rank's region and
   // reduced there; y then holds the all-reduced result (see the file header).
   FusedArParams ar;
+  // GROUPED instantiation (b200_w4a16_moe_grouped_gemm): qw / scales / qz above are unused, T is
+  // ONE expert's tile count; see ExpertGroup (w4a16_internal.h).
+  ExpertGroup grp;
 };
 
 #ifdef B200_TRACE
@@ -152,7 +155,12 @@ __device__ __forceinline__ void mma_16816(float (&d)[4], uint32_t a0, uint32_t a
 }
 
 
-template <int MT>
+// GROUPED: the local experts of a mixture-of-experts block in one launch.  The tile space is
+// (expert WITH tokens, channel tile, K block): every CTA reads the per-expert token counts (the
+// router's output, so nothing is prefetched before the dependency resolves), packs the ids of
+// the experts that have tokens into one word and cuts the space over those only -- all SMs
+// stream an equal share of the live weights, idle experts cost nothing and their y is untouched.
+template <int MT, bool GROUPED>
 __global__ void __launch_bounds__(kDecThreads, 1)
 w4a16_decode_kernel(const DecodeParams p) {
   using C = DCfg<MT>;
@@ -167,8 +175,21 @@ w4a16_decode_kernel(const DecodeParams p) {
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) TD(0);
-  const int t_begin = range_begin(blockIdx.x, p.T, p.P);
-  const int t_end = range_begin(blockIdx.x + 1, p.T, p.P);
+  int T = p.T;
+  uint32_t live = 0;                                        // 4 bits per live expert: its index
+  if constexpr (GROUPED) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");      // the counts are the router's output
+    int nlive = 0;
+    for (int e = 0; e < p.grp.n_experts; ++e)
+      if (reinterpret_cast<const volatile int*>(p.grp.counts)[e] > 0) {
+        live |= (uint32_t)e << (4 * nlive);
+        ++nlive;
+      }
+    if (nlive == 0) return;
+    T = nlive * p.T;
+  }
+  const int t_begin = range_begin(blockIdx.x, T, p.P);
+  const int t_end = range_begin(blockIdx.x + 1, T, p.P);
   const Walk walk(t_begin, t_end, p.KB);
   const int n_total = t_end - t_begin;
   (void)n_total;
@@ -218,6 +239,7 @@ w4a16_decode_kernel(const DecodeParams p) {
       int idx, base, i, n, nt, kb0;
       int stage;
       uint32_t round;
+      int e;                                                  // GROUPED: the tile's expert
     };
     auto seek = [&](Cur& c) {                                 // first tile of mine in segment idx or later
       while (c.idx < walk.nseg) {
@@ -227,6 +249,11 @@ w4a16_decode_kernel(const DecodeParams p) {
         if (c.i < c.n) {
           c.nt = t0 / p.KB;
           c.kb0 = t0 - c.nt * p.KB;
+          if constexpr (GROUPED) {
+            const int j = c.nt / p.NT;
+            c.e = (int)((live >> (4 * j)) & 15u);
+            c.nt -= j * p.NT;
+          }
           return;
         }
         c.base += c.n;
@@ -246,15 +273,24 @@ w4a16_decode_kernel(const DecodeParams p) {
       const uint32_t sb = stage0 + c.stage * C::kStageBytes;
       const uint32_t bar = bar_full + 8 * c.stage;
       const uint32_t g0 = p.Gdiv == 1 ? (uint32_t)kb : (uint32_t)kb / (uint32_t)p.Gdiv;
+      const uint32_t* qw = p.qw;
+      const uint16_t* scales = p.scales;
+      const uint32_t* qz = p.qz;
+      if constexpr (GROUPED) {
+        qw = reinterpret_cast<const uint32_t*>(p.grp.qw[c.e]);
+        scales = p.grp.scales[c.e];
+        qz = reinterpret_cast<const uint32_t*>(p.grp.qz[c.e]);
+      }
       mbar_arrive_expect_tx(bar, tx);
-      bulk_g2s_hint(sb + C::kWOff, p.qw + ((size_t)c.nt * p.KB + kb) * kTileWords, kTileWords * 4, bar, pol_w);
-      bulk_g2s(sb + C::kSOff, p.scales + c.nt * kTileN + (size_t)g0 * srow, nvalid * 2, bar);
-      bulk_g2s(sb + C::kZOff, p.qz + c.nt * 16 + (size_t)g0 * zrow, nvalid / 2, bar);
+      bulk_g2s_hint(sb + C::kWOff, qw + ((size_t)c.nt * p.KB + kb) * kTileWords, kTileWords * 4, bar, pol_w);
+      bulk_g2s(sb + C::kSOff, scales + c.nt * kTileN + (size_t)g0 * srow, nvalid * 2, bar);
+      bulk_g2s(sb + C::kZOff, qz + c.nt * 16 + (size_t)g0 * zrow, nvalid / 2, bar);
     };
     auto issue_x = [&](const Cur& c) {                        // all lanes
       const int kb = c.kb0 + c.i;
       const uint32_t dst = stage0 + c.stage * C::kStageBytes + C::kXOff + lane * 16;
-      const size_t koff = (size_t)kb * (kTileK * 2);
+      size_t koff = (size_t)kb * (kTileK * 2);
+      if constexpr (GROUPED) koff += (size_t)c.e * (size_t)p.grp.x_stride * 2;
 #pragma unroll
       for (int j = 0; j < 4; ++j)
 #pragma unroll
@@ -262,7 +298,7 @@ w4a16_decode_kernel(const DecodeParams p) {
           cp_async_16(dst + (j * MT + i) * 512, xrow[i] + koff + j * 64, xsz[i]);
       cp_async_mbar_arrive_noinc(bar_full + 8 * c.stage);
     };
-    Cur c0{0, 0, 0, 0, 0, 0, pw, 0u};
+    Cur c0{0, 0, 0, 0, 0, 0, pw, 0u, 0};
     seek(c0);
     Cur cw = c0;
     if (lane == 0) {
@@ -315,7 +351,17 @@ w4a16_decode_kernel(const DecodeParams p) {
     }
     int own_nt = -1, own_slot = 0, own_last = 0;              // tile this CTA finishes, if any
     bool own_local = false;                                   // its own piece is handed over in shared memory
+    // GROUPED: a tile index of the walk -> the expert's output and the tile inside it
+    auto expert_out = [&](int& nt) -> uint16_t* {
+      if constexpr (GROUPED) {
+        const int j = nt / p.NT;
+        nt -= j * p.NT;
+        return p.y + (size_t)((live >> (4 * j)) & 15u) * (size_t)p.grp.y_stride;
+      }
+      return p.y;
+    };
     auto write_y = [&](int nt, const float (&v)[2][MT][4]) {
+      uint16_t* const y = expert_out(nt);
       if (p.act) {
         // rows g / g + 8 of the MMA tile are the gate / up channel of one output channel: both
         // live in this thread (e, e + 2)
@@ -328,7 +374,7 @@ w4a16_decode_kernel(const DecodeParams p) {
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
               const int m = 8 * i + 2 * t + e;
-              if (m < p.M && no < NO) p.y[(size_t)m * NO + no] = silu_mul_f16(v[b][i][e], v[b][i][e + 2]);
+              if (m < p.M && no < NO) y[(size_t)m * NO + no] = silu_mul_f16(v[b][i][e], v[b][i][e + 2]);
             }
         }
         return;
@@ -344,13 +390,13 @@ w4a16_decode_kernel(const DecodeParams p) {
             const int m = m0 + (e & 1);
             const int nn = n_lo + (e >> 1) * 8;
             if (m < p.M && nn < p.N)
-              p.y[(size_t)m * p.N + nn] = __half_as_ushort(__float2half_rn(v[b][i][e]));
+              y[(size_t)m * p.N + nn] = __half_as_ushort(__float2half_rn(v[b][i][e]));
           }
         }
       }
     };
     // ---- row-parallel fusion: a finished tile goes to every rank's region instead of y
-    const bool fused = p.ar.world > 1;
+    const bool fused = !GROUPED && p.ar.world > 1;
     uint32_t epoch = 0, ar_slot = 0;
     if (fused) {
       // previous fused launch has fully completed (griddepcontrol.wait above): its bump is visible
@@ -461,10 +507,10 @@ w4a16_decode_kernel(const DecodeParams p) {
 
       // a partial segment that starts an output tile makes this CTA the tile's owner (every
       // consumer thread tracks it: the deferred fix-up below uses all of them)
-      if (n != p.KB && owner_of(nt * p.KB, p.P, p.T) == (int)blockIdx.x) {   // at most one per CTA
+      if (n != p.KB && owner_of(nt * p.KB, p.P, T) == (int)blockIdx.x) {   // at most one per CTA
         own_nt = nt;
         own_slot = idx == 0 ? 0 : 1;
-        own_last = owner_of(nt * p.KB + p.KB - 1, p.P, p.T);
+        own_last = owner_of(nt * p.KB + p.KB - 1, p.P, T);
         // Our own piece is the last thing we compute: it stays on chip (shared memory) instead
         // of a store / fence / counter round trip through L2 that nobody else needs.
         own_local = !fused && idx == walk.nseg - 1;
@@ -525,6 +571,7 @@ w4a16_decode_kernel(const DecodeParams p) {
     const int tid = threadIdx.x - kFirstConsumerWarp * 32;    // 0 .. kConsumerThreads - 1
     // quad e = (b MT + i) 128 + thread-in-group of tile nt: the accumulator fragment of write_y
     auto store_entry = [&](int nt, int e, const float (&v)[4]) {
+      uint16_t* const y = expert_out(nt);
       const int q = e / kGroupThreads, et = e % kGroupThreads;
       const int eb = q / MT, ei = q % MT;
       const int m0 = 8 * ei + 2 * (et & 3);
@@ -533,14 +580,14 @@ w4a16_decode_kernel(const DecodeParams p) {
         const int no = ((nt * kTileN + (et >> 5) * 32 + 16 * eb) >> 1) + ((et & 31) >> 2);
 #pragma unroll
         for (int k = 0; k < 2; ++k)
-          if (m0 + k < p.M && no < NO) p.y[(size_t)(m0 + k) * NO + no] = silu_mul_f16(v[k], v[k + 2]);
+          if (m0 + k < p.M && no < NO) y[(size_t)(m0 + k) * NO + no] = silu_mul_f16(v[k], v[k + 2]);
         return;
       }
       const int n0 = nt * kTileN + (et >> 5) * 32 + ((et & 31) >> 2) + 16 * eb;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const int m = m0 + (k & 1), nn = n0 + (k >> 1) * 8;
-        if (m < p.M && nn < p.N) p.y[(size_t)m * p.N + nn] = __half_as_ushort(__float2half_rn(v[k]));
+        if (m < p.M && nn < p.N) y[(size_t)m * p.N + nn] = __half_as_ushort(__float2half_rn(v[k]));
       }
     };
 
@@ -663,14 +710,14 @@ w4a16_decode_kernel(const DecodeParams p) {
   }
 }
 
-template <int MT>
+template <int MT, bool GROUPED>
 int launch_decode_impl(const DecodeParams& prm, bool pdl, cudaStream_t stream) {
   // the opt-in is per device: a process may drive several GPUs
   static bool attr_set[kMaxDevices] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= kMaxDevices || !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(w4a16_decode_kernel<MT>,
+    cudaError_t e = cudaFuncSetAttribute(w4a16_decode_kernel<MT, GROUPED>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          DCfg<MT>::kSmemBytes);
     if (e != cudaSuccess) return (int)e;
@@ -686,7 +733,7 @@ int launch_decode_impl(const DecodeParams& prm, bool pdl, cudaStream_t stream) {
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
-  return (int)cudaLaunchKernelEx(&cfg, w4a16_decode_kernel<MT>, prm);
+  return (int)cudaLaunchKernelEx(&cfg, w4a16_decode_kernel<MT, GROUPED>, prm);
 }
 
 int decode_flags() {
@@ -738,8 +785,31 @@ int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* sca
     memset(&prm.ar, 0, sizeof(prm.ar));
     prm.ar.world = 1;
   }
-  return plan.tok_tile <= 8 ? launch_decode_impl<1>(prm, pdl, stream)
-                            : launch_decode_impl<2>(prm, pdl, stream);
+  memset(&prm.grp, 0, sizeof(prm.grp));
+  return plan.tok_tile <= 8 ? launch_decode_impl<1, false>(prm, pdl, stream)
+                            : launch_decode_impl<2, false>(prm, pdl, stream);
+}
+
+int launch_decode_grouped(const uint16_t* x, const ExpertGroup& grp, uint16_t* y, int M, int K,
+                          int N, int G, const GemmPlan& plan, void* ws_partials, bool pdl,
+                          cudaStream_t stream, int act) {
+  DecodeParams prm;
+  memset(&prm, 0, sizeof(prm));
+  prm.act = act;
+  prm.x = x;
+  prm.y = y;
+  prm.partials = reinterpret_cast<uint4*>(ws_partials);
+  prm.M = M; prm.K = K; prm.N = N;
+  prm.KB = plan.k_blocks; prm.NT = plan.n_tiles;
+  prm.T = plan.n_tiles * plan.k_blocks;                     // one expert's tiles
+  prm.P = plan.ctas;
+  prm.Gdiv = G / kTileK;
+  prm.flags = decode_flags();
+  prm.trace = trace_buffer();
+  prm.ar.world = 1;
+  prm.grp = grp;
+  return plan.tok_tile <= 8 ? launch_decode_impl<1, true>(prm, pdl, stream)
+                            : launch_decode_impl<2, true>(prm, pdl, stream);
 }
 
 }  // namespace b200

@@ -62,6 +62,34 @@ int launch_decode(const uint16_t* x, const int32_t* qw_b200, const uint16_t* sca
                   const GemmPlan& plan, void* ws_partials, bool pdl, cudaStream_t stream,
                   const FusedArParams* ar = nullptr, const int* gate = nullptr, int act = 0);
 
+// The local experts of a mixture-of-experts block as ONE decode-kernel launch (w4a16_decode.cu,
+// GROUPED instantiation): same shapes, one set of weight pointers per expert.  counts[e] (device)
+// = tokens routed to local expert e; the (expert, channel tile, K block) space is cut over the
+// experts WITH tokens only, so every SM streams an equal share whatever the routing.
+constexpr int kMaxGroupExperts = 8;
+struct ExpertGroup {
+  const int32_t* qw[kMaxGroupExperts];      // B200 layout
+  const uint16_t* scales[kMaxGroupExperts];
+  const int32_t* qz[kMaxGroupExperts];
+  const int32_t* counts;                    // [n_experts], device
+  int n_experts;
+  long long x_stride;                       // halfs between the experts' activations (0: shared x)
+  long long y_stride;                       // halfs between the experts' outputs
+};
+int launch_decode_grouped(const uint16_t* x, const ExpertGroup& grp, uint16_t* y, int M, int K,
+                          int N, int G, const GemmPlan& plan, void* ws_partials, bool pdl,
+                          cudaStream_t stream, int act);
+// final[t] = sum over local experts e with counts[e] > 0, in index order, of
+// half(final[t] + half(y[e][t] * w[t][first + e])) -- the reference's mul_ / add_ arithmetic.
+int launch_moe_combine(const uint16_t* y, const float* w, const int32_t* counts, uint16_t* out,
+                       int n_experts, int w_stride, size_t rows, int hidden, cudaStream_t stream);
+
+// Router: fp16 gate GEMM -> fp32 softmax -> top-k -> renormalise, a warp per token.
+constexpr int kMaxRouteExperts = 32;
+int launch_moe_route(const uint16_t* x, const uint16_t* gate_w, float* topk_w, long long* topk_idx,
+                     float* dense_w, int32_t* counts, size_t tokens, int hidden, int n_experts,
+                     int top_k, cudaStream_t stream);
+
 // silu(x[:, :d]) * x[:, d:] (paired == 0: the reference's [gate | up] halves) or, paired == 1,
 // the channel-paired order the fused gate_up GEMM uses (every 16 channels = 8 gate + 8 up).
 int launch_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int d, int paired,

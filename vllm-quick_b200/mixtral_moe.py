@@ -124,6 +124,9 @@ class MixtralMoE(nn.Module):
     # Batches of at least this many tokens, outside CUDA-graph capture, take the routed path
     # (where it overtakes the dense loop on B200: profiles/r1e_moe_prefill_bench.jsonl).
     routed_min_tokens = 512
+    # Up to here (the decode kernel's batch sizes) the local experts run as ONE grouped launch
+    # per projection instead of one launch per expert.
+    grouped_max_tokens = 16
 
     def __init__(self, config, linear_method: Optional[LinearMethodBase] = None,
                  skip_idle_experts: bool = True):
@@ -155,6 +158,17 @@ class MixtralMoE(nn.Module):
         """softmax -> top-k -> renormalise, as the reference (:136-142).  Returns the routing
         weights ``[T, top_k]`` fp32, the chosen experts ``[T, top_k]`` and, per expert, how
         many tokens chose it ``[num_experts]`` int32 (device; feeds the GEMM gates)."""
+        return self._route(hidden_states)[:3]
+
+    def _route(self, hidden_states: torch.Tensor):
+        """``route`` plus the dense ``[T, num_experts]`` weight matrix where the router kernel
+        produced it (None otherwise).  On the GPU the whole router is one launch
+        (``ops.moe_route``) instead of a library GEMM and ten elementwise kernels -- at decode
+        batches those cost as much as streaming two experts."""
+        if (hidden_states.is_cuda and hidden_states.dtype == torch.float16
+                and self.gate.weight.dtype == torch.float16 and self.num_total_experts <= 32
+                and hidden_states.shape[1] % 8 == 0 and hidden_states.is_contiguous()):
+            return ops.moe_route(hidden_states, self.gate.weight.data, self.top_k)
         router_logits, _ = self.gate(hidden_states)
         routing_weights = F.softmax(router_logits, dim=1, dtype=torch.float)
         routing_weights, selected_experts = torch.topk(routing_weights, self.top_k, dim=-1)
@@ -163,7 +177,7 @@ class MixtralMoE(nn.Module):
                              device=hidden_states.device)
         counts.scatter_add_(0, selected_experts.reshape(-1),
                             torch.ones_like(selected_experts.reshape(-1), dtype=torch.int32))
-        return routing_weights, selected_experts, counts
+        return routing_weights, selected_experts, counts, None
 
     def _all_tokens(self, device: torch.device, tokens: int) -> torch.Tensor:
         key = (device, tokens)
@@ -175,7 +189,7 @@ class MixtralMoE(nn.Module):
             self._token_ids[key] = ids
         return ids
 
-    def _forward_routed(self, hidden_states, routing_weights, selected_experts, counts):
+    def _forward_routed(self, hidden_states, routing_weights, selected_experts, counts, per_token=None):
         """Gather each local expert's tokens, run it on M_e rows, scatter-add the weighted rows."""
         final = torch.zeros_like(hidden_states)
         order = torch.argsort(selected_experts.reshape(-1), stable=True)   # by expert, token order kept
@@ -192,13 +206,49 @@ class MixtralMoE(nn.Module):
             start += n
         return final
 
-    def _forward_dense(self, hidden_states, routing_weights, selected_experts, counts):
+    def _can_group(self, hidden_states: torch.Tensor) -> bool:
+        """Decode batches on the GPU, at most eight local experts, the decode kernel's group sizes."""
+        if not (hidden_states.is_cuda and self.skip_idle_experts and len(self.expert_indicies) <= 8
+                and 0 < hidden_states.shape[0] <= self.grouped_max_tokens):
+            return False
+        mlp = self.experts[self.expert_indicies[0]]
+        if not hasattr(mlp.linear_method, "apply_weights_silu_and_mul"):
+            return False
+        mlp.process_weights_after_loading()
+        # the decode kernel takes quantization groups of whole 128-row tiles
+        return all(k % 128 == 0 and (k // w["scales"].shape[0]) % 128 == 0
+                   for w, k in ((mlp._w13, mlp.hidden_dim), (mlp.w2.linear_weights, mlp.ffn_dim)))
+
+    def _forward_grouped(self, hidden_states, routing_weights, selected_experts, counts, per_token=None):
+        """All local experts as two grouped launches + one accumulation pass: the
+        tile walk of each launch covers the experts WITH tokens only (counts read on the
+        device), so the SMs share the live weights evenly and idle experts cost nothing."""
+        mlps = [self.experts[e] for e in self.expert_indicies]
+        for m in mlps:
+            m.process_weights_after_loading()
+        first, n_local = self.expert_indicies[0], len(mlps)
+        local_counts = counts[first:first + n_local]
+        gate_up = [m._w13 for m in mlps]
+        down = [m.w2.linear_weights for m in mlps]
+        act = ops.moe_grouped_gemm(hidden_states, [w["qweight"].data for w in gate_up],
+                                   [w["scales"].data for w in gate_up], [w["qzeros"].data for w in gate_up],
+                                   local_counts, act=True)                       # [E, T, ffn]
+        out = ops.moe_grouped_gemm(act, [w["qweight"].data for w in down], [w["scales"].data for w in down],
+                                   [w["qzeros"].data for w in down], local_counts)  # [E, T, hidden]
+        # routing weight of every (token, expert): each expert is chosen at most once per token
+        if per_token is None:
+            per_token = torch.zeros((hidden_states.shape[0], self.num_total_experts), dtype=torch.float32,
+                                    device=hidden_states.device).scatter_(1, selected_experts, routing_weights)
+        return ops.moe_combine(out, per_token[:, first:first + n_local], local_counts)
+
+    def _forward_dense(self, hidden_states, routing_weights, selected_experts, counts, dense_w=None):
         """Every local expert on every token (the reference's structure); experts without tokens
         are skipped on the device, the weighted accumulation is one kernel per expert."""
         on_gpu = hidden_states.is_cuda
         final = None
         for expert_idx in self.expert_indicies:
-            per_token = (routing_weights * (selected_experts == expert_idx)).sum(dim=-1)   # fp32 [T]
+            per_token = (dense_w[:, expert_idx] if dense_w is not None else
+                         (routing_weights * (selected_experts == expert_idx)).sum(dim=-1))   # fp32 [T]
             gate = counts[expert_idx:expert_idx + 1] if (self.skip_idle_experts and on_gpu) else None
             with ops.expert_gate(gate):
                 out = self.experts[expert_idx](hidden_states)
@@ -215,10 +265,13 @@ class MixtralMoE(nn.Module):
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
         batch_size, sequence_length, hidden_dim = hidden_states.shape
         hidden_states = hidden_states.view(-1, hidden_dim)
-        routing_weights, selected_experts, counts = self.route(hidden_states)
+        hidden_states = hidden_states.contiguous()
+        routing_weights, selected_experts, counts, dense_w = self._route(hidden_states)
         routed = (self.skip_idle_experts and hidden_states.is_cuda
                   and hidden_states.shape[0] >= self.routed_min_tokens
                   and not torch.cuda.is_current_stream_capturing())
         body = self._forward_routed if routed else self._forward_dense
-        final = body(hidden_states.contiguous(), routing_weights, selected_experts, counts)
+        if not routed and self._can_group(hidden_states):
+            body = self._forward_grouped
+        final = body(hidden_states, routing_weights, selected_experts, counts, dense_w)
         return tensor_model_parallel_all_reduce(final).view(batch_size, sequence_length, hidden_dim)

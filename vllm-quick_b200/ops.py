@@ -12,6 +12,7 @@ PyTorch is used for device memory and streams only; all arithmetic is in
 from __future__ import annotations
 
 import contextlib
+import ctypes
 import threading
 from typing import Dict, Optional, Tuple
 
@@ -385,3 +386,93 @@ def moe_scatter_add(acc: torch.Tensor, y: torch.Tensor, idx: torch.Tensor, w: to
                                                    acc.data_ptr(), y.shape[0], y.shape[1],
                                                    _stream_ptr(dev))
     _lib.check(st, "moe_scatter_add")
+
+
+def moe_grouped_gemm(x: torch.Tensor, kernels, scaling_factors, zeros, counts: torch.Tensor,
+                     act: bool = False, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """All local experts' GEMMs of a mixture-of-experts block in ONE launch (decode batches,
+    ``b200_w4a16_moe_grouped_gemm``).  ``kernels`` / ``scaling_factors`` / ``zeros``: one tensor
+    per local expert (B200 layout, identical shapes).  ``x``: ``[M, K]`` (every expert reads it)
+    or ``[E, M, K]`` (expert e reads ``x[e]``).  ``counts``: int32 ``[E]`` on the device, tokens
+    routed to each local expert; experts with a zero count are skipped and their slice of the
+    result is left unwritten.  Returns ``[E, M, N]`` (``[E, M, N / 2]`` with ``act``: SiLU-and-
+    multiply over channel-paired gate / up weights in the epilogue)."""
+    E = len(kernels)
+    if E == 0 or len(scaling_factors) != E or len(zeros) != E:
+        raise ValueError("moe_grouped_gemm: one kernel / scales / zeros tensor per expert")
+    dev = _check_cuda(x, counts, *kernels, *scaling_factors, *zeros)
+    per_expert_x = x.dim() == 3
+    if (per_expert_x and x.shape[0] != E) or x.dim() not in (2, 3) or not x.is_contiguous():
+        raise ValueError("moe_grouped_gemm: x must be contiguous [M, K] or [E, M, K]")
+    M, K = x.shape[-2], x.shape[-1]
+    N = scaling_factors[0].shape[1]
+    G = K // scaling_factors[0].shape[0] if scaling_factors[0].shape[0] else 0
+    if x.dtype != torch.float16 or counts.dtype != torch.int32 or counts.numel() != E:
+        raise ValueError("moe_grouped_gemm: x float16, counts int32 [E]")
+    L = _lib.lib()
+    for k, s, z in zip(kernels, scaling_factors, zeros):
+        if k.dtype != torch.int32 or z.dtype != torch.int32 or s.dtype != torch.float16:
+            raise ValueError("kernel and zeros must be int32, scaling_factors float16")
+        if s.shape != scaling_factors[0].shape or k.numel() != L.b200_w4a16_repacked_words(K, N) \
+                or z.shape != (K // G if G else 0, N // PACK_FACTOR):
+            raise ValueError("moe_grouped_gemm: the experts must share one shape (B200 layout)")
+    NO = N // 2 if act else N
+    if out is None:
+        out = torch.empty((E, M, NO), dtype=torch.float16, device=dev)
+    elif out.shape != (E, M, NO) or out.dtype != torch.float16 or not out.is_contiguous():
+        raise ValueError("moe_grouped_gemm: out must be contiguous float16 [E, M, N']")
+    vp = ctypes.c_void_p
+    ptrs = [(vp * E)(*[t.data_ptr() for t in ts]) for ts in (kernels, scaling_factors, zeros)]
+    with torch.cuda.device(dev):
+        ws = _workspace(dev, L.b200_w4a16_workspace_bytes(M, K, N, LAYOUT_B200))
+        st = L.b200_w4a16_moe_grouped_gemm(x.data_ptr(), ptrs[0], ptrs[1], ptrs[2], out.data_ptr(),
+                                           M, K, N, G, E, counts.data_ptr(),
+                                           M * K if per_expert_x else 0, 1 if act else 0,
+                                           ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _lib.check(st, "moe_grouped_gemm")
+    return out
+
+
+def moe_combine(y: torch.Tensor, w: torch.Tensor, counts: torch.Tensor) -> torch.Tensor:
+    """``sum_e half(y[e] * w[:, e])`` over the experts with ``counts[e] > 0``, in index order with
+    the reference's roundings (``mul_`` then ``add_`` per expert, mixtral_quant.py:152-157).
+    ``y``: ``[E, T, hidden]`` float16, ``w``: fp32 ``[T, >= E]`` (column e = expert e's routing
+    weight per token; may be a column slice of a wider matrix), ``counts``: int32 ``[E]``."""
+    dev = _check_cuda(y, counts)
+    if not w.is_cuda or w.device != dev:
+        raise RuntimeError("all tensors must be on the same CUDA device")
+    if y.dtype != torch.float16 or w.dtype != torch.float32 or counts.dtype != torch.int32:
+        raise ValueError("moe_combine: y float16, w float32, counts int32")
+    if y.dim() != 3 or w.dim() != 2 or w.shape[0] != y.shape[1] or w.shape[1] != y.shape[0] \
+            or w.stride(1) != 1 or counts.numel() != y.shape[0] or not y.is_contiguous():
+        raise ValueError("moe_combine: y [E, T, hidden], w [T, E] (unit column stride), counts [E]")
+    out = torch.empty(y.shape[1:], dtype=torch.float16, device=dev)
+    with torch.cuda.device(dev):
+        st = _lib.lib().b200_w4a16_moe_combine(y.data_ptr(), w.data_ptr(), counts.data_ptr(),
+                                               out.data_ptr(), y.shape[0], max(w.stride(0), y.shape[0]),
+                                               y.shape[1], y.shape[2], _stream_ptr(dev))
+    _lib.check(st, "moe_combine")
+    return out
+
+
+def moe_route(x: torch.Tensor, gate_weight: torch.Tensor, top_k: int):
+    """The router in one launch (``b200_w4a16_moe_route``): fp16 gate GEMM, fp32 softmax, top-k,
+    renormalise.  Returns ``(topk_weights [T, k] fp32, topk_experts [T, k] int64, counts [E]
+    int32, dense_weights [T, E] fp32)`` -- the first two are what the reference computes
+    (mixtral_quant.py:133-142), ``counts`` feeds the expert gates, ``dense_weights`` holds each
+    token's weight for every expert (zero where not chosen)."""
+    dev = _check_cuda(x, gate_weight)
+    if x.dtype != torch.float16 or gate_weight.dtype != torch.float16 or x.dim() != 2 \
+            or gate_weight.dim() != 2 or gate_weight.shape[1] != x.shape[1]:
+        raise ValueError("moe_route: x [tokens, hidden] and gate_weight [experts, hidden] float16")
+    T, E = x.shape[0], gate_weight.shape[0]
+    topk_w = torch.empty((T, top_k), dtype=torch.float32, device=dev)
+    topk_idx = torch.empty((T, top_k), dtype=torch.int64, device=dev)
+    dense = torch.empty((T, E), dtype=torch.float32, device=dev)
+    counts = torch.empty((E,), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        st = _lib.lib().b200_w4a16_moe_route(x.data_ptr(), gate_weight.data_ptr(), topk_w.data_ptr(),
+                                             topk_idx.data_ptr(), dense.data_ptr(), counts.data_ptr(),
+                                             T, x.shape[1], E, top_k, _stream_ptr(dev))
+    _lib.check(st, "moe_route")
+    return topk_w, topk_idx, counts, dense
