@@ -255,6 +255,37 @@ int b200_w4a16_moe_grouped_gemm(const uint16_t *x, const int32_t *const *qweight
                                 const int32_t *counts, size_t x_expert_stride, int act,
                                 void *workspace, size_t workspace_bytes, b200_stream_t stream);
 
+/* ---- row sets whose size only the device knows (routed experts under CUDA graphs) ----------
+ * The tokens routed to an expert are counted on the device; reading the count back would
+ * synchronise the host and break graph capture.  These entries take the buffers' row capacity
+ * (`max_rows`) from the host and the LIVE row count from `rows_dev` (device int32, clamped to
+ * [0, max_rows]); rows beyond it are neither read as indices nor written.
+ *
+ * b200_w4a16_gemm_rows: y[r, :] = x[r, :] . dequant(W) for r < *rows_dev (B200 layout; x and y
+ * have max_rows rows; y rows beyond the count are unspecified).  Above 16 rows the tcgen05
+ * kernel derives its token tiles, work items and per-CTA ranges from the live count, so an
+ * expert with few tokens streams its weights once per LIVE token tile; up to 16 rows it is
+ * b200_w4a16_gemm on all max_rows rows.  0 live rows: nothing is streamed.
+ * b200_w4a16_moe_compact: from the router's top-k lists, per local expert e < n_local the tokens
+ * that chose expert first_expert + e, ascending, and their routing weights:
+ * tok[e * tokens + i], w[e * tokens + i] for i < counts[first_expert + e].
+ * Replaces: the argsort + host read of the counts of the routed path above, i.e. the dense loop
+ *           of MixtralMoE.forward (vllm/model_executor/models/mixtral_quant.py:143-157). */
+int b200_w4a16_gemm_rows(const uint16_t *x, const int32_t *qweight, const uint16_t *scales,
+                         const int32_t *qzeros, uint16_t *y, int max_rows, const int32_t *rows_dev,
+                         int K, int N, int G, void *workspace, size_t workspace_bytes,
+                         b200_stream_t stream);
+int b200_w4a16_moe_compact(const int64_t *topk_idx, const float *topk_w, int32_t *tok, float *w,
+                           size_t tokens, int top_k, int first_expert, int n_local,
+                           b200_stream_t stream);
+int b200_w4a16_moe_gather_rows(const uint16_t *x, const int32_t *idx, const int32_t *rows_dev,
+                               uint16_t *out, size_t max_rows, int hidden, b200_stream_t stream);
+int b200_w4a16_moe_scatter_add_rows(const uint16_t *y, const int32_t *idx, const float *w,
+                                    const int32_t *rows_dev, uint16_t *acc, size_t max_rows,
+                                    int hidden, b200_stream_t stream);
+int b200_w4a16_silu_and_mul_rows(const uint16_t *in, uint16_t *out, size_t max_rows,
+                                 const int32_t *rows_dev, int d, int paired, b200_stream_t stream);
+
 /* The router of a mixture-of-experts block as one launch (plus a memset node for `counts`):
  *   logits = half(x[tokens, hidden] . gate_w[n_experts, hidden]^T)     fp32 accumulate, fp16 result
  *   p = softmax(float(logits));  (topk_w, topk_idx) = top_k largest of p, descending;

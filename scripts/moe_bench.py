@@ -44,6 +44,8 @@ def main():
     ap.add_argument("--prefill", action="store_true",
                     help="eager launches (no CUDA graph): batches above 16 tokens take the routed "
                          "gather -> per-expert GEMM -> scatter-add path; compared with the dense loop")
+    ap.add_argument("--routed-on-device-min", type=int, default=None,
+                    help="override MixtralMoE.routed_on_device_min_tokens (graph mode, batches above 16 tokens)")
     args = ap.parse_args()
     hidden, ffn, experts, top_k = 4096, 14336, 8, 2
     cfg = types.SimpleNamespace(num_local_experts=experts, num_experts_per_tok=top_k,
@@ -63,6 +65,8 @@ def main():
     torch.set_default_dtype(torch.float32)
     for moe in blocks:
         fill(moe, gen)
+        if args.routed_on_device_min is not None:
+            moe.routed_on_device_min_tokens = args.routed_on_device_min
     bytes_expert = 3 * (hidden * ffn // 2 + (hidden // G) * ffn * 5 // 2)   # packed + scales + zeros (approx.)
     if args.prefill:
         for moe in blocks:

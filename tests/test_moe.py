@@ -435,3 +435,139 @@ def test_router_kernel_arguments(pkg, cuda_lib):
     with pytest.raises(ValueError):
         pkg.ops.moe_route(torch.zeros((2, 64), dtype=torch.float16, device="cuda"),
                           torch.zeros((33, 64), dtype=torch.float16, device="cuda"), 2)           # > 32 experts
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M_max,K,N", [(32, 512, 384), (64, 1024, 768), (200, 512, 1024), (300, 2048, 256)])
+def test_gemm_with_device_side_row_count(pkg, oracle, cuda_lib, M_max, K, N):
+    """b200_w4a16_gemm_rows: the live rows equal b200_w4a16_gemm on exactly those rows up to the
+    fp32 summation order (other stream-K cut); rows beyond the count are never written, whatever
+    the input holds there (NaN here)."""
+    from gpu_util import to_dev
+    x, qw, s, qz = oracle.make_inputs(M_max, K, N, G, seed=M_max)
+    r, ds, dqz = pkg.ops.quick_repack(to_dev(qw)), to_dev(s), to_dev(qz)
+    dx = to_dev(x)
+    for rows in sorted({0, 1, 17, 32, 33, min(M_max, 129), M_max - 1, M_max, M_max + 50}):
+        live = min(rows, M_max)
+        xin = dx.clone()
+        xin[live:] = float("nan")
+        cnt = torch.tensor([rows], dtype=torch.int32, device="cuda")
+        # run it twice: the second call overwrites a result buffer pre-filled with a sentinel
+        got = pkg.ops.quick_gemm_rows(xin, r, ds, dqz, cnt)
+        torch.cuda.synchronize()
+        if live:
+            want = pkg.ops.quick_gemm(dx[:live].contiguous(), r, ds, dqz, 8)
+            assert _close(got[:live], want), rows
+            assert not torch.isnan(got[:live]).any()
+        again = pkg.ops.quick_gemm_rows(xin, r, ds, dqz, cnt)
+        assert torch.equal(got[:live], again[:live])
+    # the workspace is handed back clean: a plain launch afterwards is unaffected
+    a = pkg.ops.quick_gemm(dx, r, ds, dqz, 8)
+    assert torch.equal(a, pkg.ops.quick_gemm(dx, r, ds, dqz, 8))
+    with pytest.raises(ValueError):
+        pkg.ops.quick_gemm_rows(dx, r, ds, dqz, torch.tensor([1], dtype=torch.int64, device="cuda"))
+
+
+@pytest.mark.gpu
+def test_gemm_rows_never_writes_beyond_the_count(pkg, oracle, cuda_lib):
+    from gpu_util import to_dev
+    M_max, K, N = 160, 512, 256
+    x, qw, s, qz = oracle.make_inputs(M_max, K, N, G, seed=4)
+    r, ds, dqz, dx = pkg.ops.quick_repack(to_dev(qw)), to_dev(s), to_dev(qz), to_dev(x)
+    L = cuda_lib
+    y = torch.full((M_max, N), 3.0, dtype=torch.float16, device="cuda")
+    cnt = torch.tensor([70], dtype=torch.int32, device="cuda")
+    ws = torch.empty(L.b200_w4a16_workspace_bytes(M_max, K, N, 1), dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    assert L.b200_w4a16_workspace_init(ws.data_ptr(), ws.numel(), st) == 0
+    assert L.b200_w4a16_gemm_rows(dx.data_ptr(), r.data_ptr(), ds.data_ptr(), dqz.data_ptr(), y.data_ptr(),
+                                  M_max, cnt.data_ptr(), K, N, G, ws.data_ptr(), ws.numel(), st) == 0
+    torch.cuda.synchronize()
+    assert bool((y[70:] == 3.0).all()) and not bool((y[:70] == 3.0).all())
+    assert L.b200_w4a16_gemm_rows(dx.data_ptr(), r.data_ptr(), ds.data_ptr(), dqz.data_ptr(), y.data_ptr(),
+                                  M_max, None, K, N, G, ws.data_ptr(), ws.numel(), st) == pkg._lib.B200_ERR_BAD_ARG
+
+
+@pytest.mark.gpu
+def test_moe_compact_and_row_counted_helpers(pkg, cuda_lib):
+    from gpu_util import bits, to_dev
+    rng = np.random.default_rng(5)
+    T, E, k, H = 333, 8, 2, 256
+    sel = np.stack([rng.choice(E, k, replace=False) for _ in range(T)]).astype(np.int64)
+    wts = rng.random((T, k)).astype(np.float32)
+    first, n_local = 2, 4
+    tok, w = pkg.ops.moe_compact(torch.from_numpy(sel).cuda(), torch.from_numpy(wts).cuda(), first, n_local)
+    torch.cuda.synchronize()
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    for j in range(n_local):
+        hits = np.argwhere(sel == first + j)
+        n = len(hits)
+        assert np.array_equal(tok[j, :n].cpu().numpy(), hits[:, 0].astype(np.int32))
+        assert np.array_equal(w[j, :n].cpu().numpy(), wts[hits[:, 0], hits[:, 1]])
+        cnt = torch.tensor([n], dtype=torch.int32, device="cuda")
+        g = torch.full((T, H), 9.0, dtype=torch.float16, device="cuda")
+        got = pkg.ops.moe_gather(to_dev(x), tok[j], cnt)
+        assert np.array_equal(bits(got[:n]), x[hits[:, 0]].view(np.uint16))
+        # scatter-add of the live rows only (the rest of tok / w is uninitialised)
+        acc = torch.zeros((T, H), dtype=torch.float16, device="cuda")
+        pkg.ops.moe_scatter_add(acc, got, tok[j], w[j], cnt)
+        want = np.zeros((T, H), dtype=np.float16)
+        want[hits[:, 0]] = (x[hits[:, 0]].astype(np.float32) * wts[hits[:, 0], hits[:, 1], None]).astype(np.float16)
+        assert np.array_equal(bits(acc), want.view(np.uint16))
+        # activation on the live rows only
+        src = to_dev(rng.standard_normal((T, 2 * H)).astype(np.float16))
+        dst = torch.full((T, H), 9.0, dtype=torch.float16, device="cuda")
+        full = torch.empty((T, H), dtype=torch.float16, device="cuda")
+        pkg.ops.silu_and_mul_paired(dst, src, cnt)
+        pkg.ops.silu_and_mul_paired(full, src)
+        assert torch.equal(dst[:n], full[:n]) and bool((dst[n:] == 9.0).all())
+        del g
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tokens", [17, 64, 333])
+def test_moe_block_routed_on_device_matches_dense_and_reference(pkg, oracle, cuda_lib, tokens):
+    """The routed computation with every row count read on the device: against the dense loop,
+    the CPU block, and under CUDA-graph replay with tokens that route differently."""
+    torch.set_default_dtype(torch.float16)
+    try:
+        method = pkg.QuickConfig(4, G, True).get_linear_method()
+        with torch.device("cuda"):
+            moe = pkg.MixtralMoE(_cfg(), method)
+            dense_moe = pkg.MixtralMoE(_cfg(), method, skip_idle_experts=False)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    moe.routed_on_device_min_tokens = 17
+    dense = _fill(moe, oracle, seed=11)
+    _fill(dense_moe, oracle, seed=11)
+    g = torch.Generator().manual_seed(tokens)
+    x = torch.randn(1, tokens, 256, generator=g).half()
+    want, _ = _reference_block(x.reshape(tokens, 256).float(), moe.gate.weight.data.float().cpu(),
+                               dense, list(range(8)), 2, True)
+    calls = []
+    orig = pkg.ops.quick_gemm_rows
+    pkg.ops.quick_gemm_rows = lambda *a: (calls.append(1), orig(*a))[1]
+    try:
+        got = moe(x.cuda()).reshape(tokens, 256)
+    finally:
+        pkg.ops.quick_gemm_rows = orig
+    assert len(calls) == 16                                  # two GEMMs per local expert
+    ref = dense_moe(x.cuda()).reshape(tokens, 256).float()
+    assert bool(((got.float() - ref).abs() <= 2e-2 * ref.abs().clamp(min=1.0)).all())
+    err = (got.float().cpu() - want).abs()
+    assert bool((err <= 2e-2 * want.abs().clamp(min=1.0)).all())
+    assert torch.equal(got, moe(x.cuda()).reshape(tokens, 256))   # deterministic
+
+    st = torch.cuda.Stream()
+    static_x = x.cuda().clone()
+    with torch.cuda.stream(st):
+        moe(static_x)
+        st.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=st):
+            static_y = moe(static_x)
+        x2 = torch.randn(1, tokens, 256, generator=g).half().cuda()
+        static_x.copy_(x2)
+        graph.replay()
+        st.synchronize()
+    assert torch.equal(static_y, moe(x2))

@@ -493,6 +493,90 @@ int b200_w4a16_moe_grouped_gemm(const uint16_t* x, const int32_t* const* qweight
   return e == 0 ? B200_OK : cuda_fail(e);
 }
 
+int b200_w4a16_gemm_rows(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
+                         const int32_t* qzeros, uint16_t* y, int max_rows, const int32_t* rows_dev,
+                         int K, int N, int G, void* workspace, size_t workspace_bytes,
+                         b200_stream_t stream) {
+  if (!gemm_shape_ok(max_rows, K, N, G)) return B200_ERR_BAD_SHAPE;
+  if (max_rows == 0) return B200_OK;
+  if (!rows_dev || (reinterpret_cast<uintptr_t>(rows_dev) & 3u)) return B200_ERR_BAD_ARG;
+  if (max_rows <= b200::kDecodeMaxTokens && G % b200::kTileK == 0)   // decode kernel: all rows
+    return gemm_impl(x, qweight, scales, qzeros, y, max_rows, K, N, G, B200_LAYOUT_B200, 0, nullptr, 0,
+                     workspace, workspace_bytes, stream);
+  if (!x || !qweight || !scales || !qzeros || !y) return B200_ERR_BAD_ARG;
+  if (!aligned16(x) || !aligned16(qweight) || !aligned16(scales) || !aligned16(qzeros) || !aligned16(y))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  b200::GemmPlan plan;
+  if (b200::make_gemm_plan_rows(max_rows, K, N, G, dev.sm_count, &plan)) return B200_ERR_BAD_SHAPE;
+  const size_t part_bytes = align_up(plan.ws_partial_bytes, 256);
+  if (part_bytes > kMaxPartialBytes || !workspace || workspace_bytes < part_bytes || !aligned16(workspace))
+    return B200_ERR_WORKSPACE;
+  int e = b200::launch_gemm(x, qweight, scales, qzeros, y, max_rows, K, N, G, plan, workspace, use_pdl(),
+                            reinterpret_cast<cudaStream_t>(stream), rows_dev);
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+int b200_w4a16_moe_compact(const int64_t* topk_idx, const float* topk_w, int32_t* tok, float* w,
+                           size_t tokens, int top_k, int first_expert, int n_local,
+                           b200_stream_t stream) {
+  if (top_k < 1 || first_expert < 0 || n_local < 1 || tokens * (size_t)top_k > (size_t)0x7fffffff)
+    return B200_ERR_BAD_SHAPE;
+  if (tokens == 0) return B200_OK;
+  if (!topk_idx || !topk_w || !tok || !w || (reinterpret_cast<uintptr_t>(topk_idx) & 7u) ||
+      (reinterpret_cast<uintptr_t>(topk_w) & 3u) || (reinterpret_cast<uintptr_t>(tok) & 3u) ||
+      (reinterpret_cast<uintptr_t>(w) & 3u))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_moe_compact(reinterpret_cast<const long long*>(topk_idx), topk_w, tok, w, tokens,
+                                   top_k, first_expert, n_local, reinterpret_cast<cudaStream_t>(stream));
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+int b200_w4a16_moe_gather_rows(const uint16_t* x, const int32_t* idx, const int32_t* rows_dev,
+                               uint16_t* out, size_t max_rows, int hidden, b200_stream_t stream) {
+  if (hidden <= 0 || hidden % 8 != 0) return B200_ERR_BAD_SHAPE;
+  if (max_rows == 0) return B200_OK;
+  if (!x || !idx || !out || !rows_dev || !aligned16(x) || !aligned16(out) ||
+      (reinterpret_cast<uintptr_t>(idx) & 3u) || (reinterpret_cast<uintptr_t>(rows_dev) & 3u))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_moe_gather(x, idx, out, max_rows, hidden, reinterpret_cast<cudaStream_t>(stream), rows_dev);
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+int b200_w4a16_moe_scatter_add_rows(const uint16_t* y, const int32_t* idx, const float* w,
+                                    const int32_t* rows_dev, uint16_t* acc, size_t max_rows,
+                                    int hidden, b200_stream_t stream) {
+  if (hidden <= 0 || hidden % 8 != 0) return B200_ERR_BAD_SHAPE;
+  if (max_rows == 0) return B200_OK;
+  if (!y || !idx || !w || !acc || !rows_dev || !aligned16(y) || !aligned16(acc) ||
+      (reinterpret_cast<uintptr_t>(idx) & 3u) || (reinterpret_cast<uintptr_t>(w) & 3u) ||
+      (reinterpret_cast<uintptr_t>(rows_dev) & 3u))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_moe_scatter_add(y, idx, w, acc, max_rows, hidden,
+                                       reinterpret_cast<cudaStream_t>(stream), rows_dev);
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
+int b200_w4a16_silu_and_mul_rows(const uint16_t* in, uint16_t* out, size_t max_rows,
+                                 const int32_t* rows_dev, int d, int paired, b200_stream_t stream) {
+  if (d <= 0 || d % 8 != 0 || (paired != 0 && paired != 1)) return B200_ERR_BAD_SHAPE;
+  if (max_rows == 0) return B200_OK;
+  if (!in || !out || !rows_dev || !aligned16(in) || !aligned16(out) ||
+      (reinterpret_cast<uintptr_t>(rows_dev) & 3u))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  int e = b200::launch_silu_and_mul(in, out, max_rows, d, paired, reinterpret_cast<cudaStream_t>(stream), rows_dev);
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
 int b200_w4a16_moe_route(const uint16_t* x, const uint16_t* gate_w, float* topk_w, int64_t* topk_idx,
                          float* dense_w, int32_t* counts, size_t tokens, int hidden, int n_experts,
                          int top_k, b200_stream_t stream) {

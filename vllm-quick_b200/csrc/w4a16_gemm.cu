@@ -174,6 +174,9 @@ struct GemmParams {
   int Gdiv;     // K blocks per group: max(1, G / 128)
   int flags;    // bit 0: no L2 evict-first hint on the weight stream
   uint32_t* trace;  // B200_TRACE builds only: per-CTA event timestamps
+  // DYN instantiations (b200_w4a16_gemm_rows): the number of valid rows of x / y is read from
+  // the device (<= M, the buffers' rows); token tiles, work items and ranges follow it.
+  const int* m_dev;
 };
 
 #ifdef B200_TRACE
@@ -219,7 +222,13 @@ __device__ __forceinline__ Owned find_owned(const Walk& walk, int KB, int P, int
   return r;
 }
 
-template <int MTOK, int PAIR, bool TWO, int TP>
+// DYN: the token count comes from device memory (the routed rows of a mixture-of-experts block:
+// how many tokens chose an expert is only known on the device).  The grid is the one planned
+// for the buffers' M rows; every CTA derives the token tiles, the work-item count and its range
+// from the live count, so an expert with few tokens streams its weights once per LIVE token
+// tile.  Rows beyond the count are never stored (whatever the gather buffer holds there only
+// reaches accumulator columns of its own).
+template <int MTOK, int PAIR, bool TWO, int TP, bool DYN>
 __global__ void __launch_bounds__(kThreads, 1)
 w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
   using C = Cfg<MTOK, PAIR, TWO, TP>;
@@ -228,7 +237,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   // on); the work space is cut per PAIR of CTAs, both walk the same (token tile, K block) steps
   const uint32_t crank = TWO ? cluster_ctarank() : 0u;
   const int vblock = TWO ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
-  const int VP = TWO ? p.P >> 1 : p.P;
+  int VP = TWO ? p.P >> 1 : p.P;
   if (threadIdx.x == 0) { TRG(2); TR(7, 5); }
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -251,10 +260,25 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
+  int M = p.M, MT = p.MT, T = p.T;
+  if constexpr (DYN) {
+    static_assert(!TWO && TP == 1, "dynamic row counts: single-CTA variants only");
+    asm volatile("griddepcontrol.wait;" ::: "memory");        // the count is the previous kernel's output
+    const int m = *reinterpret_cast<const volatile int*>(p.m_dev);
+    M = m < p.M ? m : p.M;
+    if (M <= 0) return;                                       // nobody chose this expert
+    MT = (M + MTOK - 1) / MTOK;
+    T = p.NTP * MT * p.KB;
+    // Fewer work items than CTAs: the first T CTAs take one each.  (Equal ranges over all P would
+    // leave idle CTAs BETWEEN the contributors of a unit; the fix-up takes them to be consecutive.)
+    if (T < VP) VP = T;
+    if (vblock >= VP) return;
+  }
+
   // This CTA's contiguous slice of the work space, and the order it is walked in.  A work item
   // ("unit step") is one K block of one output unit = PAIR channel tiles x one token tile.
-  const int t_begin = range_begin(vblock, p.T, VP);
-  const int t_end = range_begin(vblock + 1, p.T, VP);
+  const int t_begin = range_begin(vblock, T, VP);
+  const int t_end = range_begin(vblock + 1, T, VP);
   const Walk walk(t_begin, t_end, p.KB);
   const int n_units = t_end - t_begin;
   const int n_w = n_units * PAIR;                               // weight tiles in stream order
@@ -270,13 +294,13 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   struct WStream {
     const GemmParams& p;
     const Walk& walk;
-    int crank_;
+    int crank_, MT_;
     int idx, left, h, gcnt;
     uint32_t sb0, zb0, sb1, zb1;                        // scale / zero row bytes of tile h = 0 / 1
     const uint32_t *w0, *w1, *z0, *z1;                  // weight tile, zero row
     const uint16_t *s0, *s1;                            // scale row
-    __device__ __forceinline__ WStream(const GemmParams& pp, const Walk& w, int cr)
-        : p(pp), walk(w), crank_(cr), idx(-1), left(0), h(0), gcnt(0), sb0(0), zb0(0), sb1(0), zb1(0),
+    __device__ __forceinline__ WStream(const GemmParams& pp, const Walk& w, int cr, int mt)
+        : p(pp), walk(w), crank_(cr), MT_(mt), idx(-1), left(0), h(0), gcnt(0), sb0(0), zb0(0), sb1(0), zb1(0),
           w0(nullptr), w1(nullptr), z0(nullptr), z1(nullptr), s0(nullptr), s1(nullptr) {}
     __device__ __forceinline__ void open() {
       h = 0;
@@ -285,7 +309,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       walk.seg(idx, t0, n);
       const int o = t0 / p.KB;
       const int kb = t0 - o * p.KB;
-      const int ntp = o / p.MT;
+      const int ntp = o / MT_;
       left = n;
       const int g0 = p.R > 1 ? kb * p.R : kb / p.Gdiv;
       gcnt = p.R > 1 ? 0 : kb - g0 * p.Gdiv;                  // K blocks into the current group
@@ -336,7 +360,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     }
   };
 
-  WStream cw(p, walk, (int)crank);                          // opened by a producer thread only
+  WStream cw(p, walk, (int)crank, MT);                          // opened by a producer thread only
   if (warp == kProducerWarp) {
     // Lane-parallel barrier init, then the first npre weight tiles go out BEFORE the CTA-wide
     // setup barrier and without ever waiting for the previous kernel: weights never depend on
@@ -410,7 +434,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
         walk.seg(idx, t0, n);
         const int o = t0 / p.KB;
         int k0 = (t0 - o * p.KB) * kTileK;
-        const int m0 = (o % p.MT) * (TP * MTOK) + (TWO ? (int)crank * C::kXRows : 0);   // pair: this CTA's token half
+        const int m0 = (o % MT) * (TP * MTOK) + (TWO ? (int)crank * C::kXRows : 0);   // pair: this CTA's token half
         for (int i = 0; i < n; ++i, ++u, k0 += kTileK) {
           if (u >= C::kXStages) {
             const int g = ((u - C::kXStages) * PAIR + PAIR - 1) / C::kCommit;
@@ -581,7 +605,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
       int t0, n;
       walk.seg(idx, t0, n);
       const int o = t0 / p.KB;
-      const int ntp = o / p.MT, mt = o - ntp * p.MT;
+      const int ntp = o / MT, mt = o - ntp * MT;
       const int d = idx % C::kAccBufs;
       const bool whole = (n == p.KB);
       const int slot = idx == 0 ? 0 : 1;
@@ -606,7 +630,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
 #pragma unroll
               for (int e = 0; e < 16; ++e) {
                 const int m = m0 + cc + e;
-                if (m < p.M)
+                if (m < M)
                   p.y[(size_t)m * p.N + n_glob] =
                       __half_as_ushort(__float2half_rn(__uint_as_float(v[e])));
               }
@@ -636,12 +660,12 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   // this unit FIRST in their walk, so their partials are normally long there; every CTA of the
   // grid is resident (grid <= SM count), so the wait cannot deadlock.
   if (warp < kFirstEpiWarp + kEpiThreads / 32) {
-    const Owned own = find_owned(walk, p.KB, VP, p.T, vblock);
+    const Owned own = find_owned(walk, p.KB, VP, T, vblock);
     if (own.o >= 0) {
       asm volatile("griddepcontrol.wait;" ::: "memory");      // the dequant warps write y here
       constexpr int kPartVec = MTOK * kTileN / 4;
       constexpr int kQuads = kAS * kPartVec;
-      const int ntp = own.o / p.MT, mt = own.o - ntp * p.MT;
+      const int ntp = own.o / MT, mt = own.o - ntp * MT;
       const int nother = own.last - vblock;
       constexpr int kStep = TWO ? 2 : 1;                      // pair: the same-rank CTA of the next pair
       uint4* const mine = p.partials + ((size_t)blockIdx.x * 2 + own.slot) * kQuads;
@@ -705,7 +729,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
                 const float rr[4] = {acc[i].x, acc[i].y, acc[i].z, acc[i].w};
 #pragma unroll
                 for (int u = 0; u < 4; ++u)
-                  if (m + u < p.M) p.y[(size_t)(m + u) * p.N + n_glob] = __half_as_ushort(__float2half_rn(rr[u]));
+                  if (m + u < M) p.y[(size_t)(m + u) * p.N + n_glob] = __half_as_ushort(__float2half_rn(rr[u]));
               }
             }
           }
@@ -748,7 +772,7 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-template <int MTOK, int PAIR, bool TWO = false, int TP = 1>
+template <int MTOK, int PAIR, bool TWO = false, int TP = 1, bool DYN = false>
 int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& plan, bool pdl,
                 cudaStream_t stream) {
   // the opt-in is per device: a process may drive several GPUs
@@ -756,7 +780,7 @@ int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& 
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= kMaxDevices || !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(w4a16_gemm_kernel<MTOK, PAIR, TWO, TP>,
+    cudaError_t e = cudaFuncSetAttribute(w4a16_gemm_kernel<MTOK, PAIR, TWO, TP, DYN>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg<MTOK, PAIR, TWO, TP>::kSmemBytes);
     if (e != cudaSuccess) return (int)e;
@@ -783,7 +807,7 @@ int launch_impl(const GemmParams& prm, const CUtensorMap& tmap, const GemmPlan& 
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  return (int)cudaLaunchKernelEx(&cfg, w4a16_gemm_kernel<MTOK, PAIR, TWO, TP>, prm, tmap);
+  return (int)cudaLaunchKernelEx(&cfg, w4a16_gemm_kernel<MTOK, PAIR, TWO, TP, DYN>, prm, tmap);
 }
 
 int gemm_flags() {
@@ -981,9 +1005,40 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
   return 0;
 }
 
+// Plan for a launch whose live row count is read on the device (<= M_max, the buffers' rows):
+// single-CTA, single-tile variant, token tile by M_max, the grid of the M_max problem.
+int make_gemm_plan_rows(int M_max, int K, int N, int G, int sm_count, GemmPlan* plan) {
+  (void)G;
+  if (sm_count <= 0) sm_count = kMaxCtas;
+  if (sm_count > kMaxCtas) sm_count = kMaxCtas;
+  plan->kind = kKindTcgen05;
+  plan->n_tiles = (N + kTileN - 1) / kTileN;
+  plan->k_blocks = K / kTileK;
+  plan->pair = 1;
+  plan->two_cta = 0;
+  plan->tok_pair = 1;
+  const int tok = M_max <= 32 ? 32 : M_max <= 64 ? 64 : 128;
+  plan->tok_tile = tok;
+  plan->m_tiles = (M_max + tok - 1) / tok;
+  const long long T = (long long)plan->n_tiles * plan->m_tiles * plan->k_blocks;
+  if (T >= (1LL << 31)) return 1;
+  long long ctas = T < sm_count ? T : sm_count;
+  if (ctas < 1) ctas = 1;
+  plan->ctas = (int)ctas;
+  plan->max_split = plan->k_blocks + 1;                     // the live problem may be much smaller
+  plan->ws_partial_bytes = (size_t)ctas * 2 * tok * kTileN * sizeof(float);
+  switch (tok) {
+    case 32: fill_plan<32, 1>(plan); break;
+    case 64: fill_plan<64, 1>(plan); break;
+    default: fill_plan<128, 1>(plan); break;
+  }
+  return 0;
+}
+
 int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                 const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
-                const GemmPlan& plan, void* ws_partials, bool pdl, cudaStream_t stream) {
+                const GemmPlan& plan, void* ws_partials, bool pdl, cudaStream_t stream,
+                const int* m_dev) {
   EncodeTiledFn encode = get_encode_fn();
   if (!encode) return (int)cudaErrorNotSupported;
   CUtensorMap tmap;
@@ -1018,6 +1073,16 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   // and lost: the operand with the long reuse distance is the ACTIVATION matrix, re-read once
   // per channel-tile group; 13824 -> 5120 at 2048 tokens fell from 1144 to 932 TFLOP/s.)
   prm.trace = g_trace;
+  prm.m_dev = m_dev;
+  if (m_dev) {
+    if (plan.two_cta || plan.pair != 1 || plan.tok_pair != 1) return (int)cudaErrorInvalidValue;
+    switch (plan.tok_tile) {
+      case 32: return launch_impl<32, 1, false, 1, true>(prm, tmap, plan, pdl, stream);
+      case 64: return launch_impl<64, 1, false, 1, true>(prm, tmap, plan, pdl, stream);
+      case 128: return launch_impl<128, 1, false, 1, true>(prm, tmap, plan, pdl, stream);
+      default: return (int)cudaErrorInvalidValue;
+    }
+  }
   if (plan.two_cta) {
     if (plan.tok_pair == 2) return launch_impl<128, 1, true, 2>(prm, tmap, plan, pdl, stream);
     if (plan.pair == 2) return launch_impl<128, 2, true>(prm, tmap, plan, pdl, stream);

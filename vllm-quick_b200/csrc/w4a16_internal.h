@@ -41,7 +41,11 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
 // y[M,N] = x[M,K] . dequant(W) with W in the B200 layout.  Returns cudaError_t.
 int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scales,
                 const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
-                const GemmPlan& plan, void* ws_partials, bool pdl, cudaStream_t stream);
+                const GemmPlan& plan, void* ws_partials, bool pdl, cudaStream_t stream,
+                const int* m_dev = nullptr);
+// The same with the live row count (<= M, the buffers' rows) read on the device: plan with
+// make_gemm_plan_rows, pass the count's address as m_dev (tcgen05 kernel, single-tile variants).
+int make_gemm_plan_rows(int M_max, int K, int N, int G, int sm_count, GemmPlan* plan);
 
 // Row-parallel fusion of the decode kernel with the all-reduce (w4a16_decode.cu): where in the
 // ranks' peer-mapped regions the fused path keeps its epoch counter, per-tile flags and slots.
@@ -93,7 +97,7 @@ int launch_moe_route(const uint16_t* x, const uint16_t* gate_w, float* topk_w, l
 // silu(x[:, :d]) * x[:, d:] (paired == 0: the reference's [gate | up] halves) or, paired == 1,
 // the channel-paired order the fused gate_up GEMM uses (every 16 channels = 8 gate + 8 up).
 int launch_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int d, int paired,
-                        cudaStream_t stream);
+                        cudaStream_t stream, const int32_t* rows_dev = nullptr);
 
 // NVLink peer-memory all-reduce (w4a16_allreduce.cu).  Region = header + two data slots.
 // Region layout: [0, 2 KiB) flags[block][rank] | [2 KiB, +256) per-block epochs |
@@ -133,10 +137,14 @@ int launch_allreduce_add_rmsnorm(void* const* regions, int rank, int world, cons
 
 // Routed mixture-of-experts plumbing (w4a16_moe.cu): out[i] = x[idx[i]];
 // acc[idx[i]] = half(acc[idx[i]] + half(y[i] * w[i])).  hidden % 8 == 0, idx rows distinct.
+// rows_dev (optional, device): the live row count, <= rows -- for row sets only the device knows.
 int launch_moe_gather(const uint16_t* x, const int32_t* idx, uint16_t* out, size_t rows, int hidden,
-                      cudaStream_t stream);
+                      cudaStream_t stream, const int32_t* rows_dev = nullptr);
 int launch_moe_scatter_add(const uint16_t* y, const int32_t* idx, const float* w, uint16_t* acc,
-                           size_t rows, int hidden, cudaStream_t stream);
+                           size_t rows, int hidden, cudaStream_t stream, const int32_t* rows_dev = nullptr);
+// tok[e][0 .. counts[first + e]) = tokens that chose local expert e (ascending), w = their weights.
+int launch_moe_compact(const long long* topk_idx, const float* topk_w, int32_t* tok, float* w,
+                       size_t tokens, int top_k, int first, int n_local, cudaStream_t stream);
 
 // B200_TRACE builds: device buffer of 148 x 8 x 64 uint32 timestamps (nullptr = off).
 void set_trace_buffer(uint32_t* dev);

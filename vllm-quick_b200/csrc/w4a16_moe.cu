@@ -22,8 +22,13 @@ namespace {
 
 __global__ void __launch_bounds__(256)
 moe_gather_kernel(const uint4* __restrict__ x, const int32_t* __restrict__ idx,
-                  uint4* __restrict__ out, size_t total_chunks, uint32_t chunks_per_row) {
+                  uint4* __restrict__ out, size_t total_chunks, uint32_t chunks_per_row,
+                  const int32_t* __restrict__ rows_dev) {
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (rows_dev) {                                             // live rows known on the device only
+    const size_t live = (size_t)max(*rows_dev, 0) * chunks_per_row;
+    if (live < total_chunks) total_chunks = live;
+  }
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks;
        i += (size_t)gridDim.x * blockDim.x) {
     const size_t r = i / chunks_per_row;
@@ -35,8 +40,12 @@ moe_gather_kernel(const uint4* __restrict__ x, const int32_t* __restrict__ idx,
 __global__ void __launch_bounds__(256)
 moe_scatter_add_kernel(const uint4* __restrict__ y, const int32_t* __restrict__ idx,
                        const float* __restrict__ w, uint4* __restrict__ acc, size_t total_chunks,
-                       uint32_t chunks_per_row) {
+                       uint32_t chunks_per_row, const int32_t* __restrict__ rows_dev) {
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (rows_dev) {
+    const size_t live = (size_t)max(*rows_dev, 0) * chunks_per_row;
+    if (live < total_chunks) total_chunks = live;
+  }
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks;
        i += (size_t)gridDim.x * blockDim.x) {
     const size_t r = i / chunks_per_row;
@@ -176,6 +185,43 @@ moe_route_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_w, 
     if (e < E) dense_w[(size_t)t * E + e] = ((taken >> e) & 1u) ? prob[e] / ksum : 0.f;
 }
 
+// Per local expert, the tokens that chose it (ascending) and their routing weights, from the
+// router's top-k lists: CTA e scans the (token, choice) pairs in order, a block-wide prefix sum
+// gives every hit its row.  tok / w: [n_local][tokens].  A token names an expert at most once.
+constexpr int kCompactThreads = 256;
+__global__ void __launch_bounds__(kCompactThreads)
+moe_compact_kernel(const long long* __restrict__ topk_idx, const float* __restrict__ topk_w,
+                   int32_t* __restrict__ tok, float* __restrict__ w, int tokens, int top_k, int first) {
+  __shared__ int warp_sum[kCompactThreads / 32];
+  __shared__ int base_s;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const int e = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int total = tokens * top_k;
+  if (threadIdx.x == 0) base_s = 0;
+  __syncthreads();
+  for (int i0 = 0; i0 < total; i0 += kCompactThreads) {
+    const int i = i0 + threadIdx.x;
+    const bool hit = i < total && topk_idx[i] == (long long)(first + e);
+    const unsigned m = __ballot_sync(0xffffffffu, hit);
+    if (lane == 0) warp_sum[warp] = __popc(m);
+    __syncthreads();
+    int before = base_s;
+    for (int q = 0; q < warp; ++q) before += warp_sum[q];
+    if (hit) {
+      const int pos = before + __popc(m & ((1u << lane) - 1u));
+      tok[(size_t)e * tokens + pos] = i / top_k;
+      w[(size_t)e * tokens + pos] = topk_w[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+      for (int q = 0; q < kCompactThreads / 32; ++q) t += warp_sum[q];
+      base_s += t;
+    }
+    __syncthreads();
+  }
+}
+
 // The small kernels start with griddepcontrol.wait: launched programmatically their launch
 // latency hides behind the tail of the kernel before them.
 template <typename... KArgs, typename... Args>
@@ -201,17 +247,23 @@ unsigned grid_for(size_t total) {
 }  // namespace
 
 int launch_moe_gather(const uint16_t* x, const int32_t* idx, uint16_t* out, size_t rows, int hidden,
-                      cudaStream_t stream) {
+                      cudaStream_t stream, const int32_t* rows_dev) {
   const size_t total = rows * (size_t)(hidden / 8);
   return launch_pdl(moe_gather_kernel, grid_for(total), 256, stream, reinterpret_cast<const uint4*>(x), idx,
-                    reinterpret_cast<uint4*>(out), total, (uint32_t)(hidden / 8));
+                    reinterpret_cast<uint4*>(out), total, (uint32_t)(hidden / 8), rows_dev);
 }
 
 int launch_moe_scatter_add(const uint16_t* y, const int32_t* idx, const float* w, uint16_t* acc,
-                           size_t rows, int hidden, cudaStream_t stream) {
+                           size_t rows, int hidden, cudaStream_t stream, const int32_t* rows_dev) {
   const size_t total = rows * (size_t)(hidden / 8);
   return launch_pdl(moe_scatter_add_kernel, grid_for(total), 256, stream, reinterpret_cast<const uint4*>(y),
-                    idx, w, reinterpret_cast<uint4*>(acc), total, (uint32_t)(hidden / 8));
+                    idx, w, reinterpret_cast<uint4*>(acc), total, (uint32_t)(hidden / 8), rows_dev);
+}
+
+int launch_moe_compact(const long long* topk_idx, const float* topk_w, int32_t* tok, float* w,
+                       size_t tokens, int top_k, int first, int n_local, cudaStream_t stream) {
+  return launch_pdl(moe_compact_kernel, (unsigned)n_local, kCompactThreads, stream, topk_idx, topk_w, tok, w,
+                    (int)tokens, top_k, first);
 }
 
 int launch_moe_route(const uint16_t* x, const uint16_t* gate_w, float* topk_w, long long* topk_idx,

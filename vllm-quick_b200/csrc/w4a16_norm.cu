@@ -398,8 +398,12 @@ namespace {
 // weight was channel-paired for the fused epilogue (used for batches above the decode kernel).
 __global__ void __launch_bounds__(256)
 silu_and_mul_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, size_t total_chunks,
-                    uint32_t chunks_per_row, int paired) {
+                    uint32_t chunks_per_row, int paired, const int32_t* __restrict__ rows_dev) {
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (rows_dev) {                                             // live rows known on the device only
+    const size_t live = (size_t)max(*rows_dev, 0) * chunks_per_row;
+    if (live < total_chunks) total_chunks = live;
+  }
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_chunks;
        i += (size_t)gridDim.x * blockDim.x) {
     const size_t r = i / chunks_per_row;
@@ -421,12 +425,12 @@ silu_and_mul_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, size_
 }  // namespace
 
 int launch_silu_and_mul(const uint16_t* in, uint16_t* out, size_t rows, int d, int paired,
-                        cudaStream_t stream) {
+                        cudaStream_t stream, const int32_t* rows_dev) {
   const size_t total = rows * (size_t)(d / 8);
   size_t blocks = (total + 255) / 256;
   if (blocks > (size_t)kMaxCtas * 8) blocks = (size_t)kMaxCtas * 8;
   silu_and_mul_kernel<<<(unsigned)blocks, 256, 0, stream>>>(
-      reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), total, (uint32_t)(d / 8), paired);
+      reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), total, (uint32_t)(d / 8), paired, rows_dev);
   return (int)cudaGetLastError();
 }
 

@@ -22,6 +22,10 @@ What runs instead of the reference's three GEMMs + four eager tensor ops per exp
   and contributes zeros.  No host synchronisation: the block stays CUDA-graph capturable.
 * prefill batches outside graph capture gather each expert's tokens, run the expert on M_e rows
   instead of T, and scatter-add the weighted result (one host read of the counts).
+* in between, and under graph capture at any size, the same routed computation runs with the
+  per-expert row counts read ON THE DEVICE by every kernel (``ops.quick_gemm_rows`` and friends).
+* decode batches: the router is one kernel, all local experts with tokens run as ONE grouped
+  launch per projection, one pass accumulates their weighted outputs.
 """
 from __future__ import annotations
 
@@ -127,6 +131,10 @@ class MixtralMoE(nn.Module):
     # Up to here (the decode kernel's batch sizes) the local experts run as ONE grouped launch
     # per projection instead of one launch per expert.
     grouped_max_tokens = 16
+    # From here up (below routed_min_tokens, or at any size under CUDA-graph capture) the routed
+    # path runs with the row counts read on the device: even at 32-64 tokens, 1.37x ahead from 96
+    # (profiles/r3p_moe_mid_epr{1,8}.jsonl, r3q_moe_mid_epr1.jsonl).
+    routed_on_device_min_tokens = 65
 
     def __init__(self, config, linear_method: Optional[LinearMethodBase] = None,
                  skip_idle_experts: bool = True):
@@ -241,6 +249,30 @@ class MixtralMoE(nn.Module):
                                     device=hidden_states.device).scatter_(1, selected_experts, routing_weights)
         return ops.moe_combine(out, per_token[:, first:first + n_local], local_counts)
 
+    def _forward_routed_on_device(self, hidden_states, routing_weights, selected_experts, counts, dense_w=None):
+        """The routed path without the host ever seeing the routing (CUDA-graph capturable): the
+        tokens of every local expert are compacted on the device, and gather, the expert's GEMMs,
+        the activation and the scatter-add all take the live row count from ``counts`` on the
+        device -- the GEMM derives its token tiles from it (``ops.quick_gemm_rows``), so an expert
+        streams its weights once per LIVE token tile instead of once per tile of the batch."""
+        tokens = hidden_states.shape[0]
+        first, n_local = self.expert_indicies[0], len(self.expert_indicies)
+        tok, w = ops.moe_compact(selected_experts, routing_weights, first, n_local)
+        final = torch.zeros_like(hidden_states)
+        for j, expert_idx in enumerate(self.expert_indicies):
+            mlp = self.experts[expert_idx]
+            mlp.process_weights_after_loading()
+            rows = counts[expert_idx:expert_idx + 1]
+            gate_up, down = mlp._w13, mlp.w2.linear_weights
+            x_e = ops.moe_gather(hidden_states, tok[j], rows)
+            h = ops.quick_gemm_rows(x_e, gate_up["qweight"].data, gate_up["scales"].data,
+                                    gate_up["qzeros"].data, rows)
+            act = torch.empty((tokens, h.shape[1] // 2), dtype=h.dtype, device=h.device)
+            ops.silu_and_mul_paired(act, h, rows)
+            out = ops.quick_gemm_rows(act, down["qweight"].data, down["scales"].data, down["qzeros"].data, rows)
+            ops.moe_scatter_add(final, out, tok[j], w[j], rows)
+        return final
+
     def _forward_dense(self, hidden_states, routing_weights, selected_experts, counts, dense_w=None):
         """Every local expert on every token (the reference's structure); experts without tokens
         are skipped on the device, the weighted accumulation is one kernel per expert."""
@@ -273,5 +305,9 @@ class MixtralMoE(nn.Module):
         body = self._forward_routed if routed else self._forward_dense
         if not routed and self._can_group(hidden_states):
             body = self._forward_grouped
+        elif (not routed and self.skip_idle_experts and hidden_states.is_cuda
+              and hidden_states.shape[0] >= self.routed_on_device_min_tokens
+              and hasattr(self.experts[self.expert_indicies[0]].linear_method, "apply_weights_silu_and_mul")):
+            body = self._forward_routed_on_device
         final = body(hidden_states, routing_weights, selected_experts, counts, dense_w)
         return tensor_model_parallel_all_reduce(final).view(batch_size, sequence_length, hidden_dim)

@@ -299,17 +299,28 @@ def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torc
     _lib.check(st, "fused_add_rms_norm")
 
 
-def _silu(out: torch.Tensor, input: torch.Tensor, paired: int) -> None:
+def _rows_ptr(rows: Optional[torch.Tensor], dev: torch.device) -> int:
+    """Device int32 scalar holding a live row count (routed experts: known on the device only)."""
+    if not rows.is_cuda or rows.device != dev or rows.dtype != torch.int32 or rows.numel() != 1:
+        raise ValueError("rows must be a one-element int32 tensor on the same device")
+    return rows.data_ptr()
+
+
+def _silu(out: torch.Tensor, input: torch.Tensor, paired: int, rows: Optional[torch.Tensor] = None) -> None:
     dev = _check_cuda(out, input)
     if out.dtype != torch.float16 or input.dtype != torch.float16:
         raise ValueError("the B200 activation kernels take float16 tensors only")
     d = input.shape[-1] // 2
     if input.shape[-1] != 2 * d or out.shape != input.shape[:-1] + (d,):
         raise ValueError("silu_and_mul: out must be [..., d] for input [..., 2 * d]")
+    n_rows = input.numel() // (2 * d) if d else 0
     with torch.cuda.device(dev):
-        st = _lib.lib().b200_w4a16_silu_and_mul(input.data_ptr(), out.data_ptr(),
-                                                input.numel() // (2 * d) if d else 0, d, paired,
-                                                _stream_ptr(dev))
+        if rows is None:
+            st = _lib.lib().b200_w4a16_silu_and_mul(input.data_ptr(), out.data_ptr(), n_rows, d, paired,
+                                                    _stream_ptr(dev))
+        else:
+            st = _lib.lib().b200_w4a16_silu_and_mul_rows(input.data_ptr(), out.data_ptr(), n_rows,
+                                                         _rows_ptr(rows, dev), d, paired, _stream_ptr(dev))
     _lib.check(st, "silu_and_mul")
 
 
@@ -319,10 +330,11 @@ def silu_and_mul(out: torch.Tensor, input: torch.Tensor) -> None:
     _silu(out, input, 0)
 
 
-def silu_and_mul_paired(out: torch.Tensor, input: torch.Tensor) -> None:
+def silu_and_mul_paired(out: torch.Tensor, input: torch.Tensor, rows: Optional[torch.Tensor] = None) -> None:
     """The same on the channel-paired order a paired gate_up weight produces (every 16
-    channels = 8 gate + the 8 up channels of the same indices)."""
-    _silu(out, input, 1)
+    channels = 8 gate + the 8 up channels of the same indices).  ``rows``: device int32 scalar,
+    only that many leading rows are processed."""
+    _silu(out, input, 1, rows)
 
 
 def quick_gemm_silu_mul(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_factors: torch.Tensor,
@@ -359,21 +371,29 @@ def quick_gemm_silu_mul(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_fa
     return out
 
 
-def moe_gather(x: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
-    """``x[idx]`` for an int32 index vector: the tokens routed to one expert as a dense batch."""
+def moe_gather(x: torch.Tensor, idx: torch.Tensor, rows: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``x[idx]`` for an int32 index vector: the tokens routed to one expert as a dense batch.
+    ``rows`` (device int32 scalar): only ``idx[:rows]`` is valid -- the other rows of the result
+    are left unwritten (``b200_w4a16_moe_gather_rows``)."""
     dev = _check_cuda(x, idx)
     if x.dtype != torch.float16 or idx.dtype != torch.int32 or x.dim() != 2 or idx.dim() != 1:
         raise ValueError("moe_gather: x [tokens, hidden] float16, idx [rows] int32")
     out = torch.empty((idx.numel(), x.shape[1]), dtype=torch.float16, device=dev)
     with torch.cuda.device(dev):
-        st = _lib.lib().b200_w4a16_moe_gather(x.data_ptr(), idx.data_ptr(), out.data_ptr(),
-                                              idx.numel(), x.shape[1], _stream_ptr(dev))
+        if rows is None:
+            st = _lib.lib().b200_w4a16_moe_gather(x.data_ptr(), idx.data_ptr(), out.data_ptr(),
+                                                  idx.numel(), x.shape[1], _stream_ptr(dev))
+        else:
+            st = _lib.lib().b200_w4a16_moe_gather_rows(x.data_ptr(), idx.data_ptr(), _rows_ptr(rows, dev),
+                                                       out.data_ptr(), idx.numel(), x.shape[1], _stream_ptr(dev))
     _lib.check(st, "moe_gather")
     return out
 
 
-def moe_scatter_add(acc: torch.Tensor, y: torch.Tensor, idx: torch.Tensor, w: torch.Tensor) -> None:
-    """In place: ``acc[idx[i]] += half(y[i] * w[i])`` (w fp32; rows of idx distinct)."""
+def moe_scatter_add(acc: torch.Tensor, y: torch.Tensor, idx: torch.Tensor, w: torch.Tensor,
+                    rows: Optional[torch.Tensor] = None) -> None:
+    """In place: ``acc[idx[i]] += half(y[i] * w[i])`` (w fp32; rows of idx distinct), for
+    ``i < rows`` when a device-side row count is given."""
     dev = _check_cuda(acc, y, idx, w)
     if (acc.dtype != torch.float16 or y.dtype != torch.float16 or idx.dtype != torch.int32
             or w.dtype != torch.float32):
@@ -382,9 +402,14 @@ def moe_scatter_add(acc: torch.Tensor, y: torch.Tensor, idx: torch.Tensor, w: to
             or w.numel() != y.shape[0]:
         raise ValueError("moe_scatter_add: y [rows, hidden], idx [rows], w [rows], acc [tokens, hidden]")
     with torch.cuda.device(dev):
-        st = _lib.lib().b200_w4a16_moe_scatter_add(y.data_ptr(), idx.data_ptr(), w.data_ptr(),
-                                                   acc.data_ptr(), y.shape[0], y.shape[1],
-                                                   _stream_ptr(dev))
+        if rows is None:
+            st = _lib.lib().b200_w4a16_moe_scatter_add(y.data_ptr(), idx.data_ptr(), w.data_ptr(),
+                                                       acc.data_ptr(), y.shape[0], y.shape[1],
+                                                       _stream_ptr(dev))
+        else:
+            st = _lib.lib().b200_w4a16_moe_scatter_add_rows(y.data_ptr(), idx.data_ptr(), w.data_ptr(),
+                                                            _rows_ptr(rows, dev), acc.data_ptr(), y.shape[0],
+                                                            y.shape[1], _stream_ptr(dev))
     _lib.check(st, "moe_scatter_add")
 
 
@@ -476,3 +501,47 @@ def moe_route(x: torch.Tensor, gate_weight: torch.Tensor, top_k: int):
                                              T, x.shape[1], E, top_k, _stream_ptr(dev))
     _lib.check(st, "moe_route")
     return topk_w, topk_idx, counts, dense
+
+
+def quick_gemm_rows(in_feats: torch.Tensor, kernel: torch.Tensor, scaling_factors: torch.Tensor,
+                    zeros: torch.Tensor, rows: torch.Tensor) -> torch.Tensor:
+    """``quick_gemm`` on the first ``rows`` rows of ``in_feats`` where ``rows`` is a device int32
+    scalar (``b200_w4a16_gemm_rows``): the work follows the live count without the host ever
+    reading it.  Returns ``[M, N]``; rows beyond the count are unspecified."""
+    dev = _check_cuda(in_feats, kernel, scaling_factors, zeros)
+    if in_feats.dtype != torch.float16 or scaling_factors.dtype != torch.float16:
+        raise ValueError("in_feats and scaling_factors must be float16")
+    if kernel.dtype != torch.int32 or zeros.dtype != torch.int32 or in_feats.dim() != 2:
+        raise ValueError("kernel and zeros must be int32, in_feats [M, K]")
+    M, K = in_feats.shape
+    N = scaling_factors.shape[1]
+    G = K // scaling_factors.shape[0] if scaling_factors.shape[0] else 0
+    L = _lib.lib()
+    if G == 0 or kernel.numel() != L.b200_w4a16_repacked_words(K, N) or zeros.shape != (K // G, N // PACK_FACTOR):
+        raise ValueError("kernel / zeros do not match the B200 layout for these shapes")
+    out = torch.empty((M, N), dtype=torch.float16, device=dev)
+    with torch.cuda.device(dev):
+        ws = _workspace(dev, L.b200_w4a16_workspace_bytes(M, K, N, LAYOUT_B200))
+        st = L.b200_w4a16_gemm_rows(in_feats.data_ptr(), kernel.data_ptr(), scaling_factors.data_ptr(),
+                                    zeros.data_ptr(), out.data_ptr(), M, _rows_ptr(rows, dev), K, N, G,
+                                    ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _lib.check(st, "w4a16 gemm (device-side row count)")
+    return out
+
+
+def moe_compact(topk_experts: torch.Tensor, topk_weights: torch.Tensor, first_expert: int, n_local: int):
+    """Per local expert, the tokens that chose it (ascending) and their routing weights, from
+    the router's ``[T, k]`` lists: ``(tok [n_local, T] int32, w [n_local, T] fp32)``, row e valid
+    up to the expert's token count (``b200_w4a16_moe_compact``; no host synchronisation)."""
+    dev = _check_cuda(topk_experts, topk_weights)
+    if topk_experts.dtype != torch.int64 or topk_weights.dtype != torch.float32 \
+            or topk_experts.dim() != 2 or topk_experts.shape != topk_weights.shape:
+        raise ValueError("moe_compact: topk_experts int64 [T, k], topk_weights float32 [T, k]")
+    T, k = topk_experts.shape
+    tok = torch.empty((n_local, T), dtype=torch.int32, device=dev)
+    w = torch.empty((n_local, T), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        st = _lib.lib().b200_w4a16_moe_compact(topk_experts.data_ptr(), topk_weights.data_ptr(), tok.data_ptr(),
+                                               w.data_ptr(), T, k, first_expert, n_local, _stream_ptr(dev))
+    _lib.check(st, "moe_compact")
+    return tok, w
