@@ -309,6 +309,60 @@ def bench_gemm_list(torch, pkg, dev, gemms, iters=10, warm=3, seed=7):
     return {"us_per_launch": ms * 1e3 / n, "GBps": b / ms / 1e6, "TFLOPs": f / ms / 1e9, "launches": n}
 
 
+def bench_moe_block(torch, pkg, dev, tokens, local_experts=1, blocks=2, iters=10, seed=11):
+    """One Mixtral-8x7B MoE block (router + this rank's experts + accumulation) as a rank of a
+    TP = 8 group holds it (config 5), CUDA-graph replay over `blocks` distinct blocks: the
+    product path against the reference's dense loop (every local expert on every token)."""
+    import types
+    hidden, ffn, experts, top_k, G = 4096, 14336, 8, 2, 128
+    cfg = types.SimpleNamespace(num_local_experts=experts, num_experts_per_tok=top_k,
+                                hidden_size=hidden, intermediate_size=ffn)
+    g = torch.Generator(device=dev).manual_seed(seed)
+    method = pkg.QuickConfig(4, G, True).get_linear_method()
+    torch.set_default_dtype(torch.float16)
+    try:
+        with torch.device(dev):
+            moes = [pkg.MixtralMoE(cfg, method) for _ in range(blocks)]
+    finally:
+        torch.set_default_dtype(torch.float32)
+    for moe in moes:
+        moe.expert_indicies = list(range(local_experts))
+        for e in range(local_experts, experts):
+            moe.experts[e] = None
+        for mlp in moe.experts:
+            if mlp is None:
+                continue
+            for lin in (mlp.w1, mlp.w2, mlp.w3):
+                lin.qweight.data.copy_(torch.randint(-2**31, 2**31 - 1, lin.qweight.shape, dtype=torch.int32, device=dev, generator=g))
+                lin.qzeros.data.copy_(torch.randint(-2**31, 2**31 - 1, lin.qzeros.shape, dtype=torch.int32, device=dev, generator=g))
+                lin.scales.data.copy_((torch.rand(lin.scales.shape, device=dev, generator=g) * 0.004 + 0.001).half())
+        moe.gate.weight.data.copy_(torch.randn(moe.gate.weight.shape, device=dev, generator=g).half())
+    x = torch.randn(1, tokens, hidden, device=dev, generator=g).half()
+    res = {}
+    for name, skip in (("us_per_block", True), ("us_per_block_dense_reference_loop", False)):
+        for moe in moes:
+            moe.skip_idle_experts = skip
+        st = torch.cuda.Stream(device=dev)
+        with torch.cuda.stream(st):
+            for moe in moes:
+                moe(x)
+            st.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=st):
+                for moe in moes:
+                    moe(x)
+            for _ in range(3):
+                graph.replay()
+            st.synchronize()
+            res[name] = time_graph(torch, st, graph, iters) * 1e3 / blocks
+        del graph
+    del moes
+    torch.cuda.empty_cache()
+    res["local_experts"] = local_experts
+    res["tokens"] = tokens
+    return res
+
+
 def run_extras(torch, pkg, dev, peaks):
     """The other BASELINE configs, briefly (N = 1): kernel-only numbers with their roofline
     fraction, so every config of the metric has a driver-visible figure in the default run."""
@@ -323,14 +377,18 @@ def run_extras(torch, pkg, dev, peaks):
         gem = [(n, M, K, N, 2) for (n, K, N, _) in layer_shapes("llama2-70b", 1)]
         r = bench_gemm_list(torch, pkg, dev, gem)
         out[f"config4_llama2-70b_layer_M{M}"] = {**r, "hbm_frac": r["GBps"] / peaks["hbm"]}
-    for M in (512, 2048, 8192):
-        gem = [(n, M, K, N, 2) for (n, K, N, _) in layer_shapes("llama2-13b", 1)]
-        r = bench_gemm_list(torch, pkg, dev, gem, iters=4, warm=2)
-        out[f"config3_llama2-13b_prefill_M{M}"] = {**r, "tensor_frac_burst": r["TFLOPs"] / peaks["tensor_burst"]}
     for M in (8, 64, 256):
         gem = [("w1w3", M, 4096, 28672, 8), ("w2", M, 14336, 4096, 8)]
         r = bench_gemm_list(torch, pkg, dev, gem)
         out[f"config5_mixtral_expert_gemms_M{M}"] = {**r, "hbm_frac": r["GBps"] / peaks["hbm"]}
+    for T in (8, 256):      # the whole MoE block as one rank of the TP = 8 group runs it
+        out[f"config5_mixtral_moe_block_tp8_rank_T{T}"] = bench_moe_block(torch, pkg, dev, T)
+    # the prefill GEMMs last: they drive the GPU into its power cap, and the memory-bound lines
+    # measured right behind them read up to 1.6x slow on some boxes (profiles/r3t_ab_config5.md)
+    for M in (512, 2048, 8192):
+        gem = [(n, M, K, N, 2) for (n, K, N, _) in layer_shapes("llama2-13b", 1)]
+        r = bench_gemm_list(torch, pkg, dev, gem, iters=4, warm=2)
+        out[f"config3_llama2-13b_prefill_M{M}"] = {**r, "tensor_frac_burst": r["TFLOPs"] / peaks["tensor_burst"]}
     return out
 
 
