@@ -199,6 +199,52 @@ def test_pre_interleaved_checkpoint_world_of_one():
     _pre_interleaved_checks(pkg, pl, oracle, 0, 1)
 
 
+def _moe_checks(pkg, oracle, method, rank, world):
+    """Mixture-of-experts block across ranks (mixtral_quant.py:113-118, :159): contiguous expert
+    blocks per rank, parameters for the local experts only, partial sums all-reduced."""
+    import types
+    import torch.nn.functional as F
+    hidden, ffn, experts, top_k = 256, 256, 8, 2
+    cfg = types.SimpleNamespace(num_local_experts=experts, num_experts_per_tok=top_k,
+                                hidden_size=hidden, intermediate_size=ffn)
+    torch.set_default_dtype(torch.float16)
+    try:
+        moe = pkg.MixtralMoE(cfg, method)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    per = experts // world
+    assert moe.expert_indicies == list(range(rank * per, (rank + 1) * per))
+    owned = {int(n.split(".")[1]) for n, _ in moe.named_parameters() if n.startswith("experts.")}
+    assert owned == set(moe.expert_indicies)
+    dense = {}
+    for e in range(experts):                                   # same checkpoint on every rank
+        for j, name in enumerate(("w1", "w2", "w3")):
+            K, N = (ffn, hidden) if name == "w2" else (hidden, ffn)
+            _, qw, s, qz = oracle.make_inputs(1, K, N, G, seed=100 + 10 * e + j)
+            dense[(e, name)] = torch.from_numpy(oracle.dequantize(qw, s, qz).astype(np.float32))
+            if moe.experts[e] is not None:
+                lin = getattr(moe.experts[e], name)
+                lin.qweight.data.copy_(torch.from_numpy(qw))
+                lin.scales.data.copy_(torch.from_numpy(s.view(np.int16)).view(torch.float16))
+                lin.qzeros.data.copy_(torch.from_numpy(qz))
+    g = torch.Generator().manual_seed(5)
+    moe.gate.weight.data = torch.randn(experts, hidden, generator=g) * 0.5
+    x = torch.randn(1, 6, hidden, generator=g)
+    got = moe(x).reshape(6, hidden)                            # all-reduced inside
+    xf = x.reshape(6, hidden)
+    w = F.softmax(xf @ moe.gate.weight.data.t(), dim=1, dtype=torch.float)
+    w, sel = torch.topk(w, top_k, dim=-1)
+    w = w / w.sum(dim=-1, keepdim=True)
+    want = torch.zeros(6, hidden)
+    for e in range(experts):
+        ew = (w * (sel == e)).sum(dim=-1, keepdim=True)
+        want += ((F.silu(xf @ dense[(e, "w1")]) * (xf @ dense[(e, "w3")])) @ dense[(e, "w2")]) * ew
+    assert torch.allclose(got.float(), want, rtol=1e-4, atol=1e-4)
+    with pytest.raises(ValueError):                            # more ranks than experts
+        pkg.MixtralMoE(types.SimpleNamespace(num_local_experts=1, num_experts_per_tok=1, hidden_size=hidden,
+                                             intermediate_size=ffn), method)
+
+
 def _worker(rank, world, port, q):
     try:
         os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -276,6 +322,7 @@ def _worker(rank, world, port, q):
         with pytest.raises(ValueError):
             pl.RowParallelLinear(128, N, bias=False, linear_method=method)  # K/tp not a multiple of G
         _pre_interleaved_checks(pkg, pl, oracle, rank, world)
+        _moe_checks(pkg, oracle, method, rank, world)
         pu.destroy_model_parallel()
         assert pu.get_tensor_model_parallel_world_size() == 1
         dist.destroy_process_group()
