@@ -5,6 +5,10 @@ Times one MoE block (router + experts; CUDA graph over `--layers` distinct block
 weights exceed L2) with idle experts skipped on the device (b200_w4a16_gemm_gated) and with
 the reference's dense loop (every local expert streams its weights for every batch).
 Usage: python scripts/moe_bench.py [--tokens 1,4,16] [--layers 3] [--experts-per-rank 8]
+Under torchrun (WORLD_SIZE > 1) it is the real thing: every rank builds its share of the experts
+(`MixtralMoE`'s own split), the block ends in the tensor-parallel all-reduce (NVLink kernels), time =
+max over ranks, the ranks' results are compared bit for bit:
+  torchrun --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 scripts/moe_bench.py --tokens 1,8,64,256
 """
 import argparse
 import importlib
@@ -47,6 +51,18 @@ def main():
     ap.add_argument("--routed-on-device-min", type=int, default=None,
                     help="override MixtralMoE.routed_on_device_min_tokens (graph mode, batches above 16 tokens)")
     args = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    dist = pu = None
+    if world > 1:
+        import torch.distributed as dist
+        local = int(os.environ.get("LOCAL_RANK", rank))
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        pu = pkg.parallel_utils
+        pu.initialize_model_parallel(world)
+        pu.custom_all_reduce.init_custom_all_reduce(max_bytes=max(int(v) for v in args.tokens.split(",")) * 4096 * 2)
+        args.experts_per_rank = 8 // world
     hidden, ffn, experts, top_k = 4096, 14336, 8, 2
     cfg = types.SimpleNamespace(num_local_experts=experts, num_experts_per_tok=top_k,
                                 hidden_size=hidden, intermediate_size=ffn)
@@ -57,14 +73,17 @@ def main():
     with torch.device("cuda"):
         for _ in range(args.layers):
             moe = pkg.MixtralMoE(cfg, method)
-            # one rank of a wider tensor-parallel group: keep the first n experts only
-            moe.expert_indicies = list(range(args.experts_per_rank))
-            for e in range(args.experts_per_rank, experts):
-                moe.experts[e] = None
+            if world == 1:
+                # one rank of a wider tensor-parallel group: keep the first n experts only
+                moe.expert_indicies = list(range(args.experts_per_rank))
+                for e in range(args.experts_per_rank, experts):
+                    moe.experts[e] = None
             blocks.append(moe)
     torch.set_default_dtype(torch.float32)
     for moe in blocks:
         fill(moe, gen)
+        if world > 1:                      # the router is replicated: same weights on every rank
+            dist.broadcast(moe.gate.weight.data, 0)
         if args.routed_on_device_min is not None:
             moe.routed_on_device_min_tokens = args.routed_on_device_min
     bytes_expert = 3 * (hidden * ffn // 2 + (hidden // G) * ffn * 5 // 2)   # packed + scales + zeros (approx.)
@@ -95,7 +114,10 @@ def main():
         return
     for T in (int(v) for v in args.tokens.split(",")):
         x = torch.randn(1, T, hidden, device="cuda", generator=gen).half()
+        if world > 1:
+            dist.broadcast(x, 0)
         res = {}
+        same = True
         # grouped: one launch per projection over the local experts with tokens (<= 16 tokens);
         # gated: one gated launch per expert; False: the reference's dense loop
         for skip in (True, "gated", False):
@@ -114,6 +136,8 @@ def main():
                 for _ in range(3):
                     graph.replay()
                 st.synchronize()
+                if world > 1:
+                    dist.barrier()
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(st)
                 for _ in range(args.iters):
@@ -121,18 +145,36 @@ def main():
                 e1.record(st)
                 st.synchronize()
             res[skip] = e0.elapsed_time(e1) * 1e3 / (args.iters * len(blocks))
+            if world > 1:
+                t = torch.tensor([res[skip]], device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                res[skip] = float(t)
+                y = blocks[0](x)                             # every rank must hold the same bits
+                ys = [torch.empty_like(y) for _ in range(world)]
+                dist.all_gather(ys, y)
+                same = same and all(torch.equal(ys[0], t_) for t_ in ys)
+            del graph
         active = []
         for moe in blocks:
             _, _, counts = moe.route(x.view(-1, hidden))
             active.append(int((counts[:args.experts_per_rank] > 0).sum()))
         mean_active = sum(active) / len(active)
-        print(json.dumps({"tokens": T, "local_experts": args.experts_per_rank,
+        if rank != 0:
+            continue
+        print(json.dumps({"tokens": T, "local_experts": args.experts_per_rank, "world": world,
+                          "ranks_bit_identical": same,
                           "active_experts_mean": round(mean_active, 2),
                           "us_per_block_skip_idle": round(res[True], 1),
                           "us_per_block_gated_launch_per_expert": round(res["gated"], 1),
                           "us_per_block_dense_reference_loop": round(res[False], 1),
                           "speedup": round(res[False] / res[True], 2),
-                          "GBps_active_weights": round(mean_active * bytes_expert / res[True] / 1e3, 1)}))
+                          "GBps_active_weights": round(mean_active * bytes_expert / res[True] / 1e3, 1)}), flush=True)
+    if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
+        pu.custom_all_reduce.destroy_custom_all_reduce()
+        torch.cuda.synchronize()
+        os._exit(0)
 
 
 if __name__ == "__main__":
