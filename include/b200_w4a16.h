@@ -40,7 +40,9 @@ typedef enum {
   B200_ERR_BAD_ARG = 2,    /* null / misaligned pointer, unknown layout */
   B200_ERR_WORKSPACE = 3,  /* workspace missing, misaligned or smaller than b200_w4a16_workspace_bytes */
   B200_ERR_CUDA = 4,       /* a CUDA runtime / driver call failed (see b200_w4a16_last_cuda_error) */
-  B200_ERR_NO_DEVICE = 5   /* no sm_100 device: the library has no fallback path */
+  B200_ERR_NO_DEVICE = 5,  /* no sm_100 device: the library has no fallback path */
+  B200_ERR_STATIC_LIMIT = 6 /* b200_w4a16_gemm_noalloc: the problem needs more scratch than the
+                               library's built-in array holds (M > B200_NOALLOC_MAX_TOKENS) */
 } b200_status_t;
 
 enum { B200_LAYOUT_AWQ = 0, B200_LAYOUT_B200 = 1 };
@@ -399,6 +401,28 @@ int b200_w4a16_allreduce_add_rms_norm_ll(void *const *regions, int rank, int wor
                                          uint16_t *residual_out, float eps, size_t rows,
                                          int hidden, size_t ll_offset, size_t ll_message_bytes,
                                          int barrier, b200_stream_t stream);
+
+/* ---- GEMM without any caller- or runtime-provided scratch ------------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).
+ *   y[M,N] = x[M,K] . dequant(qweight, scales, qzeros)       qweight in the B200 layout
+ * is b200_w4a16_gemm's decode-batch path (M <= B200_NOALLOC_MAX_TOKENS, G % 128 == 0; same
+ * kernel, same plan, bit-identical result) with the stream-K partial-tile scratch in an array built
+ * into the library: B200_NOALLOC_SCRATCH_BYTES of device memory per GPU that loads the library,
+ * held until the process exits.  The call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine): it clears the part of the array the launch uses (asynchronously,
+ * on `stream`) and launches the kernel.
+ * M > B200_NOALLOC_MAX_TOKENS returns B200_ERR_STATIC_LIMIT (use b200_w4a16_gemm with a
+ * workspace); G % 128 != 0 returns B200_ERR_BAD_SHAPE; other preconditions as b200_w4a16_gemm.
+ * EVERY call on a GPU shares the one array: calls that may overlap on the GPU (different
+ * streams, or graph branches, without an ordering between them) race on it and give wrong
+ * results; calls ordered on one stream are safe. */
+#define B200_NOALLOC_MAX_TOKENS 16
+#define B200_NOALLOC_SCRATCH_BYTES (148u * 2u * 2048u * 4u) /* 2 424 832: [CTA][2 slots][16 x 128 fp32] */
+int b200_w4a16_gemm_noalloc(const uint16_t *x, const int32_t *qweight, const uint16_t *scales,
+                            const int32_t *qzeros, uint16_t *y, int M, int K, int N, int G,
+                            b200_stream_t stream);
 
 #ifdef __cplusplus
 }

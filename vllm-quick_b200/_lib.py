@@ -29,7 +29,7 @@ def use_library(file_name: str) -> None:
     LIB_PATH = os.path.join(_PKG, "lib", file_name)
 
 B200_OK, B200_ERR_BAD_SHAPE, B200_ERR_BAD_ARG, B200_ERR_WORKSPACE, B200_ERR_CUDA, \
-    B200_ERR_NO_DEVICE = range(6)
+    B200_ERR_NO_DEVICE, B200_ERR_STATIC_LIMIT = range(7)
 LAYOUT_AWQ, LAYOUT_B200 = 0, 1
 REPACK_AWQ_TO_B200, REPACK_B200_TO_AWQ = 0, 1
 
@@ -41,7 +41,7 @@ EXPORTS = (
     "b200_w4a16_ar_region_bytes", "b200_w4a16_ar_alloc", "b200_w4a16_ar_free",
     "b200_w4a16_ar_export", "b200_w4a16_ar_import", "b200_w4a16_ar_unimport",
     "b200_w4a16_allreduce", "b200_w4a16_allreduce_twoshot", "b200_w4a16_gemm_allreduce", "b200_w4a16_gemm_gated",
-    "b200_w4a16_moe_gather", "b200_w4a16_moe_scatter_add", "b200_w4a16_moe_grouped_gemm", "b200_w4a16_moe_combine", "b200_w4a16_moe_route", "b200_w4a16_gemm_rows", "b200_w4a16_moe_compact", "b200_w4a16_moe_gather_rows", "b200_w4a16_moe_scatter_add_rows", "b200_w4a16_silu_and_mul_rows", "b200_w4a16_silu_and_mul", "b200_w4a16_gemm_silu_mul", "b200_w4a16_gemm_silu_mul_gated", "b200_w4a16_add_rms_norm", "b200_w4a16_allreduce_add_rms_norm",
+    "b200_w4a16_moe_gather", "b200_w4a16_moe_scatter_add", "b200_w4a16_moe_grouped_gemm", "b200_w4a16_moe_combine", "b200_w4a16_moe_route", "b200_w4a16_gemm_noalloc", "b200_w4a16_gemm_rows", "b200_w4a16_moe_compact", "b200_w4a16_moe_gather_rows", "b200_w4a16_moe_scatter_add_rows", "b200_w4a16_silu_and_mul_rows", "b200_w4a16_silu_and_mul", "b200_w4a16_gemm_silu_mul", "b200_w4a16_gemm_silu_mul_gated", "b200_w4a16_add_rms_norm", "b200_w4a16_allreduce_add_rms_norm",
     "b200_w4a16_allreduce_add_rms_norm_ll", "b200_w4a16_allreduce_ll", "b200_w4a16_workspace_init",
 )
 
@@ -138,6 +138,8 @@ def lib() -> ctypes.CDLL:
     L.b200_w4a16_moe_scatter_add_rows.argtypes = [vp, vp, vp, vp, vp, sz, i32, vp]
     L.b200_w4a16_silu_and_mul_rows.restype = i32
     L.b200_w4a16_silu_and_mul_rows.argtypes = [vp, vp, sz, vp, i32, i32, vp]
+    L.b200_w4a16_gemm_noalloc.restype = i32
+    L.b200_w4a16_gemm_noalloc.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
     L.b200_w4a16_moe_combine.restype = i32
     L.b200_w4a16_moe_combine.argtypes = [vp, vp, vp, vp, i32, i32, sz, i32, vp]
     L.b200_w4a16_silu_and_mul.restype = i32

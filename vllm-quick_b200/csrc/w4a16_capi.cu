@@ -101,6 +101,9 @@ const char* b200_w4a16_strerror(int status) {
     case B200_ERR_WORKSPACE: return "workspace missing, too small or misaligned (initialise it with b200_w4a16_workspace_init)";
     case B200_ERR_CUDA: return "CUDA call failed";
     case B200_ERR_NO_DEVICE: return "no sm_100 device (this library has no fallback path)";
+    case B200_ERR_STATIC_LIMIT:
+      return "b200_w4a16_gemm_noalloc: more than 16 tokens need more scratch than the library's built-in "
+             "array holds (use b200_w4a16_gemm with a workspace)";
     default: return "unknown status";
   }
 }
@@ -705,3 +708,63 @@ int b200_w4a16_allreduce_add_rms_norm_ll(void* const* regions, int rank, int wor
 }
 
 }  // extern "C"
+
+// ---- b200_w4a16_gemm_noalloc: the decode-batch GEMM on scratch built into the library ---------
+// (no counterpart in the reference; see include/b200_w4a16.h).  The array is the decode kernel's
+// partial-tile workspace for the largest plan it is used with: [148 CTAs][2 slots][16 tokens x 128
+// channels] fp32.  Every GPU that loads the library holds its own copy until the process exits.
+namespace {
+
+static __device__ __align__(256) uint8_t g_noalloc_scratch[B200_NOALLOC_SCRATCH_BYTES];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in for the symbol, not a device address:
+// the address a kernel can use comes from cudaGetSymbolAddress, once per device, with that
+// device current.  (A benign race between threads: every thread stores the same value.)
+int noalloc_scratch(int dev, uint8_t** out) {
+  static uint8_t* addr[b200::kMaxDevices] = {};
+  if (dev >= 0 && dev < b200::kMaxDevices && addr[dev]) { *out = addr[dev]; return 0; }
+  void* p = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+  if (e != cudaSuccess || !p) return e != cudaSuccess ? (int)e : (int)cudaErrorInvalidSymbol;
+  if (dev >= 0 && dev < b200::kMaxDevices) addr[dev] = static_cast<uint8_t*>(p);
+  *out = static_cast<uint8_t*>(p);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200_w4a16_gemm_noalloc(const uint16_t* x, const int32_t* qweight, const uint16_t* scales,
+                                       const int32_t* qzeros, uint16_t* y, int M, int K, int N, int G,
+                                       b200_stream_t stream) {
+  if (!gemm_shape_ok(M, K, N, G)) return B200_ERR_BAD_SHAPE;
+  if (M > B200_NOALLOC_MAX_TOKENS) return B200_ERR_STATIC_LIMIT;
+  if (G % b200::kTileK != 0) return B200_ERR_BAD_SHAPE;      // the decode kernel's group sizes
+  if (M == 0) return B200_OK;
+  if (!x || !qweight || !scales || !qzeros || !y) return B200_ERR_BAD_ARG;
+  if (!aligned16(x) || !aligned16(qweight) || !aligned16(scales) || !aligned16(qzeros) || !aligned16(y))
+    return B200_ERR_BAD_ARG;
+  const DeviceInfo dev = device_info();
+  if (dev.status != B200_OK) return dev.status;
+  b200::GemmPlan plan;
+  if (b200::make_gemm_plan(M, K, N, G, 0, dev.sm_count, &plan)) return B200_ERR_BAD_SHAPE;
+  if (plan.kind != b200::kKindDecode) return B200_ERR_STATIC_LIMIT;
+  const size_t part_bytes = align_up(plan.ws_partial_bytes, 256);
+  if (part_bytes > (size_t)B200_NOALLOC_SCRATCH_BYTES) return B200_ERR_STATIC_LIMIT;
+  int cur = 0;
+  cudaError_t ce = cudaGetDevice(&cur);
+  if (ce != cudaSuccess) return cuda_fail((int)ce);
+  uint8_t* scratch = nullptr;
+  int e = noalloc_scratch(cur, &scratch);
+  if (e != 0) return cuda_fail(e);
+  // The array is shared by every call and keeps what the last one left (a launch that faulted
+  // mid-way, another process state after a device reset: zeros): the partial-tile slots must read
+  // "unwritten" (all 0xFF) when the kernel starts, so the part this launch uses is cleared first.
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  ce = cudaMemsetAsync(scratch, 0xFF, part_bytes, s);
+  if (ce != cudaSuccess) return cuda_fail((int)ce);
+  // no programmatic launch: the kernel must not start before the clear has finished
+  e = b200::launch_decode(x, qweight, scales, qzeros, y, M, K, N, G, plan, scratch, /*pdl=*/false, s,
+                          nullptr, nullptr, 0);
+  return e == 0 ? B200_OK : cuda_fail(e);
+}
+
