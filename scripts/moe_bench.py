@@ -93,9 +93,13 @@ def main():
         for T in (int(v) for v in args.tokens.split(",")):
             x = torch.randn(1, T, hidden, device="cuda", generator=gen).half()
             res = {}
-            for skip in (True, False):
+            # True: host-routed (one read of the counts); "device": routed with the counts read on
+            # the device (no synchronisation); False: the reference's dense loop
+            for skip in (True, "device", False):
                 for moe in blocks:
-                    moe.skip_idle_experts = skip
+                    moe.skip_idle_experts = bool(skip)
+                    moe.routed_min_tokens = (1 << 30) if skip == "device" else 17
+                    moe.routed_on_device_min_tokens = 17
                 for moe in blocks:
                     moe(x)
                 torch.cuda.synchronize()
@@ -109,6 +113,7 @@ def main():
                 res[skip] = e0.elapsed_time(e1) * 1e3 / (args.iters * len(blocks))
             print(json.dumps({"mode": "prefill_eager", "tokens": T, "local_experts": args.experts_per_rank,
                               "us_per_block_routed": round(res[True], 1),
+                              "us_per_block_routed_on_device": round(res["device"], 1),
                               "us_per_block_dense_reference_loop": round(res[False], 1),
                               "speedup": round(res[False] / res[True], 2)}), flush=True)
         return

@@ -20,10 +20,12 @@ What runs instead of the reference's three GEMMs + four eager tensor ops per exp
   the whole cost, so the number of tokens routed to each expert is computed on the device and
   handed to the GEMM launches (``ops.expert_gate``): an expert nobody chose streams nothing
   and contributes zeros.  No host synchronisation: the block stays CUDA-graph capturable.
-* prefill batches outside graph capture gather each expert's tokens, run the expert on M_e rows
-  instead of T, and scatter-add the weighted result (one host read of the counts).
-* in between, and under graph capture at any size, the same routed computation runs with the
-  per-expert row counts read ON THE DEVICE by every kernel (``ops.quick_gemm_rows`` and friends).
+* large prefill batches (>= 8192 tokens) outside graph capture gather each expert's tokens, run
+  the expert on M_e rows instead of T, and scatter-add the weighted result (one host
+  read of the counts).
+* from 65 tokens up to there, and under graph capture at any size, the same routed computation
+  runs with the per-expert row counts read ON THE DEVICE by every kernel (``ops.quick_gemm_rows``
+  and friends): no host synchronisation.
 * decode batches: the router is one kernel, all local experts with tokens run as ONE grouped
   launch per projection, one pass accumulates their weighted outputs.
 """
@@ -125,9 +127,11 @@ class MixtralMoE(nn.Module):
     (transformers' MixtralConfig has them).  ``skip_idle_experts=False`` gives the reference's
     dense behaviour (every local expert streams its weights for every batch)."""
 
-    # Batches of at least this many tokens, outside CUDA-graph capture, take the routed path
-    # (where it overtakes the dense loop on B200: profiles/r1e_moe_prefill_bench.jsonl).
-    routed_min_tokens = 512
+    # Batches of at least this many tokens, outside CUDA-graph capture, take the HOST-routed path
+    # (one read of the per-expert counts; every expert GEMM then gets the plan of its exact row
+    # count, CTA pairs included).  Below, the device-routed path is ahead -- no synchronisation:
+    # 1.1-1.8x at 512-4096 tokens, level at 8192 (profiles/r3y_moe_prefill_epr{1,8}.jsonl).
+    routed_min_tokens = 8192
     # Up to here (the decode kernel's batch sizes) the local experts run as ONE grouped launch
     # per projection instead of one launch per expert.
     grouped_max_tokens = 16
