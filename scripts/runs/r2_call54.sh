@@ -1,0 +1,6 @@
+#!/bin/bash
+# round 2, call 54: prologue stamps of the tcgen05 kernel (trace build)
+set -x
+O=gpurun_out
+timeout 200 python scripts/trace_gemm.py --m 64 --k 4096 --n 4096 > $O/r4b_trace_m64_4096x4096.txt 2>&1
+timeout 200 python scripts/trace_gemm.py --m 512 --k 5120 --n 5120 > $O/r4b_trace_m512_5120x5120.txt 2>&1

@@ -76,7 +76,9 @@ def main():
             continue
         base = t[cta, 7, 0]
         rel = lambda v: int(np.int64(v) - np.int64(base)) if v else -1
-        print(f"== CTA {cta}: exit at {rel(t[cta,7,1])} cycles after setup")
+        print(f"== CTA {cta}: exit at {rel(t[cta,7,1])} cycles after setup; prologue (cycles before setup): entry "
+              f"{rel(t[cta,7,5])} walk {rel(t[cta,7,8])} barriers {rel(t[cta,7,9])} cursor {rel(t[cta,7,10])} "
+              f"ring issued {rel(t[cta,7,11])} tmem {rel(t[cta,7,12])} | dependency resolved {rel(t[cta,7,13])}")
         print("  it " + " ".join(f"{n:>10s}" for n in names))
         for it in range(64):
             if not t[cta, 0, it]:

@@ -507,7 +507,8 @@ w4a16_decode_kernel(const DecodeParams p) {
 
       // a partial segment that starts an output tile makes this CTA the tile's owner (every
       // consumer thread tracks it: the deferred fix-up below uses all of them)
-      if (n != p.KB && owner_of(nt * p.KB, p.P, T) == (int)blockIdx.x) {   // at most one per CTA
+      // (the tile's first K block lies in this CTA's range: its start is not before t_begin)
+      if (n != p.KB && nt * p.KB >= t_begin) {                 // at most one per CTA
         own_nt = nt;
         own_slot = idx == 0 ? 0 : 1;
         own_last = owner_of(nt * p.KB + p.KB - 1, p.P, T);

@@ -213,7 +213,7 @@ __device__ __forceinline__ Owned find_owned(const Walk& walk, int KB, int P, int
   for (int idx = 0; idx < nlook; ++idx) {
     int t0, n;
     walk.seg(idx, t0, n);
-    if (n != KB && t0 % KB == 0 && owner_of(t0, P, T) == cta) {
+    if (n != KB && t0 % KB == 0) {                       // t0 lies in this CTA's own range: it owns the unit
       r.o = t0 / KB;
       r.slot = idx == 0 ? 0 : 1;
       r.last = owner_of(t0 + KB - 1, P, T);
@@ -283,6 +283,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
   const int n_units = t_end - t_begin;
   const int n_w = n_units * PAIR;                               // weight tiles in stream order
   const int npre = n_w < C::kWStages ? n_w : C::kWStages;
+  if (threadIdx.x == 0) TR(7, 8);                               // ranges and walk derived
 
   // Weight stream of this CTA: for every unit step of the walk its PAIR weight tiles, every
   // address advanced incrementally -- consecutive K blocks of a channel tile are contiguous in
@@ -376,14 +377,18 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     fence_barrier_init();
     __syncwarp();
     if (elect_one()) {
+      TR(7, 9);                                                 // barriers initialised
       // Let the next kernel in the stream start its own weight prefetch as soon as an SM frees.
       asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
       cw.open();
+      TR(7, 10);                                                // weight cursor opened
       for (int i = 0; i < npre; ++i) { TR(0, i); issue_w(cw, i); cw.next(); }
+      TR(7, 11);                                                // first ring issued
     }
     __syncwarp();
   } else if (warp == kAllocWarp) {
     if (TWO) tmem_alloc_pair<kTmemCols>(tmem_slot); else tmem_alloc<kTmemCols>(tmem_slot);
+    if (lane == 0) TR(7, 12);                                   // TMEM allocated
   }
   tc_fence_before();
   __syncthreads();
@@ -427,6 +432,7 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     if (elect_one()) {
       tma_prefetch_desc(&tmap_x);
       asm volatile("griddepcontrol.wait;" ::: "memory");      // x is the previous kernel's output
+      TR(7, 13);                                                // dependency resolved (activation producer)
       int u = 0;
       uint32_t sb = xring, bar = bar_xfull;
       for (int idx = 0; idx < walk.nseg; ++idx) {
@@ -858,6 +864,63 @@ int forced_two() {
   return -1;
 #endif
 }
+// Grid sizing when the output units are fewer than the SMs (see aligned_workers).
+#ifndef B200_GEMM_SPLIT_CAP
+#define B200_GEMM_SPLIT_CAP 4        // most workers sharing one output unit
+#endif
+#ifndef B200_GEMM_SPLIT_MIN_TOK
+#define B200_GEMM_SPLIT_MIN_TOK 64   // ... from this token tile up (partial tiles of 32 KiB and more)
+#endif
+#ifndef B200_GEMM_ALIGN_PCT
+#define B200_GEMM_ALIGN_PCT 64       // unit-aligned ranges when they keep at least this share of the workers busy
+#endif
+#ifndef B200_DECODE_ALIGN_PCT
+#define B200_DECODE_ALIGN_PCT 80     // the decode kernel: same idea, ...
+#endif
+#ifndef B200_DECODE_ALIGN_MAX_ITEMS
+#define B200_DECODE_ALIGN_MAX_ITEMS 30   // ... for short walks only (tiles per CTA); longer ones balance better over all SMs
+#endif
+int tuning_int(const char* name, int dflt) {
+#ifdef B200_TUNING
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+#else
+  (void)name;
+  return dflt;
+#endif
+}
+int split_cap() { static const int k = tuning_int("B200_W4A16_SPLITCAP", B200_GEMM_SPLIT_CAP); return k; }
+int split_min_tok() { static const int k = tuning_int("B200_W4A16_SPLITMINTOK", B200_GEMM_SPLIT_MIN_TOK); return k; }
+int align_pct() { static const int k = tuning_int("B200_W4A16_ALIGNPCT", B200_GEMM_ALIGN_PCT); return k; }
+int decode_align_pct() { static const int k = tuning_int("B200_W4A16_DALIGNPCT", B200_DECODE_ALIGN_PCT); return k; }
+
+// Stream-K cuts units x KB work items into equal ranges over all workers; when the units are fewer
+// than the workers every unit is shared by workers / units of them, ranges straddle unit borders
+// (two segments per worker) and the unit's owner sums the others' partial tiles through L2 ON ITS
+// OWN while everybody else has left: at 128-token tiles 64 KiB per contributor and channel tile
+// at ~36 B/clk -- 25 us of a 41 us launch on 8192 -> 2560 at 256 tokens
+// (profiles/r4e_trace_m256_8192x2560.txt).  Two remedies, both a smaller grid:
+//   * a cap on the workers per unit (cap > 0): few units with a long K;
+//   * S = floor(workers / units) workers per unit, so that ranges END at unit borders (one
+//     segment per worker, S - 1 contributors, none at S = 1), when that keeps `pct` percent of the
+//     workers busy.
+// Measured, three interleaved repetitions (profiles/r4g_*): 7-25 % on the Llama-2-7B / 13B / 70B-TP8
+// layers at 32-1024 tokens wherever the grid changes, 2.1-2.3x on 8192 -> 1280 at 64-128 tokens,
+// never slower beyond the run-to-run spread; the decode kernel gains 3-11 % on walks of up to 28
+// tiles per CTA (4096 -> 4096 at 16 tokens: 6.44 -> 5.89 us) and loses 1-10 % on longer ones,
+// hence B200_DECODE_ALIGN_MAX_ITEMS.
+// Returns the worker count to use, or 0 to keep them all.
+long long aligned_workers(long long units, int k_blocks, long long workers, int cap, int pct) {
+  if (units <= 0 || units > workers || pct <= 0) return 0;
+  long long S = workers / units;
+  bool capped = false;
+  if (cap > 0 && S > cap) { S = cap; capped = true; }
+  if (S > k_blocks) S = k_blocks;
+  if (S < 1) S = 1;
+  const long long aligned = units * S;
+  if (capped || aligned * 100 >= workers * pct) return aligned;
+  return 0;
+}
 int forced_tp() {
 #ifdef B200_TUNING
   static const int k = [] {
@@ -907,6 +970,10 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
     if (T >= (1LL << 31)) return 1;
     long long ctas = (long long)sm_count * kDecodeCtasPerSm;
     if (T < ctas) ctas = T;
+    {   // unit-aligned ranges on short walks: one segment per CTA, fewer partial tiles to fix up
+      const long long a = aligned_workers(plan->n_tiles, plan->k_blocks, ctas, 0, decode_align_pct());
+      if (a > 0 && T <= a * B200_DECODE_ALIGN_MAX_ITEMS) ctas = a;
+    }
     if (ctas < 1) ctas = 1;
     plan->ctas = (int)ctas;
     const long long per = T / ctas;
@@ -973,6 +1040,17 @@ int make_gemm_plan(int M, int K, int N, int G, int split_k_hint, int sm_count, G
   if (plan->two_cta) {
     const long long workers = T < sm_count / 2 ? T : sm_count / 2;
     ctas = 2 * workers;
+  }
+  // Few output units with a long K (8192 -> 1280: 10 units of 64 K blocks): equal ranges over all
+  // SMs would cut every unit among ~15 CTAs, and its owner would sum that many 32-64 KiB partial
+  // tiles through L2 on its own -- 22 us at 64 tokens for 2 us of bytes.  At these tile sizes the
+  // contributors per unit are capped; the idle SMs cost less than the serial reduction.
+  {
+    const long long units = (long long)ntp * mtp;
+    long long workers = plan->two_cta ? ctas / 2 : ctas;
+    const long long aligned = aligned_workers(units, plan->k_blocks, workers, tok >= split_min_tok() ? split_cap() : 0,
+                                              align_pct());
+    if (aligned > 0) ctas = plan->two_cta ? 2 * aligned : aligned;
   }
   if (ctas < 1) ctas = 1;
   plan->ctas = (int)ctas;

@@ -6,11 +6,37 @@
 
 namespace b200 {
 
-__device__ __forceinline__ int range_begin(int p, int T, int P) {
-  return (int)((long long)p * T / P);
+#ifndef B200_HD
+#ifdef __CUDACC__
+#define B200_HD __host__ __device__ __forceinline__
+#else
+#define B200_HD inline      // tests/streamk_check.cpp compiles this header for the host
+#endif
+#endif
+
+// floor(n / P) for 0 <= n < 2^22, 1 <= P < 2^11 through one float multiply: (n + 0.5) / P is at
+// least 0.5 / P away from an integer, far more than the rounding of the product (2^-22 relative).
+B200_HD unsigned small_div(unsigned n, float inv_p) {
+  return (unsigned)(((float)n + 0.5f) * inv_p);
 }
-__device__ __forceinline__ int owner_of(int t, int P, int T) {
-  return (int)((((long long)t + 1) * P - 1) / T);
+
+// Range p of P equal contiguous ranges of [0, T): begins at floor(p T / P).  Every thread of every
+// CTA evaluates this at kernel entry, on the critical path to the first weight fetch, so no 64-bit
+// division (a ~100-instruction dependent chain): with T = q P + r,
+//   floor(p T / P) = p q + floor(p r / P),   p r < P^2 < 2^22  (P <= 2 x 148).
+B200_HD int range_begin(int p, int T, int P) {
+  const unsigned q = (unsigned)T / (unsigned)P, r = (unsigned)T - q * (unsigned)P;
+  return (int)((unsigned)p * q + small_div((unsigned)p * r, 1.0f / (float)P));
+}
+// The range that holds work item t: floor(((t + 1) P - 1) / T) = the largest p with
+// range_begin(p) <= t.  A float estimate (relative error 2^-21: off by at most one) settled with
+// range_begin.
+B200_HD int owner_of(int t, int P, int T) {
+  int p = (int)(((float)t + 0.5f) * ((float)P / (float)T));
+  if (p > P - 1) p = P - 1;
+  while (p > 0 && range_begin(p, T, P) > t) --p;
+  while (p + 1 < P && range_begin(p + 1, T, P) <= t) ++p;
+  return p;
 }
 
 // The order in which a CTA walks its contiguous work range [t_begin, t_end): the segment
