@@ -114,9 +114,9 @@ def test_no_device_means_no_compute(pkg, cuda_lib):
     # above: tcgen05 stream-K kernel, one persistent CTA per SM
     (2048, 5120, 15360, 128, 148), (8192, 5120, 15360, 128, 148),
     # fewer output units than SMs: a whole number of CTAs per unit when that keeps >= 64 % of the SMs
-    # busy (32 units x 4, 64 x 2, 96 x 1), at most four per unit from 64-token tiles up (10 units x 4)
+    # busy (32 units x 4, 64 x 2, 96 x 1), at most four per unit from 32-token tiles up (10 units x 4)
     (17, 4096, 4096, 32, 128), (64, 11008 // 128 * 128, 4096, 64, 128), (256, 4096, 4096, 128, 128),
-    (64, 4096, 12288, 64, 96), (64, 8192, 1280, 64, 40), (32, 8192, 1280, 32, 140),
+    (64, 4096, 12288, 64, 96), (64, 8192, 1280, 64, 40), (32, 8192, 1280, 32, 40),
     (512, 4096, 4096, 128, 128), (40, 4096, 22016, 64, 148),
 ])
 def test_gemm_plan(pkg, M, K, N, tok, grid):

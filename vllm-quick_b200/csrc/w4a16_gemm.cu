@@ -177,6 +177,7 @@ struct GemmParams {
   // DYN instantiations (b200_w4a16_gemm_rows): the number of valid rows of x / y is read from
   // the device (<= M, the buffers' rows); token tiles, work items and ranges follow it.
   const int* m_dev;
+  int split_cap, align_pct;   // DYN: the planner's grid policy (aligned_workers), applied to the live problem
 };
 
 #ifdef B200_TRACE
@@ -269,6 +270,16 @@ w4a16_gemm_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x
     if (M <= 0) return;                                       // nobody chose this expert
     MT = (M + MTOK - 1) / MTOK;
     T = p.NTP * MT * p.KB;
+    // The planner's grid policy on the live problem (aligned_workers): a whole number of CTAs per
+    // output unit when the live units are fewer than the CTAs.
+    const int units = p.NTP * MT;
+    if (units <= VP && p.align_pct > 0) {
+      int S = VP / units;
+      bool capped = false;
+      if (p.split_cap > 0 && S > p.split_cap) { S = p.split_cap; capped = true; }
+      if (S > p.KB) S = p.KB;
+      if (capped || units * S * 100 >= VP * p.align_pct) VP = units * S;
+    }
     // Fewer work items than CTAs: the first T CTAs take one each.  (Equal ranges over all P would
     // leave idle CTAs BETWEEN the contributors of a unit; the fix-up takes them to be consecutive.)
     if (T < VP) VP = T;
@@ -869,7 +880,7 @@ int forced_two() {
 #define B200_GEMM_SPLIT_CAP 4        // most workers sharing one output unit
 #endif
 #ifndef B200_GEMM_SPLIT_MIN_TOK
-#define B200_GEMM_SPLIT_MIN_TOK 64   // ... from this token tile up (partial tiles of 32 KiB and more)
+#define B200_GEMM_SPLIT_MIN_TOK 32   // ... from this token tile up (partial tiles of 16 KiB and more)
 #endif
 #ifndef B200_GEMM_ALIGN_PCT
 #define B200_GEMM_ALIGN_PCT 64       // unit-aligned ranges when they keep at least this share of the workers busy
@@ -1152,6 +1163,8 @@ int launch_gemm(const uint16_t* x, const int32_t* qw_b200, const uint16_t* scale
   // per channel-tile group; 13824 -> 5120 at 2048 tokens fell from 1144 to 932 TFLOP/s.)
   prm.trace = g_trace;
   prm.m_dev = m_dev;
+  prm.split_cap = plan.tok_tile >= split_min_tok() ? split_cap() : 0;
+  prm.align_pct = align_pct();
   if (m_dev) {
     if (plan.two_cta || plan.pair != 1 || plan.tok_pair != 1) return (int)cudaErrorInvalidValue;
     switch (plan.tok_tile) {
