@@ -65,12 +65,12 @@ class CustomAllreduce:
         # win up to 1 MiB at TP = 2 (r1e_allreduce_norm_bench_tp2.jsonl); not yet measured per
         # size at TP = 8, so stay at the size the one-shot kernel was already trusted with there
         self.ll_max_bytes = (1 << 20) if self.world <= 2 else (512 << 10)
-        # Row-parallel decode GEMMs: at TP = 2 GEMM then packet all-reduce (two launches) beats
-        # the fused GEMM + all-reduce kernel, whose tile exchange still pays a system fence and a
-        # flag round trip per tile (7.37 vs 8.26 ms per Llama-2-70B decode step); at TP = 8 the
-        # fused kernel's overlap wins (5.85 vs 6.33 ms: seven peers' packets at twice the bytes).
-        # profiles/r1e_bench_tp{2,8}_*.json.  TP = 4 not measured: treated like 8.
-        self.prefer_fused_gemm = self.world > 2
+        # Row-parallel decode GEMMs: the fused GEMM + all-reduce kernel at every TP.  (Round 1, when
+        # its tile exchange still paid a system fence and a flag round trip per tile, GEMM then
+        # packet all-reduce won at TP = 2: 7.37 vs 8.26 ms per Llama-2-70B decode step.  With the
+        # tiles travelling as packets the fused kernel is ahead there too: 6.15 vs 6.96 ms,
+        # profiles/r4j_bench_tp2{,_fused}.json; TP = 4 / 8: 4.46 / 4.26 vs 6.01 / 6.32 ms, r2r / r3a.)
+        self.prefer_fused_gemm = True
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.fused_out_features = int(fused_out_features)
         region_bytes = L.b200_w4a16_ar_region_bytes(self.max_bytes, self.world, self.fused_out_features)
