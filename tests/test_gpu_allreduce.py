@@ -226,8 +226,10 @@ def _rank_main(rank, world, port, q):
         pu.custom_all_reduce.init_custom_all_reduce(max_bytes=256 * 8192 * 2, fused_out_features=8192)
         assert pu.custom_all_reduce._handle.oneshot_max_bytes in (128 << 10, 512 << 10)
         pu.custom_all_reduce._handle.oneshot_max_bytes = 1 << 30     # exercise the kernel at every size
-        assert (pu.custom_all_reduce.fused_handle(16, 4096, 128) is None) == (world <= 2)   # packets preferred at TP = 2
-        pu.custom_all_reduce._handle.prefer_fused_gemm = True        # ... the fused GEMM kernel is tested below
+        assert pu.custom_all_reduce.fused_handle(16, 4096, 128) is not None   # the fused GEMM kernel at every TP
+        pu.custom_all_reduce._handle.prefer_fused_gemm = False
+        assert pu.custom_all_reduce.fused_handle(16, 4096, 128) is None       # ... unless packets are asked for
+        pu.custom_all_reduce._handle.prefer_fused_gemm = True
         g = torch.Generator(device=dev).manual_seed(100 + rank)
         for shape in [(1, 8192), (16, 8192), (256, 8192), (3, 4096)]:
             x = torch.randn(shape, device=dev, generator=g).half()
