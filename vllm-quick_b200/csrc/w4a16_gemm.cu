@@ -209,6 +209,7 @@ struct Owned {
   int o, slot, last;   // o < 0: none; last = highest CTA contributing to the unit
 };
 __device__ __forceinline__ Owned find_owned(const Walk& walk, int KB, int P, int T, int cta) {
+  (void)cta;
   Owned r{-1, 0, 0};
   const int nlook = walk.nseg < 2 ? walk.nseg : 2;
   for (int idx = 0; idx < nlook; ++idx) {
