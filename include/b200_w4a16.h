@@ -247,8 +247,9 @@ int b200_w4a16_moe_scatter_add(const uint16_t *y, const int32_t *idx, const floa
  * act == 0: N' = N.  act == 1: SiLU-and-multiply in the epilogue over channel-paired gate / up
  * weights (see b200_w4a16_gemm_silu_mul), N' = N / 2.  The (expert, channel tile, K block)
  * space is cut into equal ranges over the experts WITH tokens only: every SM streams an equal
- * share of the live weights whatever the routing.  Per expert bit-identical to
- * b200_w4a16_gemm / b200_w4a16_gemm_silu_mul when one expert is live (same walk, same fix-up order).
+ * share of the live weights whatever the routing.  Per expert within the GEMM tolerance of
+ * b200_w4a16_gemm / b200_w4a16_gemm_silu_mul (other stream-K cut, other fp32 summation order; the
+ * same bits when one expert is live and the grids coincide).
  * Replaces: the per-expert launches of the dense loop in MixtralMoE.forward
  *           (vllm/model_executor/models/mixtral_quant.py:143-157; expert body :84-93). */
 int b200_w4a16_moe_grouped_gemm(const uint16_t *x, const int32_t *const *qweight,

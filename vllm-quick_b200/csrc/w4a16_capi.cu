@@ -484,6 +484,13 @@ int b200_w4a16_moe_grouped_gemm(const uint16_t* x, const int32_t* const* qweight
   if (b200::make_gemm_plan(M, K, N, G, 0, dev.sm_count, &plan) || plan.kind != b200::kKindDecode)
     return B200_ERR_BAD_SHAPE;
   if ((long long)plan.n_tiles * plan.k_blocks * n_experts >= (1LL << 31)) return B200_ERR_BAD_SHAPE;
+  if (n_experts > 1) {
+    // The single-expert plan may have sized the grid to end ranges at tile borders (short walks);
+    // over several experts' tiles the walk is long and border alignment is moot: all SMs.
+    const long long t_one = (long long)plan.n_tiles * plan.k_blocks;
+    plan.ctas = (int)(t_one < dev.sm_count ? t_one : dev.sm_count);
+    b200::fill_decode_plan(M, &plan);                        // workspace bytes follow the grid
+  }
   const size_t part_bytes = align_up(plan.ws_partial_bytes, 256);
   if (part_bytes > kMaxPartialBytes || !workspace || workspace_bytes < part_bytes || !aligned16(workspace))
     return B200_ERR_WORKSPACE;
