@@ -100,6 +100,30 @@ def test_moe_cpu_matches_reference_loop(pkg, oracle):
     assert counts.tolist() == [int((sel == e).sum()) for e in range(8)]
 
 
+def test_path_policy_by_batch_size(pkg):
+    """Which body a batch takes (MixtralMoE.select_path): decode batches grouped, then the gated
+    dense loop, device-routed from 65 tokens, host-routed from 8192 -- never under graph capture."""
+    torch.set_default_dtype(torch.float16)
+    try:
+        moe = pkg.MixtralMoE(_cfg(), pkg.AWQLinearMethod(pkg.AWQConfig(4, G, True)))
+    finally:
+        torch.set_default_dtype(torch.float32)
+    yes, no = (lambda: True), (lambda: False)
+    group = lambda t: (lambda: t <= moe.grouped_max_tokens)
+    pick = lambda t, capturing=False, fused=True: moe.select_path(t, True, capturing, group(t), fused)
+    assert [pick(t) for t in (1, 16, 17, 64, 65, 4096, 8191, 8192, 100000)] == [
+        "grouped", "grouped", "dense", "dense", "routed_on_device", "routed_on_device", "routed_on_device",
+        "routed", "routed"]
+    assert pick(8192, capturing=True) == "routed_on_device" and pick(100000, capturing=True) == "routed_on_device"
+    assert pick(300, fused=False) == "dense"                  # a linear method without the fused epilogue
+    assert moe.select_path(8, True, False, no, True) == "dense"     # e.g. group size 64: no grouped launch
+    assert moe.select_path(8, False, False, yes, True) == "dense"   # host tensors: the reference's loop
+    moe.skip_idle_experts = False
+    assert [pick(t) for t in (1, 300, 9000)] == ["dense"] * 3  # the reference's behaviour on request
+    for name in ("grouped", "dense", "routed_on_device", "routed"):
+        assert callable(getattr(moe, "_forward_" + name))
+
+
 def test_expert_gate_context_validates(pkg):
     with pytest.raises(ValueError):
         with pkg.ops.expert_gate(torch.zeros(1, dtype=torch.int32)):   # not a CUDA tensor

@@ -298,20 +298,32 @@ class MixtralMoE(nn.Module):
                 final = out if final is None else final.add_(out)
         return final
 
+    def select_path(self, tokens: int, on_gpu: bool, capturing: bool, can_group, fused_method: bool) -> str:
+        """Which body runs a batch of ``tokens``: ``"grouped"`` (decode batches, one launch per
+        projection over the local experts), ``"dense"`` (the reference's loop, idle experts gated
+        on the device), ``"routed_on_device"`` (per-expert row counts read by the kernels) or
+        ``"routed"`` (counts read once by the host; never under graph capture).  ``can_group`` is
+        called only where it matters (it may interleave the weights)."""
+        if not (on_gpu and self.skip_idle_experts):
+            return "dense"
+        if tokens >= self.routed_min_tokens and not capturing:
+            return "routed"
+        if can_group():
+            return "grouped"
+        if tokens >= self.routed_on_device_min_tokens and fused_method:
+            return "routed_on_device"
+        return "dense"
+
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
         batch_size, sequence_length, hidden_dim = hidden_states.shape
         hidden_states = hidden_states.view(-1, hidden_dim)
         hidden_states = hidden_states.contiguous()
         routing_weights, selected_experts, counts, dense_w = self._route(hidden_states)
-        routed = (self.skip_idle_experts and hidden_states.is_cuda
-                  and hidden_states.shape[0] >= self.routed_min_tokens
-                  and not torch.cuda.is_current_stream_capturing())
-        body = self._forward_routed if routed else self._forward_dense
-        if not routed and self._can_group(hidden_states):
-            body = self._forward_grouped
-        elif (not routed and self.skip_idle_experts and hidden_states.is_cuda
-              and hidden_states.shape[0] >= self.routed_on_device_min_tokens
-              and hasattr(self.experts[self.expert_indicies[0]].linear_method, "apply_weights_silu_and_mul")):
-            body = self._forward_routed_on_device
+        on_gpu = hidden_states.is_cuda
+        path = self.select_path(
+            hidden_states.shape[0], on_gpu, on_gpu and torch.cuda.is_current_stream_capturing(),
+            lambda: self._can_group(hidden_states),
+            hasattr(self.experts[self.expert_indicies[0]].linear_method, "apply_weights_silu_and_mul"))
+        body = getattr(self, "_forward_" + path)
         final = body(hidden_states, routing_weights, selected_experts, counts, dense_w)
         return tensor_model_parallel_all_reduce(final).view(batch_size, sequence_length, hidden_dim)
